@@ -1,0 +1,61 @@
+// Shared helpers of libdqn_b200: error reporting across the C ABI, checked CUDA calls.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+
+#include "../../include/dqn_b200.h"
+
+namespace dqn {
+
+// Thread-local message behind dqn_last_error().
+char* err_buf();
+int set_err(int code, const char* fmt, ...);
+
+#define DQN_CUDA(expr)                                                                              \
+  do {                                                                                              \
+    cudaError_t e__ = (expr);                                                                       \
+    if (e__ != cudaSuccess)                                                                         \
+      return ::dqn::set_err(DQN_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__),  \
+                            __FILE__, __LINE__);                                                    \
+  } while (0)
+
+#define DQN_REQUIRE(cond, code, ...)                              \
+  do {                                                            \
+    if (!(cond)) return ::dqn::set_err(code, __VA_ARGS__);        \
+  } while (0)
+
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = true;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; }
+    if (prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+    cur = dev;
+  }
+  ~DeviceGuard() { if (prev >= 0 && prev != cur) cudaSetDevice(prev); }
+  int cur = -1;
+};
+
+static inline int64_t round_up(int64_t v, int64_t m) { return (v + m - 1) / m * m; }
+
+// Ring view passed to kernels that read the replay ring (replay.cu, and the fused step).
+struct RingView {
+  const uint8_t* frames;   // frame_capacity x pitch bytes
+  const void* meta;        // capacity x 32-byte records
+  const int64_t* state;    // device {head, size}
+  int64_t capacity;
+  int64_t frame_capacity;
+  int32_t pitch;           // bytes between frames (frame_bytes rounded up to 16)
+  int32_t frame_bytes;
+  int32_t elem_bytes;
+  int32_t frames_per_state;
+};
+
+}  // namespace dqn
+
+// Internal cross-file hooks (not part of the public ABI).
+int dqn_replay_view_(dqn_replay_t h, dqn::RingView* out);
+int dqn_replay_device_(dqn_replay_t h);

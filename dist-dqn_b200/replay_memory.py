@@ -1,0 +1,223 @@
+"""ReplayMemory with the reference's surface (reference src/replay_memory.py:18-53) on top of the
+device-resident frame ring of libdqn_b200 (csrc/replay.cu).
+
+What changes underneath
+* The reference keeps (state, action, reward, next_state, terminal) tuples in a deque, i.e. every
+  frame four times in host RAM, and samples with ``random.sample(deque, k)`` (O(n) indexing).
+* Here ``add`` recognises that ``state`` is the previous transition's ``next_state`` and that
+  ``next_state`` is ``state`` shifted by one frame, and appends only the NEW frame to a ring in HBM
+  (one copy per frame).  Stacks that do not chain (episode start, arbitrary callers) are simply
+  stored in full, so any input sequence round-trips bit-exactly.
+* ``get_minibatch`` draws ``random.sample(range(size), k)`` from Python's global generator -- the
+  same logical indices ``random.sample(self.memory, k)`` picks for the same seed -- and one CUDA
+  gather kernel rebuilds the stacks.  ``sample`` is the device-resident fast path the agent uses.
+"""
+from __future__ import annotations
+
+import collections
+import random
+
+import numpy as np
+
+import _cabi as _c
+
+Batch = collections.namedtuple("Batch", "states next_states actions rewards terminals indices")
+
+
+class ReplayMemory(object):
+    def __init__(self, capacity, device=None, frame_capacity=0, trusted=False):
+        """capacity as in the reference; the rest are optional extensions: CUDA device index
+        (default: current), frame ring size (default 2*capacity+2*frames_per_state), and
+        ``trusted`` to skip the content comparison in ``add`` when ``state is previous next_state``."""
+        self._capacity = int(capacity)
+        self._device = device
+        self._frame_capacity = int(frame_capacity)
+        self._trusted = trusted
+        self._h = None
+        self._last_next = None       # the ndarray passed as next_state on the previous add
+        self._last_next_pos = -1
+        self._stack = None           # (frames_per_state, frame_shape, dtype) once known
+        self._bufs = {}
+
+    # ------------------------------------------------------------------ construction of the ring
+    @staticmethod
+    def _describe(state):
+        a = np.asarray(state)
+        if a.ndim == 3 and a.shape[-1] <= 16:
+            return a.shape[-1], a.shape[:-1], a.dtype          # HWC stack, channel = time
+        return 1, a.shape, a.dtype                             # bare frame / vector observation
+
+    def _ensure(self, state):
+        if self._h is not None:
+            return
+        import torch
+        S, fshape, dt = self._describe(state)
+        if dt.itemsize not in (1, 4, 8):
+            raise RuntimeError("unsupported observation dtype %s" % dt)
+        dev = torch.cuda.current_device() if self._device is None else int(self._device)
+        self._device = dev
+        self._stack = (S, tuple(fshape), np.dtype(dt))
+        self._elems = int(np.prod(fshape)) if len(fshape) else 1
+        h = _c.c_vp()
+        _c.check(_c.lib.dqn_replay_create(_c.C.byref(h), self._capacity, self._frame_capacity,
+                                          self._elems * dt.itemsize, dt.itemsize, S, dev), "ReplayMemory")
+        self._h = h
+
+    def __del__(self):
+        try:
+            if self._h is not None:
+                _c.lib.dqn_replay_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    @property
+    def handle(self):
+        return self._h
+
+    @property
+    def device(self):
+        return self._device
+
+    # ------------------------------------------------------------------ reference surface
+    def _frames_of(self, stack):
+        """[S, frame...] contiguous view/copy of an HWC stack (or the bare frame as [1, ...])."""
+        S, fshape, dt = self._stack
+        a = np.asarray(stack)
+        if a.dtype != dt or tuple(a.shape) != (fshape + (S,) if S > 1 else fshape):
+            raise RuntimeError("observation shape/dtype changed: got %s %s" % (a.shape, a.dtype))
+        if S == 1:
+            return np.ascontiguousarray(a).reshape((1,) + fshape)
+        return np.ascontiguousarray(np.moveaxis(a, -1, 0))
+
+    def _append(self, frames):
+        pos = _c.c_i64()
+        _c.check(_c.lib.dqn_replay_append_frames(self._h, frames.ctypes.data, frames.shape[0], _c.C.byref(pos)),
+                 "ReplayMemory.add")
+        return pos.value
+
+    def add(self, state, action, reward, observation, terminal):
+        """replay_memory.py:22-23.  ``observation`` is the next state."""
+        self._ensure(state)
+        S = self._stack[0]
+        if self._trusted:
+            chained = state is self._last_next
+        else:   # _last_next is a private copy, so in-place edits by the caller cannot fool the check
+            chained = self._last_next is not None and np.array_equal(state, self._last_next)
+        if chained:
+            spos = self._last_next_pos
+        else:
+            fr = self._frames_of(state)
+            spos = self._append(fr) + S - 1
+        nxt = np.asarray(observation)
+        nfp = _c.c_i64()
+        _c.lib.dqn_replay_next_frame_pos(self._h, _c.C.byref(nfp))
+        shifted = (nfp.value == spos + 1) and (
+            S == 1 or (self._trusted and chained) or np.array_equal(nxt[..., :-1], np.asarray(state)[..., 1:]))
+        if shifted:
+            newest = nxt[..., -1] if S > 1 else nxt
+            npos = self._append(np.ascontiguousarray(newest).reshape((1,) + self._stack[1]))
+        else:
+            npos = self._append(self._frames_of(nxt)) + S - 1
+        _c.check(_c.lib.dqn_replay_add(self._h, spos, npos, int(action), float(reward), 1 if terminal else 0),
+                 "ReplayMemory.add")
+        self._last_next = observation if self._trusted else np.array(observation, copy=True)
+        self._last_next_pos = npos
+
+    def size(self):
+        if self._h is None:
+            return 0
+        n = _c.c_i64()
+        _c.lib.dqn_replay_size(self._h, _c.C.byref(n), None)
+        return n.value
+
+    def capacity(self):
+        return self._capacity
+
+    def get_minibatch(self, minibatch_size):
+        """replay_memory.py:31-45: (non_terminal_iter, terminal_iter) of 5-tuples in sample order,
+        or (None, None) when fewer than ``minibatch_size`` transitions are stored.  Compatibility
+        path: copies the gathered batch back to the host."""
+        if self.size() < minibatch_size:
+            return None, None
+        b = self.sample(minibatch_size)
+        states = b.states.cpu().numpy()
+        nexts = b.next_states.cpu().numpy()
+        acts = b.actions.cpu().numpy()
+        rews = b.rewards.cpu().numpy()
+        terms = b.terminals.cpu().numpy()
+        items = [(states[i], int(acts[i]), float(rews[i]), nexts[i], bool(terms[i])) for i in range(minibatch_size)]
+        return (x for x in items if not x[4]), (x for x in items if x[4])
+
+    @staticmethod
+    def get_states(iterable):
+        return (item[0] for item in iterable)
+
+    @staticmethod
+    def get_next_states(iterable):
+        return (item[3] for item in iterable)
+
+    # ------------------------------------------------------------------ device-resident fast path
+    def sample_indices(self, k):
+        """The logical indices (0 = oldest) ``random.sample(self.memory, k)`` would pick in the
+        reference for the current state of Python's global generator."""
+        return random.sample(range(self.size()), k)
+
+    def _buffers(self, k):
+        import torch
+        if k not in self._bufs:
+            S, fshape, dt = self._stack
+            tdt = {np.dtype(np.uint8): torch.uint8, np.dtype(np.float32): torch.float32,
+                   np.dtype(np.float64): torch.float64, np.dtype(np.int32): torch.int32,
+                   np.dtype(np.int64): torch.int64}.get(dt)
+            if tdt is None:
+                raise RuntimeError("unsupported observation dtype %s" % dt)
+            dev = torch.device("cuda", self._device)
+            shp = (k,) + fshape + ((S,) if S > 1 else ())
+            self._bufs[k] = dict(
+                idx_pin=[torch.empty(k, dtype=torch.int32, pin_memory=True) for _ in range(4)],
+                idx_evt=[None] * 4, idx_turn=0,
+                idx=torch.empty(k, dtype=torch.int32, device=dev),
+                states=torch.empty(shp, dtype=tdt, device=dev), next_states=torch.empty(shp, dtype=tdt, device=dev),
+                actions=torch.empty(k, dtype=torch.int32, device=dev),
+                rewards=torch.empty(k, dtype=torch.float64, device=dev),
+                terminals=torch.empty(k, dtype=torch.uint8, device=dev))
+        return self._bufs[k]
+
+    def upload_indices(self, indices):
+        """Host list of logical indices -> device int32 tensor (pinned staging, async)."""
+        k = len(indices)
+        b = self._buffers(k)
+        import torch
+        t = b["idx_turn"]
+        b["idx_turn"] = (t + 1) % 4
+        if b["idx_evt"][t] is not None:
+            b["idx_evt"][t].synchronize()      # the pinned buffer may still be the source of an earlier copy
+        b["idx_pin"][t].numpy()[:] = indices
+        b["idx"].copy_(b["idx_pin"][t], non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        b["idx_evt"][t] = ev
+        return b["idx"]
+
+    def gather(self, d_indices, out=None):
+        """Gathers the transitions at the given device int32 logical indices into device tensors."""
+        k = int(d_indices.numel())
+        b = out or self._buffers(k)
+        _c.check(_c.lib.dqn_replay_gather(self._h, _c.ptr(d_indices), k, _c.ptr(b["states"]), _c.ptr(b["next_states"]),
+                                          _c.ptr(b["actions"]), _c.ptr(b["rewards"]), _c.ptr(b["terminals"]),
+                                          _c.current_stream()), "ReplayMemory.gather")
+        return Batch(b["states"], b["next_states"], b["actions"], b["rewards"], b["terminals"], d_indices)
+
+    def sample(self, k, indices=None):
+        """Device-resident minibatch: a ``Batch`` of CUDA tensors (states/next_states keep the
+        observation dtype, e.g. uint8 [k,84,84,4])."""
+        if self.size() < k:
+            raise RuntimeError("ReplayMemory.sample: only %d transitions stored, %d requested" % (self.size(), k))
+        if indices is None:
+            indices = self.sample_indices(k)
+        return self.gather(self.upload_indices(indices))
+
+    def flush(self):
+        if self._h is not None:
+            _c.check(_c.lib.dqn_replay_flush(self._h, _c.current_stream()), "ReplayMemory.flush")

@@ -1,0 +1,187 @@
+/*
+ * dqn_b200.h -- C ABI of libdqn_b200.so: the DQN minibatch-update hot path of hbfs/dist-dqn,
+ * rebuilt as hand-written CUDA for sm_100a (B200).
+ *
+ * The reference has no FFI of its own: its boundary is a Python class surface.
+ * Every entry point below therefore cites the reference Python interface (file:line under the
+ * reference's src/) whose work it takes over; the Python shells in dist-dqn_b200/ keep those
+ * class/method names and call down to this ABI through ctypes.
+ *
+ * Conventions
+ *  - every function returns 0 on success and a negative dqn_status on failure; the message is
+ *    available (thread-local) from dqn_last_error().  Nothing throws across the boundary.
+ *  - "d_" pointers are device pointers owned by the caller (e.g. torch tensors' data_ptr()); they
+ *    must stay alive until the stream reaches the work enqueued by the call.
+ *  - all work is enqueued on the caller's stream (a cudaStream_t passed as void*; NULL = the legacy
+ *    default stream).  No hidden synchronisation except where stated.
+ *  - a handle belongs to one GPU and is not thread-safe (cf. replay_memory.py:11-17).
+ *  - there is no CPU fallback anywhere: without a CUDA device every compute call fails.
+ */
+#ifndef DQN_B200_H_
+#define DQN_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct dqn_replay_s* dqn_replay_t;
+typedef struct dqn_net_s* dqn_net_t;
+typedef void* dqn_stream_t; /* cudaStream_t */
+
+enum dqn_status {
+  DQN_OK = 0,
+  DQN_ERR_INVALID = -1,  /* bad argument */
+  DQN_ERR_CUDA = -2,     /* a CUDA runtime call failed (sticky on the handle) */
+  DQN_ERR_STATE = -3,    /* call not valid in the current state (e.g. sampling more than size()) */
+  DQN_ERR_OVERFLOW = -4, /* frame ring would overwrite frames still referenced by live transitions */
+  DQN_ERR_UNSUPPORTED = -5
+};
+
+enum dqn_arch {
+  DQN_ARCH_SIMPLE = 0, /* network.py:258-313  SimpleNetwork: in -> 20 tanh -> 20 tanh -> A */
+  DQN_ARCH_CNN = 1,    /* network.py:317-424  ConvNetwork: 3 x (conv SAME + relu + 2x2 max-pool), fc256, A */
+  DQN_ARCH_NATURE = 2  /* Mnih 2015 variant (VALID convs, no pooling, fc512); north_star sweep, not in the reference */
+};
+
+enum dqn_dtype { DQN_U8 = 0, DQN_F32 = 1, DQN_F64 = 2 };
+
+enum dqn_optimizer { /* network.py:169-177 */
+  DQN_OPT_SGD = 0, DQN_OPT_MOMENTUM = 1, DQN_OPT_RMSPROP = 2, DQN_OPT_ADAM = 3,
+  DQN_OPT_ADAGRAD = 4, DQN_OPT_ADADELTA = 5, DQN_OPT_FTRL = 6
+};
+
+enum dqn_loss { DQN_LOSS_MSE = 0 /* network.py:150 */, DQN_LOSS_HUBER = 1 /* north_star variant, delta=1 */ };
+
+enum dqn_buffer { /* flat fp32 buffers behind a net handle, all in the reference's tuple order */
+  DQN_BUF_ONLINE = 0, DQN_BUF_TARGET = 1, DQN_BUF_GRAD = 2, DQN_BUF_SLOT0 = 3, DQN_BUF_SLOT1 = 4
+};
+
+/* Hyper-parameters of one update; mirrors the argparse namespace the reference passes around as
+ * `config` (main.py:28-39, 42-69): lr, reg_param, optimizer, momentum, rmsprop_decay, reward_discount. */
+typedef struct dqn_hyper {
+  double gamma;        /* --reward_discount; used in float64 like dqn_agent.py:246 */
+  float lr;            /* --lr */
+  float reg_param;     /* --reg_param (L2 on the fully-connected weights, network.py:151-152, 311, 407) */
+  float momentum;      /* --momentum (MomentumOptimizer only) */
+  float rmsprop_decay; /* --rmsprop_decay */
+  int32_t optimizer;   /* enum dqn_optimizer */
+  int32_t loss;        /* enum dqn_loss */
+  float grad_scale;    /* multiplies the data gradient before the update: 1/world_size after an
+                          all-reduce(sum) across data-parallel ranks (SyncReplicas mean, network.py:187-192) */
+  int32_t reserved;
+} dqn_hyper_t;
+
+const char* dqn_last_error(void);
+int32_t dqn_version(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * Replay ring -- replaces ReplayMemory (replay_memory.py:18-53) and the frame stacking that
+ * FrameBuffer.get_state() materialises per transition (frame_buffer.py:40-51).
+ *
+ * HBM layout: ONE copy of every frame in a byte ring (frame_capacity x frame_bytes) plus a
+ * 32-byte record per transition {state_pos, next_pos, reward f64, action i32, terminal u8};
+ * state_pos/next_pos are the ring positions of the NEWEST frame of each stack, whose
+ * frames_per_state frames are consecutive.  Logical index 0 is the oldest live transition and
+ * the oldest is evicted on every add when full, exactly like deque(maxlen) (replay_memory.py:20-23).
+ * ------------------------------------------------------------------------------------------------ */
+
+/* ReplayMemory.__init__ (replay_memory.py:19-20).  frame_bytes: bytes of one preprocessed frame
+ * (84*84 for Atari, 8*obs_dim for float64 vector observations), must be a multiple of
+ * elem_bytes; elem_bytes in {1,4,8} is the size of one frame element (stack interleave unit);
+ * frame_capacity 0 = 2*capacity + 2*frames_per_state. */
+int dqn_replay_create(dqn_replay_t* out, int64_t capacity, int64_t frame_capacity, int32_t frame_bytes,
+                      int32_t elem_bytes, int32_t frames_per_state, int32_t device);
+int dqn_replay_destroy(dqn_replay_t h);
+
+/* Appends n consecutive frames from HOST memory to the frame ring (staged in pinned memory, sent
+ * by the next flush); *first_pos receives the ring position of the first one.  Together with
+ * dqn_replay_add this is ReplayMemory.add (replay_memory.py:22-23): the Python shell appends only
+ * the frames it has not stored yet (normally one per env step). */
+int dqn_replay_append_frames(dqn_replay_t h, const void* host_frames, int32_t n, int64_t* first_pos);
+/* Same, from DEVICE memory (device-side actors; enqueued on stream immediately). */
+int dqn_replay_append_frames_device(dqn_replay_t h, const void* d_frames, int32_t n, int64_t* first_pos,
+                                    dqn_stream_t stream);
+/* Records one transition whose state / next_state stacks end at the given frame positions. */
+int dqn_replay_add(dqn_replay_t h, int64_t state_pos, int64_t next_pos, int32_t action, double reward,
+                   uint8_t terminal);
+/* Sends staged frames + records to the device (async H2D on stream). Called by gather itself. */
+int dqn_replay_flush(dqn_replay_t h, dqn_stream_t stream);
+/* ReplayMemory.size / capacity (replay_memory.py:25-29); host-side counters, no sync. */
+int dqn_replay_size(dqn_replay_t h, int64_t* size, int64_t* capacity);
+/* Frame-ring position that the next appended frame will get. */
+int dqn_replay_next_frame_pos(dqn_replay_t h, int64_t* pos);
+
+/* The gather behind ReplayMemory.get_minibatch + get_states/get_next_states + the feed conversion
+ * (replay_memory.py:31-53, dqn_agent.py:186-189, 249-253): for each logical index (0 = oldest,
+ * the values random.sample(range(size), k) yields) rebuilds state and next_state stacks
+ * [k][frame elems][frames_per_state] (HWC, channel = time, oldest -> newest, frame_buffer.py:51)
+ * and copies action / reward / terminal.  Any of the five outputs may be NULL.  Bit-exact. */
+int dqn_replay_gather(dqn_replay_t h, const int32_t* d_logical_idx, int32_t k, void* d_states,
+                      void* d_next_states, int32_t* d_actions, double* d_rewards, uint8_t* d_terminals,
+                      dqn_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Q-network -- replaces Network.create_network and the graph it builds (network.py:13-116), the
+ * session.run calls of DQNAgent (dqn_agent.py:132-138, 189, 222) and the host TD-target loop
+ * (dqn_agent.py:118-125, 224-253).
+ *
+ * Parameters live in ONE flat fp32 buffer per set (online, target, gradient, two optimizer slots),
+ * tensors in the reference's tuple order (network.py:296, 387) and TF layouts (HWIO conv filters,
+ * [in,out] matrices), each tensor starting at a multiple of 4 floats.
+ * ------------------------------------------------------------------------------------------------ */
+
+/* Network.create_network (network.py:35-57).  in_shape: {dim} for SIMPLE, {84,84,4} for CNN/NATURE.
+ * in_dtype: element type of the states the net is fed (DQN_U8 frames, DQN_F32, or DQN_F64 vectors).
+ * Weights start at zero: the shell draws truncated_normal(0.01) (network.py:269, 341) and uploads. */
+int dqn_net_create(dqn_net_t* out, int32_t arch, const int32_t* in_shape, int32_t in_rank,
+                   int32_t num_actions, int32_t max_batch, int32_t in_dtype, int32_t device);
+int dqn_net_destroy(dqn_net_t h);
+int dqn_net_param_count(dqn_net_t h, int64_t* padded_floats, int32_t* num_tensors);
+/* Tensor i of the reference's params tuple: offset (floats) into a flat buffer, element count, shape. */
+int dqn_net_tensor_info(dqn_net_t h, int32_t i, int64_t* offset, int64_t* numel, int32_t* rank, int64_t shape[4]);
+/* Device pointer of a flat buffer (enum dqn_buffer). */
+int dqn_net_buffer(dqn_net_t h, int32_t which, float** d_ptr, int64_t* floats);
+/* Synchronous host<->device copies of a whole flat buffer (init / checkpoint / tests). */
+int dqn_net_upload(dqn_net_t h, int32_t which, const float* host, int64_t floats);
+int dqn_net_download(dqn_net_t h, int32_t which, float* host, int64_t floats);
+/* (Re)initialises optimizer slots the way TF does for h->optimizer (RMSProp ms=1, Adagrad/Ftrl 0.1)
+ * and resets the update counter (global_step, network.py:83). */
+int dqn_net_set_hyper(dqn_net_t h, const dqn_hyper_t* hyper, int32_t reset_slots);
+int dqn_net_global_step(dqn_net_t h, int64_t* step, dqn_stream_t stream); /* synchronises the stream */
+
+/* DQNAgent._predict_q_values (dqn_agent.py:176-189): forward of n states through the online
+ * (which = DQN_BUF_ONLINE) or target (DQN_BUF_TARGET) parameters -> d_q [n][A]; if d_argmax is not
+ * NULL also the greedy action per row (first maximum, dqn_agent.py:159-160). n <= max_batch. */
+int dqn_net_forward(dqn_net_t h, int32_t which, const void* d_x, int32_t n, float* d_q, int32_t* d_argmax,
+                    dqn_stream_t stream);
+
+/* One minibatch update (DQNAgent._train_minibatch, dqn_agent.py:108-143, minus sampling and the
+ * target-sync cadence): target forward on next_states, y = r + gamma*max_a Q_target (0 bootstrap for
+ * terminals, float64 then rounded to float32), online forward, loss (network.py:149-152), backward,
+ * optimizer update (network.py:198-202), global_step += 1.  d_loss (device float) and d_q
+ * (device [k][A], the online Q-values before the update) may be NULL. */
+int dqn_net_train_step(dqn_net_t h, const void* d_states, const void* d_next_states, const int32_t* d_actions,
+                       const double* d_rewards, const uint8_t* d_terminals, int32_t k, float* d_loss, float* d_q,
+                       dqn_stream_t stream);
+/* The same step split for data parallelism: backward leaves the LOCAL mean gradient of the data
+ * term (no L2 term) in the DQN_BUF_GRAD buffer (include_reg != 0 adds reg_param*w, for parity
+ * checks); the caller all-reduces that buffer; apply runs the optimizer on grad_scale * grad
+ * (+ reg_param*w) and bumps global_step. */
+int dqn_net_backward(dqn_net_t h, const void* d_states, const void* d_next_states, const int32_t* d_actions,
+                     const double* d_rewards, const uint8_t* d_terminals, int32_t k, float* d_loss, float* d_q,
+                     int32_t include_reg, dqn_stream_t stream);
+int dqn_net_apply(dqn_net_t h, dqn_stream_t stream);
+/* DQNAgent._update_target_network's assigns (dqn_agent.py:215-222, network.py:251-252): one D2D copy. */
+int dqn_net_target_sync(dqn_net_t h, dqn_stream_t stream);
+
+/* Sample-to-update in one call: gather from the ring (d_logical_idx as in dqn_replay_gather) into the
+ * net's own staging buffers, then dqn_net_train_step.  This is the unit bench.py times. */
+int dqn_train_step(dqn_net_t net, dqn_replay_t replay, const int32_t* d_logical_idx, int32_t k, float* d_loss,
+                   dqn_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DQN_B200_H_ */
