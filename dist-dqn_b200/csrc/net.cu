@@ -1,19 +1,903 @@
-// TEMPORARY stub so the ring can be exercised on the GPU first; replaced by the real kernels.
+// Q-network training step: everything Network.create_network builds (reference src/network.py:13-424)
+// and DQNAgent runs through session.run (src/dqn_agent.py:108-143, 176-189, 215-253), as hand-written
+// CUDA kernels over flat parameter buffers.
+//
+// Kernel inventory (fp32 path)
+//   conv_fwd_kernel     conv/fc + bias + ReLU + 2x2 max-pool, online and target pass in one launch
+//   td_head_kernel      Q head of both nets, max_a Q_target, TD target (float64), loss term, dL/dQ,
+//                       gradient into the last hidden layer      (dqn_agent.py:118-125, 242-246; network.py:149-150)
+//   head_wgrad_kernel   gradient of the head weights/bias
+//   conv_wgrad_kernel   weight + bias gradients, split over the batch into scratch partial sums
+//   conv_dgrad_kernel   gradient into the previous layer's activations
+//   optimizer_kernel    adds the partial sums up, L2 term, and applies one of TF's 7 update rules (network.py:169-202)
+//   mlp_*_kernel        the 4-20-20-A tanh net of SimpleNetwork as warp-level kernels (network.py:258-313)
 #include "common.cuh"
+#include "gemm_core.cuh"
+
+#include <cmath>
+#include <new>
+#include <vector>
+
+namespace dqn {
+
+// ConvNetwork (network.py:318-333, 389-424) on 84x84x4: SAME pads (2,2),(1,2),(1,1); pools 21->11, 6->3, 3->2
+using C1 = Geo<84, 84, 4, 8, 4, 2, 2, 21, 21, 32, true>;
+using C2 = Geo<11, 11, 32, 4, 2, 1, 1, 6, 6, 64, true>;
+using C3 = Geo<3, 3, 64, 3, 1, 1, 1, 3, 3, 64, true>;
+using F4 = Geo<1, 1, 256, 1, 1, 0, 0, 1, 1, 256, false>;
+// Nature-paper variant: VALID convs, no pooling, fc 512
+using N1 = Geo<84, 84, 4, 8, 4, 0, 0, 20, 20, 32, false>;
+using N2 = Geo<20, 20, 32, 4, 2, 0, 0, 9, 9, 64, false>;
+using N3 = Geo<9, 9, 64, 3, 1, 0, 0, 7, 7, 64, false>;
+using NF = Geo<1, 1, 3136, 1, 1, 0, 0, 1, 1, 512, false>;
+
+constexpr int HID = 20;          // SimpleNetwork.HIDDEN1_SIZE == HIDDEN2_SIZE (network.py:255-256)
+constexpr int MLP_MAX_IN = 16;
+constexpr int MLP_MAX_A = 16;
+constexpr int MLP_WARPS = 8;
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__device__ __forceinline__ void td_terms(float q_sel, float maxq, double reward, bool terminal, double gamma, int B,
+                                         int loss_kind, float* se, float* g) {
+  // dqn_agent.py:242-246: python float64 arithmetic, rounded to float32 by the q_placeholder
+  const float y = (float)(reward + gamma * (terminal ? 0.0 : (double)maxq));
+  const float diff = q_sel - y;
+  if (loss_kind == DQN_LOSS_HUBER) {
+    const float ad = fabsf(diff);
+    *se = ad <= 1.f ? 0.5f * diff * diff : ad - 0.5f;
+    *g = fminf(fmaxf(diff, -1.f), 1.f) / (float)B;
+  } else {                                   // network.py:150  reduce_mean(squared_difference)
+    *se = diff * diff;
+    *g = 2.f * diff / (float)B;
+  }
+}
+
+// One warp per sample.
+__global__ void __launch_bounds__(256)
+td_head_kernel(const float* __restrict__ h_on, const float* __restrict__ h_tg, const float* __restrict__ w_on,
+               const float* __restrict__ b_on, const float* __restrict__ w_tg, const float* __restrict__ b_tg,
+               const int32_t* __restrict__ actions, const double* __restrict__ rewards,
+               const uint8_t* __restrict__ terminals, int B, int F, int A, double gamma, int loss_kind,
+               float* __restrict__ qout, float* __restrict__ se, float* __restrict__ g, float* __restrict__ dh,
+               long long* __restrict__ step) {
+  const int lane = threadIdx.x & 31;
+  const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (blockIdx.x == 0 && threadIdx.x == 0) *step += 1;      // global_step (network.py:83, 198-202)
+  if (b >= B) return;
+  const float* x = h_on + (size_t)b * F;
+  const float* xt = h_tg + (size_t)b * F;
+  const int act = actions[b];
+  float q_sel = 0.f, maxq = 0.f;
+  for (int a = 0; a < A; ++a) {
+    float s = 0.f, st = 0.f;
+    for (int j = lane; j < F; j += 32) {
+      s = fmaf(x[j], w_on[j * A + a], s);
+      st = fmaf(xt[j], w_tg[j * A + a], st);
+    }
+    s = warp_sum(s) + b_on[a];
+    st = warp_sum(st) + b_tg[a];
+    if (qout && lane == 0) qout[(size_t)b * A + a] = s;
+    if (a == 0 || st > maxq) maxq = st;
+    if (a == act) q_sel = s;
+  }
+  float e, gg;
+  td_terms(q_sel, maxq, rewards[b], terminals[b] != 0, gamma, B, loss_kind, &e, &gg);
+  if (lane == 0) { se[b] = e; g[b] = gg; }
+  for (int j = lane; j < F; j += 32) dh[(size_t)b * F + j] = gg * w_on[j * A + act];
+}
+
+// out[(F+1)*A]: rows 0..F-1 = dL/dw5 (data term), row F = dL/db5.
+__global__ void __launch_bounds__(256)
+head_wgrad_kernel(const float* __restrict__ h_on, const float* __restrict__ g, const int32_t* __restrict__ actions,
+                  int B, int F, int A, float* __restrict__ out) {
+  const int o = blockIdx.x * blockDim.x + threadIdx.x;
+  if (o >= (F + 1) * A) return;
+  const int j = o / A, a = o - j * A;
+  float s = 0.f;
+  if (j < F) {
+    for (int b = 0; b < B; ++b) s += (actions[b] == a) ? h_on[(size_t)b * F + j] * g[b] : 0.f;
+  } else {
+    for (int b = 0; b < B; ++b) s += (actions[b] == a) ? g[b] : 0.f;
+  }
+  out[o] = s;
+}
+
+// Predict path (dqn_agent.py:176-189, 159-160): q = h @ w + b, optional row-wise arg-max (first maximum).
+__global__ void __launch_bounds__(256)
+head_forward_kernel(const float* __restrict__ h, const float* __restrict__ w, const float* __restrict__ bias, int n,
+                    int F, int A, float* __restrict__ q, int32_t* __restrict__ argmax) {
+  const int lane = threadIdx.x & 31;
+  const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (b >= n) return;
+  const float* x = h + (size_t)b * F;
+  float best = 0.f;
+  int bi = 0;
+  for (int a = 0; a < A; ++a) {
+    float s = 0.f;
+    for (int j = lane; j < F; j += 32) s = fmaf(x[j], w[j * A + a], s);
+    s = warp_sum(s) + bias[a];
+    if (q && lane == 0) q[(size_t)b * A + a] = s;
+    if (a == 0 || s > best) { best = s; bi = a; }
+  }
+  if (argmax && lane == 0) argmax[b] = bi;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Optimizer (network.py:159-203): one thread per parameter; the gradient is the fixed-order sum of
+// the wgrad partials (or the all-reduced flat gradient), times grad_scale, plus reg_param * w on
+// the regularised tensors (network.py:151-152).  Update rules are TF r0.9-era (see oracle/net_ref.py).
+// ------------------------------------------------------------------------------------------------
+struct Seg {
+  long long off;          // first float of the segment [w | b] in the flat buffers
+  int len;                // K*N + N
+  int reg_len;            // leading floats under L2 (K*N or 0)
+  const float* partial;   // [nsplit][stride]
+  int nsplit;
+  long long stride;
+};
+constexpr int MAX_SEGS = 6;
+struct OptArgs {
+  Seg seg[MAX_SEGS];
+  int nseg;
+  float* w;
+  float* s0;
+  float* s1;
+  const long long* step;
+  float lr, reg, momentum, decay, gscale;
+  int opt;
+};
+
+__device__ __forceinline__ float seg_grad(const Seg& s, int i) {
+  float gsum = 0.f;
+  for (int k = 0; k < s.nsplit; ++k) gsum += s.partial[(size_t)k * s.stride + i];
+  return gsum;
+}
+
+__global__ void __launch_bounds__(256) optimizer_kernel(OptArgs a) {
+  const Seg s = a.seg[blockIdx.y];
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  __shared__ float lr_t_s;
+  if (a.opt == DQN_OPT_ADAM) {
+    if (threadIdx.x == 0) {
+      const double t = (double)*a.step;
+      lr_t_s = (float)((double)a.lr * sqrt(1.0 - pow(0.999, t)) / (1.0 - pow(0.9, t)));
+    }
+    __syncthreads();
+  }
+  if (i >= s.len) return;
+  const size_t p = (size_t)s.off + i;
+  float w = a.w[p];
+  float g = seg_grad(s, i) * a.gscale;
+  if (i < s.reg_len) g = fmaf(a.reg, w, g);
+  switch (a.opt) {
+    case DQN_OPT_SGD:
+      w -= a.lr * g;
+      break;
+    case DQN_OPT_MOMENTUM: {
+      const float acc = a.momentum * a.s0[p] + g;
+      a.s0[p] = acc;
+      w -= a.lr * acc;
+    } break;
+    case DQN_OPT_RMSPROP: {
+      float ms = a.s0[p];
+      ms += (1.f - a.decay) * (g * g - ms);
+      const float mom = a.lr * g / sqrtf(ms + 1e-10f);      // TF default momentum = 0
+      a.s0[p] = ms;
+      a.s1[p] = mom;
+      w -= mom;
+    } break;
+    case DQN_OPT_ADAM: {
+      float m = a.s0[p], v = a.s1[p];
+      m += (1.f - 0.9f) * (g - m);
+      v += (1.f - 0.999f) * (g * g - v);
+      a.s0[p] = m;
+      a.s1[p] = v;
+      w -= lr_t_s * m / (sqrtf(v) + 1e-8f);
+    } break;
+    case DQN_OPT_ADAGRAD: {
+      const float acc = a.s0[p] + g * g;
+      a.s0[p] = acc;
+      w -= a.lr * g / sqrtf(acc);
+    } break;
+    case DQN_OPT_ADADELTA: {
+      float acc = a.s0[p], accu = a.s1[p];
+      acc = 0.95f * acc + 0.05f * g * g;
+      const float u = sqrtf(accu + 1e-8f) / sqrtf(acc + 1e-8f) * g;
+      accu = 0.95f * accu + 0.05f * u * u;
+      a.s0[p] = acc;
+      a.s1[p] = accu;
+      w -= a.lr * u;
+    } break;
+    case DQN_OPT_FTRL: {
+      const float acc = a.s0[p];
+      float lin = a.s1[p];
+      const float nacc = acc + g * g;
+      lin += g - (sqrtf(nacc) - sqrtf(acc)) / a.lr * w;
+      w = -lin / (sqrtf(nacc) / a.lr);
+      a.s0[p] = nacc;
+      a.s1[p] = lin;
+    } break;
+  }
+  a.w[p] = w;
+}
+
+// Materialises the flat gradient (data-parallel path and parity checks).
+__global__ void __launch_bounds__(256) reduce_grad_kernel(OptArgs a, float* __restrict__ grad, float reg) {
+  const Seg s = a.seg[blockIdx.y];
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= s.len) return;
+  float g = seg_grad(s, i);
+  if (i < s.reg_len) g = fmaf(reg, a.w[(size_t)s.off + i], g);
+  grad[(size_t)s.off + i] = g;
+}
+
+// loss = mean_b se_b + reg * sum_{reg tensors} ||w||^2 / 2   (network.py:150-152); one CTA.
+__global__ void __launch_bounds__(256) loss_kernel(OptArgs a, const float* __restrict__ se, int B, float* __restrict__ out) {
+  __shared__ float red[256];
+  float s = 0.f;
+  for (int b = threadIdx.x; b < B; b += 256) s += se[b];
+  s /= (float)B;
+  float r = 0.f;
+  for (int k = 0; k < a.nseg; ++k) {
+    const Seg sg = a.seg[k];
+    for (int i = threadIdx.x; i < sg.reg_len; i += 256) {
+      const float w = a.w[(size_t)sg.off + i];
+      r = fmaf(w, w, r);
+    }
+  }
+  red[threadIdx.x] = s + 0.5f * a.reg * r;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *out = red[0];
+}
+
+__global__ void fill_kernel(float* p, long long n, float v) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) p[i] = v;
+}
+
+// ------------------------------------------------------------------------------------------------
+// SimpleNetwork (network.py:258-313): lane j of a warp owns hidden unit j of both hidden layers.
+// ------------------------------------------------------------------------------------------------
+struct MlpOff { int w1, b1, w2, b2, w3, b3, total; };
+
+template <typename TIn>
+__device__ __forceinline__ void mlp_forward_lane(const float* __restrict__ w, const MlpOff& o, const TIn* __restrict__ xin,
+                                                 int IN, int A, int lane, float xv[MLP_MAX_IN], float* h1o, float* h2o,
+                                                 float* qo) {
+  const int j = lane < HID ? lane : HID - 1;
+#pragma unroll
+  for (int i = 0; i < MLP_MAX_IN; ++i) xv[i] = i < IN ? (float)xin[i] : 0.f;   // float32 placeholder feed (network.py:61)
+  float s = w[o.b1 + j];
+#pragma unroll
+  for (int i = 0; i < MLP_MAX_IN; ++i)
+    if (i < IN) s = fmaf(xv[i], w[o.w1 + i * HID + j], s);
+  const float h1 = lane < HID ? tanhf(s) : 0.f;
+  s = w[o.b2 + j];
+#pragma unroll
+  for (int i = 0; i < HID; ++i) s = fmaf(__shfl_sync(0xffffffffu, h1, i), w[o.w2 + i * HID + j], s);
+  const float h2 = lane < HID ? tanhf(s) : 0.f;
+  const int a = lane < A ? lane : A - 1;
+  s = w[o.b3 + a];
+#pragma unroll
+  for (int i = 0; i < HID; ++i) s = fmaf(__shfl_sync(0xffffffffu, h2, i), w[o.w3 + i * A + a], s);
+  *h1o = h1; *h2o = h2; *qo = s;            // q valid on lanes < A
+}
+
+template <typename TIn>
+__global__ void __launch_bounds__(256)
+mlp_forward_kernel(const TIn* __restrict__ x, int n, int IN, int A, MlpOff o, const float* __restrict__ params,
+                   float* __restrict__ q, int32_t* __restrict__ argmax) {
+  extern __shared__ float sm[];
+  for (int t = threadIdx.x; t < o.total; t += blockDim.x) sm[t] = params[t];
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (b >= n) return;
+  float xv[MLP_MAX_IN], h1, h2, qv;
+  mlp_forward_lane<TIn>(sm, o, x + (size_t)b * IN, IN, A, lane, xv, &h1, &h2, &qv);
+  if (q && lane < A) q[(size_t)b * A + lane] = qv;
+  if (argmax) {
+    float best = __shfl_sync(0xffffffffu, qv, 0);
+    int bi = 0;
+    for (int a = 1; a < A; ++a) {
+      const float v = __shfl_sync(0xffffffffu, qv, a);
+      if (v > best) { best = v; bi = a; }
+    }
+    if (lane == 0) argmax[b] = bi;
+  }
+}
+
+// Whole backward of SimpleNetwork in ONE CTA: both forwards, TD target, loss term, all gradients
+// (batch mean, data term) into the flat gradient buffer.
+template <typename TIn>
+__global__ void __launch_bounds__(MLP_WARPS * 32)
+mlp_backward_kernel(const TIn* __restrict__ states, const TIn* __restrict__ next_states,
+                    const int32_t* __restrict__ actions, const double* __restrict__ rewards,
+                    const uint8_t* __restrict__ terminals, int B, int IN, int A, MlpOff o,
+                    const float* __restrict__ online, const float* __restrict__ target, double gamma, int loss_kind,
+                    float* __restrict__ grad, float* __restrict__ qout, float* __restrict__ se_out,
+                    long long* __restrict__ step) {
+  extern __shared__ float sm[];
+  float* w = sm;
+  float* wt = sm + o.total;
+  float* accs = sm + 2 * o.total;                   // [MLP_WARPS][total]
+  for (int t = threadIdx.x; t < o.total; t += blockDim.x) { w[t] = online[t]; wt[t] = target[t]; }
+  for (int t = threadIdx.x; t < MLP_WARPS * o.total; t += blockDim.x) accs[t] = 0.f;
+  if (threadIdx.x == 0) *step += 1;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int j = lane < HID ? lane : HID - 1;
+  float dw1[MLP_MAX_IN], dw2[HID], dw3[MLP_MAX_A];
+  float db1 = 0.f, db2 = 0.f, db3 = 0.f;
+#pragma unroll
+  for (int i = 0; i < MLP_MAX_IN; ++i) dw1[i] = 0.f;
+#pragma unroll
+  for (int i = 0; i < HID; ++i) dw2[i] = 0.f;
+#pragma unroll
+  for (int i = 0; i < MLP_MAX_A; ++i) dw3[i] = 0.f;
+  for (int b = warp; b < B; b += MLP_WARPS) {
+    float xv[MLP_MAX_IN], xn[MLP_MAX_IN], h1, h2, qv, t1, t2, tq;
+    mlp_forward_lane<TIn>(w, o, states + (size_t)b * IN, IN, A, lane, xv, &h1, &h2, &qv);
+    mlp_forward_lane<TIn>(wt, o, next_states + (size_t)b * IN, IN, A, lane, xn, &t1, &t2, &tq);
+    float maxq = lane < A ? tq : -INFINITY;
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) maxq = fmaxf(maxq, __shfl_xor_sync(0xffffffffu, maxq, s));
+    const int act = actions[b];
+    const float q_sel = __shfl_sync(0xffffffffu, qv, act);
+    float e, g;
+    td_terms(q_sel, maxq, rewards[b], terminals[b] != 0, gamma, B, loss_kind, &e, &g);
+    if (lane == 0) se_out[b] = e;
+    if (qout && lane < A) qout[(size_t)b * A + lane] = qv;
+    // output layer
+#pragma unroll
+    for (int a = 0; a < MLP_MAX_A; ++a)
+      if (a == act) dw3[a] = fmaf(h2, g, dw3[a]);
+    if (lane == act) db3 += g;
+    const float d2 = lane < HID ? g * w[o.w3 + j * A + act] * (1.f - h2 * h2) : 0.f;
+#pragma unroll
+    for (int i = 0; i < HID; ++i) dw2[i] = fmaf(__shfl_sync(0xffffffffu, h1, i), d2, dw2[i]);
+    db2 += d2;
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < HID; ++k) s = fmaf(__shfl_sync(0xffffffffu, d2, k), w[o.w2 + j * HID + k], s);
+    const float d1 = lane < HID ? s * (1.f - h1 * h1) : 0.f;
+#pragma unroll
+    for (int i = 0; i < MLP_MAX_IN; ++i) dw1[i] = fmaf(xv[i], d1, dw1[i]);
+    db1 += d1;
+  }
+  float* my = accs + warp * o.total;
+  if (lane < HID) {
+#pragma unroll
+    for (int i = 0; i < MLP_MAX_IN; ++i)
+      if (i < IN) my[o.w1 + i * HID + lane] = dw1[i];
+    my[o.b1 + lane] = db1;
+#pragma unroll
+    for (int i = 0; i < HID; ++i) my[o.w2 + i * HID + lane] = dw2[i];
+    my[o.b2 + lane] = db2;
+#pragma unroll
+    for (int a = 0; a < MLP_MAX_A; ++a)
+      if (a < A) my[o.w3 + lane * A + a] = dw3[a];
+  }
+  if (lane < A) my[o.b3 + lane] = db3;
+  __syncthreads();
+  for (int t = threadIdx.x; t < o.total; t += blockDim.x) {
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < MLP_WARPS; ++k) s += accs[k * o.total + t];
+    grad[t] = s;
+  }
+}
+
+}  // namespace dqn
+
+// ================================================================================================
+// Host side
+// ================================================================================================
 using namespace dqn;
-#define STUB(name, ...) extern "C" int name(__VA_ARGS__) { return set_err(DQN_ERR_UNSUPPORTED, #name ": not built yet"); }
-STUB(dqn_net_create, dqn_net_t*, int32_t, const int32_t*, int32_t, int32_t, int32_t, int32_t, int32_t)
-STUB(dqn_net_destroy, dqn_net_t)
-STUB(dqn_net_param_count, dqn_net_t, int64_t*, int32_t*)
-STUB(dqn_net_tensor_info, dqn_net_t, int32_t, int64_t*, int64_t*, int32_t*, int64_t*)
-STUB(dqn_net_buffer, dqn_net_t, int32_t, float**, int64_t*)
-STUB(dqn_net_upload, dqn_net_t, int32_t, const float*, int64_t)
-STUB(dqn_net_download, dqn_net_t, int32_t, float*, int64_t)
-STUB(dqn_net_set_hyper, dqn_net_t, const dqn_hyper_t*, int32_t)
-STUB(dqn_net_global_step, dqn_net_t, int64_t*, dqn_stream_t)
-STUB(dqn_net_forward, dqn_net_t, int32_t, const void*, int32_t, float*, int32_t*, dqn_stream_t)
-STUB(dqn_net_train_step, dqn_net_t, const void*, const void*, const int32_t*, const double*, const uint8_t*, int32_t, float*, float*, dqn_stream_t)
-STUB(dqn_net_backward, dqn_net_t, const void*, const void*, const int32_t*, const double*, const uint8_t*, int32_t, float*, float*, int32_t, dqn_stream_t)
-STUB(dqn_net_apply, dqn_net_t, dqn_stream_t)
-STUB(dqn_net_target_sync, dqn_net_t, dqn_stream_t)
-STUB(dqn_train_step, dqn_net_t, dqn_replay_t, const int32_t*, int32_t, float*, dqn_stream_t)
+
+namespace {
+struct Tensor { int64_t off, numel; int rank; int64_t shape[4]; };
+
+struct GemmLayer {           // conv1..3 + fc of the conv architectures
+  int K, N, rows, in_elems, out_elems;
+  int maxsplit;
+  float* partial = nullptr;
+  int w_tensor;              // index of the weight tensor (bias = +1)
+};
+}  // namespace
+
+struct dqn_net_s {
+  int device = 0, arch = 0, A = 0, MB = 0, in_dtype = 0, in_dim = 0, F = 0;
+  int num_sms = 148;
+  int64_t P = 0;
+  std::vector<Tensor> tensors;
+  float *online = nullptr, *target = nullptr, *grad = nullptr, *slot0 = nullptr, *slot1 = nullptr;
+  GemmLayer L[4];
+  float* act[2][4] = {};         // [pass][layer] pooled activations; layer 3 = fc output
+  uint8_t* arg[2][3] = {};
+  float* dact[4] = {};
+  float* head_partial = nullptr; // (F+1)*A
+  float *se = nullptr, *g = nullptr, *loss_tmp = nullptr, *q_tmp = nullptr;
+  long long* step = nullptr;
+  void *st_states = nullptr, *st_next = nullptr;
+  int32_t* st_actions = nullptr;
+  double* st_rewards = nullptr;
+  uint8_t* st_term = nullptr;
+  size_t state_bytes = 0;        // bytes of one state
+  dqn_hyper_t hyper;
+  MlpOff mo;
+  std::vector<void*> allocs;
+};
+
+static int dev_alloc(dqn_net_s* h, void** p, size_t bytes) {
+  DQN_CUDA(cudaMalloc(p, bytes ? bytes : 16));
+  DQN_CUDA(cudaMemset(*p, 0, bytes ? bytes : 16));
+  h->allocs.push_back(*p);
+  return 0;
+}
+#define NET_ALLOC(ptr, bytes)                                         \
+  do {                                                                \
+    int rc__ = dev_alloc(h, reinterpret_cast<void**>(&(ptr)), bytes); \
+    if (rc__) { dqn_net_destroy(h); return rc__; }                    \
+  } while (0)
+
+static void add_tensor(dqn_net_s* h, std::initializer_list<int64_t> shape) {
+  Tensor t{};
+  t.off = h->P;
+  t.rank = (int)shape.size();
+  t.numel = 1;
+  int i = 0;
+  for (int64_t s : shape) { t.shape[i++] = s; t.numel *= s; }
+  h->P += round_up(t.numel, 4);
+  h->tensors.push_back(t);
+}
+
+extern "C" int dqn_net_create(dqn_net_t* out, int32_t arch, const int32_t* in_shape, int32_t in_rank,
+                              int32_t num_actions, int32_t max_batch, int32_t in_dtype, int32_t device) {
+  DQN_REQUIRE(out && in_shape, DQN_ERR_INVALID, "dqn_net_create: NULL argument");
+  *out = nullptr;
+  DQN_REQUIRE(arch == DQN_ARCH_SIMPLE || arch == DQN_ARCH_CNN || arch == DQN_ARCH_NATURE, DQN_ERR_INVALID,
+              "Unsupported network type %d", arch);                          // network.py:46-47
+  DQN_REQUIRE(num_actions >= 1, DQN_ERR_INVALID, "num_actions must be positive");
+  DQN_REQUIRE(max_batch >= 1 && max_batch <= 4096, DQN_ERR_INVALID, "max_batch must be in [1, 4096]");
+  if (arch == DQN_ARCH_SIMPLE) {
+    DQN_REQUIRE(in_rank == 1, DQN_ERR_INVALID, "SimpleNetwork expects 1-d input");         // network.py:265-266
+    DQN_REQUIRE(in_shape[0] >= 1 && in_shape[0] <= MLP_MAX_IN, DQN_ERR_UNSUPPORTED,
+                "SimpleNetwork kernel supports 1..%d inputs, got %d", MLP_MAX_IN, in_shape[0]);
+    DQN_REQUIRE(num_actions <= MLP_MAX_A, DQN_ERR_UNSUPPORTED, "SimpleNetwork kernel supports up to %d actions", MLP_MAX_A);
+    DQN_REQUIRE(in_dtype == DQN_F32 || in_dtype == DQN_F64, DQN_ERR_INVALID, "SimpleNetwork input must be f32 or f64");
+  } else {
+    DQN_REQUIRE(in_rank == 3, DQN_ERR_INVALID, "ConvNetwork expects 3-d input");           // network.py:338-339
+    DQN_REQUIRE(in_shape[0] == 84 && in_shape[1] == 84 && in_shape[2] == 4, DQN_ERR_UNSUPPORTED,
+                "conv kernels are specialised for 84x84x4 input (the reference's fc layer fixes this too, "
+                "network.py:372-373); got %dx%dx%d", in_shape[0], in_shape[1], in_shape[2]);
+    DQN_REQUIRE(in_dtype == DQN_U8 || in_dtype == DQN_F32, DQN_ERR_INVALID, "ConvNetwork input must be u8 or f32");
+    DQN_REQUIRE(num_actions <= 64, DQN_ERR_UNSUPPORTED, "at most 64 actions");
+  }
+  int ndev = 0;
+  DQN_CUDA(cudaGetDeviceCount(&ndev));
+  DQN_REQUIRE(device >= 0 && device < ndev, DQN_ERR_INVALID, "no CUDA device %d (found %d); there is no CPU path", device, ndev);
+  DeviceGuard guard(device);
+  DQN_REQUIRE(guard.ok, DQN_ERR_CUDA, "cannot select device %d", device);
+  dqn_net_s* h = new (std::nothrow) dqn_net_s();
+  DQN_REQUIRE(h, DQN_ERR_INVALID, "out of host memory");
+  h->device = device; h->arch = arch; h->A = num_actions; h->MB = max_batch; h->in_dtype = in_dtype;
+  cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device);
+  memset(&h->hyper, 0, sizeof(h->hyper));
+  h->hyper.gamma = 0.9; h->hyper.lr = 0.001f; h->hyper.reg_param = 0.001f; h->hyper.momentum = 0.9f;
+  h->hyper.rmsprop_decay = 0.95f; h->hyper.optimizer = DQN_OPT_SGD; h->hyper.grad_scale = 1.f;   // main.py:30-39, 55
+  const int A = num_actions, MB = max_batch;
+  if (arch == DQN_ARCH_SIMPLE) {
+    const int IN = in_shape[0];
+    h->in_dim = IN;
+    h->state_bytes = (size_t)IN * (in_dtype == DQN_F64 ? 8 : 4);
+    add_tensor(h, {IN, HID}); add_tensor(h, {HID}); add_tensor(h, {HID, HID}); add_tensor(h, {HID});
+    add_tensor(h, {HID, A}); add_tensor(h, {A});
+    h->mo = MlpOff{(int)h->tensors[0].off, (int)h->tensors[1].off, (int)h->tensors[2].off, (int)h->tensors[3].off,
+                   (int)h->tensors[4].off, (int)h->tensors[5].off, (int)h->P};
+  } else {
+    h->state_bytes = (size_t)84 * 84 * 4 * (in_dtype == DQN_U8 ? 1 : 4);
+    const bool nat = arch == DQN_ARCH_NATURE;
+    add_tensor(h, {8, 8, 4, 32}); add_tensor(h, {32});
+    add_tensor(h, {4, 4, 32, 64}); add_tensor(h, {64});
+    add_tensor(h, {3, 3, 64, 64}); add_tensor(h, {64});
+    h->F = nat ? 512 : 256;
+    const int flat = nat ? 3136 : 256;
+    add_tensor(h, {flat, h->F}); add_tensor(h, {h->F});
+    add_tensor(h, {h->F, A}); add_tensor(h, {A});
+    auto setL = [&](int i, int K, int N, int rows, int in_e, int out_e) {
+      GemmLayer& l = h->L[i];
+      l.K = K; l.N = N; l.rows = rows; l.in_elems = in_e; l.out_elems = out_e; l.w_tensor = 2 * i;
+      const int base = (K / BM) * (N / BN);
+      int ms = (2 * h->num_sms + base - 1) / base;
+      l.maxsplit = ms < 1 ? 1 : (ms > 64 ? 64 : ms);
+    };
+    if (!nat) {
+      setL(0, C1::K, C1::COUT, C1::ROWS, 84 * 84 * 4, C1::OUT_PER_SAMPLE);
+      setL(1, C2::K, C2::COUT, C2::ROWS, C1::OUT_PER_SAMPLE, C2::OUT_PER_SAMPLE);
+      setL(2, C3::K, C3::COUT, C3::ROWS, C2::OUT_PER_SAMPLE, C3::OUT_PER_SAMPLE);
+      setL(3, F4::K, F4::COUT, F4::ROWS, C3::OUT_PER_SAMPLE, F4::OUT_PER_SAMPLE);
+    } else {
+      setL(0, N1::K, N1::COUT, N1::ROWS, 84 * 84 * 4, N1::OUT_PER_SAMPLE);
+      setL(1, N2::K, N2::COUT, N2::ROWS, N1::OUT_PER_SAMPLE, N2::OUT_PER_SAMPLE);
+      setL(2, N3::K, N3::COUT, N3::ROWS, N2::OUT_PER_SAMPLE, N3::OUT_PER_SAMPLE);
+      setL(3, NF::K, NF::COUT, NF::ROWS, N3::OUT_PER_SAMPLE, NF::OUT_PER_SAMPLE);
+    }
+  }
+  const size_t PB = (size_t)h->P * sizeof(float);
+  NET_ALLOC(h->online, PB); NET_ALLOC(h->target, PB); NET_ALLOC(h->grad, PB);
+  NET_ALLOC(h->slot0, PB); NET_ALLOC(h->slot1, PB);
+  NET_ALLOC(h->se, (size_t)MB * 4); NET_ALLOC(h->g, (size_t)MB * 4); NET_ALLOC(h->loss_tmp, 16);
+  NET_ALLOC(h->q_tmp, (size_t)MB * A * 4); NET_ALLOC(h->step, 16);
+  NET_ALLOC(h->st_states, (size_t)MB * h->state_bytes); NET_ALLOC(h->st_next, (size_t)MB * h->state_bytes);
+  NET_ALLOC(h->st_actions, (size_t)MB * 4); NET_ALLOC(h->st_rewards, (size_t)MB * 8); NET_ALLOC(h->st_term, (size_t)MB);
+  if (arch != DQN_ARCH_SIMPLE) {
+    for (int p = 0; p < 2; ++p)
+      for (int l = 0; l < 4; ++l) {
+        NET_ALLOC(h->act[p][l], (size_t)MB * h->L[l].out_elems * 4);
+        if (l < 3) NET_ALLOC(h->arg[p][l], (size_t)MB * h->L[l].out_elems);
+      }
+    for (int l = 0; l < 4; ++l) {
+      NET_ALLOC(h->dact[l], (size_t)MB * h->L[l].out_elems * 4);
+      NET_ALLOC(h->L[l].partial, (size_t)h->L[l].maxsplit * (h->L[l].K + 1) * h->L[l].N * 4);
+    }
+    NET_ALLOC(h->head_partial, (size_t)(h->F + 1) * A * 4);
+  }
+  *out = h;
+  return 0;
+}
+
+extern "C" int dqn_net_destroy(dqn_net_t h) {
+  if (!h) return 0;
+  DeviceGuard g(h->device);
+  cudaDeviceSynchronize();
+  for (void* p : h->allocs) cudaFree(p);
+  delete h;
+  return 0;
+}
+
+extern "C" int dqn_net_param_count(dqn_net_t h, int64_t* padded_floats, int32_t* num_tensors) {
+  DQN_REQUIRE(h, DQN_ERR_INVALID, "NULL handle");
+  if (padded_floats) *padded_floats = h->P;
+  if (num_tensors) *num_tensors = (int32_t)h->tensors.size();
+  return 0;
+}
+
+extern "C" int dqn_net_tensor_info(dqn_net_t h, int32_t i, int64_t* offset, int64_t* numel, int32_t* rank, int64_t shape[4]) {
+  DQN_REQUIRE(h && i >= 0 && i < (int)h->tensors.size(), DQN_ERR_INVALID, "tensor index out of range");
+  const Tensor& t = h->tensors[i];
+  if (offset) *offset = t.off;
+  if (numel) *numel = t.numel;
+  if (rank) *rank = t.rank;
+  if (shape) for (int k = 0; k < 4; ++k) shape[k] = k < t.rank ? t.shape[k] : 1;
+  return 0;
+}
+
+static float* buf_of(dqn_net_s* h, int which) {
+  switch (which) {
+    case DQN_BUF_ONLINE: return h->online;
+    case DQN_BUF_TARGET: return h->target;
+    case DQN_BUF_GRAD: return h->grad;
+    case DQN_BUF_SLOT0: return h->slot0;
+    case DQN_BUF_SLOT1: return h->slot1;
+  }
+  return nullptr;
+}
+
+extern "C" int dqn_net_buffer(dqn_net_t h, int32_t which, float** d_ptr, int64_t* floats) {
+  DQN_REQUIRE(h && buf_of(h, which), DQN_ERR_INVALID, "unknown buffer %d", which);
+  if (d_ptr) *d_ptr = buf_of(h, which);
+  if (floats) *floats = h->P;
+  return 0;
+}
+
+extern "C" int dqn_net_upload(dqn_net_t h, int32_t which, const float* host, int64_t floats) {
+  DQN_REQUIRE(h && host && buf_of(h, which), DQN_ERR_INVALID, "upload: bad argument");
+  DQN_REQUIRE(floats == h->P, DQN_ERR_INVALID, "upload: expected %lld floats, got %lld", (long long)h->P, (long long)floats);
+  DeviceGuard g(h->device);
+  DQN_CUDA(cudaDeviceSynchronize());
+  DQN_CUDA(cudaMemcpy(buf_of(h, which), host, (size_t)floats * 4, cudaMemcpyHostToDevice));
+  return 0;
+}
+
+extern "C" int dqn_net_download(dqn_net_t h, int32_t which, float* host, int64_t floats) {
+  DQN_REQUIRE(h && host && buf_of(h, which), DQN_ERR_INVALID, "download: bad argument");
+  DQN_REQUIRE(floats == h->P, DQN_ERR_INVALID, "download: expected %lld floats, got %lld", (long long)h->P, (long long)floats);
+  DeviceGuard g(h->device);
+  DQN_CUDA(cudaDeviceSynchronize());
+  DQN_CUDA(cudaMemcpy(host, buf_of(h, which), (size_t)floats * 4, cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+extern "C" int dqn_net_set_hyper(dqn_net_t h, const dqn_hyper_t* hyper, int32_t reset_slots) {
+  DQN_REQUIRE(h && hyper, DQN_ERR_INVALID, "set_hyper: NULL argument");
+  DQN_REQUIRE(hyper->optimizer >= DQN_OPT_SGD && hyper->optimizer <= DQN_OPT_FTRL, DQN_ERR_INVALID,
+              "Unsupported optimizer %d", hyper->optimizer);                  // network.py:179-180
+  DQN_REQUIRE(hyper->loss == DQN_LOSS_MSE || hyper->loss == DQN_LOSS_HUBER, DQN_ERR_INVALID, "unknown loss %d", hyper->loss);
+  h->hyper = *hyper;
+  if (h->hyper.grad_scale == 0.f) h->hyper.grad_scale = 1.f;
+  if (reset_slots) {
+    DeviceGuard g(h->device);
+    float v0 = 0.f;
+    if (hyper->optimizer == DQN_OPT_RMSPROP) v0 = 1.f;                         // TF: rms slot starts at 1
+    if (hyper->optimizer == DQN_OPT_ADAGRAD || hyper->optimizer == DQN_OPT_FTRL) v0 = 0.1f;   // initial_accumulator_value
+    DQN_CUDA(cudaDeviceSynchronize());
+    fill_kernel<<<64, 256>>>(h->slot0, h->P, v0);
+    fill_kernel<<<64, 256>>>(h->slot1, h->P, 0.f);
+    DQN_CUDA(cudaGetLastError());
+    DQN_CUDA(cudaMemset(h->step, 0, 16));
+    DQN_CUDA(cudaDeviceSynchronize());
+  }
+  return 0;
+}
+
+extern "C" int dqn_net_global_step(dqn_net_t h, int64_t* step, dqn_stream_t stream) {
+  DQN_REQUIRE(h && step, DQN_ERR_INVALID, "global_step: NULL argument");
+  DeviceGuard g(h->device);
+  long long v = 0;
+  DQN_CUDA(cudaMemcpyAsync(&v, h->step, sizeof(v), cudaMemcpyDeviceToHost, static_cast<cudaStream_t>(stream)));
+  DQN_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+  *step = v;
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------- launch helpers
+template <class G, typename TIn>
+static void launch_fwd(const FwdArgs& a, int npass, cudaStream_t st) {
+  dim3 grid((unsigned)((a.B * G::ROWS + BM - 1) / BM), G::COUT / BN, npass);
+  conv_fwd_kernel<G, TIn><<<grid, NT, 0, st>>>(a);
+}
+
+template <class G, typename TIn>
+static void launch_wgrad(dqn_net_s* h, int l, const void* x, int B, cudaStream_t st, int* nsplit_out) {
+  const GemmLayer& L = h->L[l];
+  const int R = B * G::ROWS;
+  const int tiles = (R + BK - 1) / BK;
+  int ns = L.maxsplit < tiles ? L.maxsplit : tiles;
+  const int per = (tiles + ns - 1) / ns;
+  ns = (tiles + per - 1) / per;
+  WgradArgs a{x, h->dact[l], h->act[0][l], l < 3 ? h->arg[0][l] : nullptr, L.partial, B, per * BK};
+  dim3 grid(G::K / BM, G::COUT / BN, ns);
+  conv_wgrad_kernel<G, TIn><<<grid, NT, 0, st>>>(a);
+  *nsplit_out = ns;
+}
+
+template <class G>
+static void launch_dgrad(dqn_net_s* h, int l, int B, cudaStream_t st) {
+  DgradArgs a{h->online + h->tensors[2 * l].off, h->dact[l], h->act[0][l], l < 3 ? h->arg[0][l] : nullptr, h->dact[l - 1], B};
+  dim3 grid((unsigned)((B * G::IH * G::IW + BM - 1) / BM), G::CIN / BN, 1);
+  conv_dgrad_kernel<G><<<grid, NT, 0, st>>>(a);
+}
+
+static FwdPass make_pass(dqn_net_s* h, const float* params, int pass, int l, const void* x) {
+  FwdPass p;
+  p.x = x;
+  p.w = params + h->tensors[2 * l].off;
+  p.bias = params + h->tensors[2 * l + 1].off;
+  p.out = h->act[pass][l];
+  p.arg = l < 3 ? h->arg[pass][l] : nullptr;
+  return p;
+}
+
+// Runs the trunk (conv1..3 + fc) for 1 or 2 passes. x[p]: input states of pass p, params[p]: flat params.
+static int run_trunk(dqn_net_s* h, int npass, const void* const x[2], const float* const params[2], const int pass_id[2],
+                     int B, cudaStream_t st) {
+  const bool nat = h->arch == DQN_ARCH_NATURE;
+  const bool u8 = h->in_dtype == DQN_U8;
+  for (int l = 0; l < 4; ++l) {
+    FwdArgs a;
+    a.B = B;
+    for (int p = 0; p < npass; ++p)
+      a.p[p] = make_pass(h, params[p], pass_id[p], l, l == 0 ? x[p] : (const void*)h->act[pass_id[p]][l - 1]);
+    if (npass == 1) a.p[1] = a.p[0];
+    switch (l) {
+      case 0:
+        if (nat) { if (u8) launch_fwd<N1, uint8_t>(a, npass, st); else launch_fwd<N1, float>(a, npass, st); }
+        else     { if (u8) launch_fwd<C1, uint8_t>(a, npass, st); else launch_fwd<C1, float>(a, npass, st); }
+        break;
+      case 1: if (nat) launch_fwd<N2, float>(a, npass, st); else launch_fwd<C2, float>(a, npass, st); break;
+      case 2: if (nat) launch_fwd<N3, float>(a, npass, st); else launch_fwd<C3, float>(a, npass, st); break;
+      case 3: if (nat) launch_fwd<NF, float>(a, npass, st); else launch_fwd<F4, float>(a, npass, st); break;
+    }
+  }
+  DQN_CUDA(cudaGetLastError());
+  return 0;
+}
+
+static void fill_segs(dqn_net_s* h, OptArgs* o, const int nsplit[4], bool from_flat_grad) {
+  memset(o, 0, sizeof(*o));
+  if (h->arch == DQN_ARCH_SIMPLE) {
+    o->nseg = 3;
+    for (int i = 0; i < 3; ++i) {
+      const Tensor& w = h->tensors[2 * i];
+      const Tensor& b = h->tensors[2 * i + 1];
+      o->seg[i] = Seg{(long long)w.off, (int)(w.numel + b.numel), (int)w.numel, h->grad + w.off, 1, 0};
+    }
+  } else {
+    o->nseg = 5;
+    for (int l = 0; l < 4; ++l) {
+      const Tensor& w = h->tensors[2 * l];
+      const GemmLayer& L = h->L[l];
+      Seg s{(long long)w.off, L.K * L.N + L.N, l == 3 ? L.K * L.N : 0, L.partial, nsplit[l], (long long)(L.K + 1) * L.N};
+      if (from_flat_grad) { s.partial = h->grad + w.off; s.nsplit = 1; s.stride = 0; }
+      o->seg[l] = s;
+    }
+    const Tensor& w5 = h->tensors[8];
+    Seg s{(long long)w5.off, (h->F + 1) * h->A, h->F * h->A, h->head_partial, 1, 0};
+    if (from_flat_grad) s.partial = h->grad + w5.off;
+    o->seg[4] = s;
+  }
+  o->w = h->online; o->s0 = h->slot0; o->s1 = h->slot1; o->step = h->step;
+  o->lr = h->hyper.lr; o->reg = h->hyper.reg_param; o->momentum = h->hyper.momentum; o->decay = h->hyper.rmsprop_decay;
+  o->gscale = h->hyper.grad_scale; o->opt = h->hyper.optimizer;
+}
+
+static int max_seg_len(const OptArgs& o) {
+  int m = 0;
+  for (int i = 0; i < o.nseg; ++i) m = o.seg[i].len > m ? o.seg[i].len : m;
+  return m;
+}
+
+extern "C" int dqn_net_forward(dqn_net_t h, int32_t which, const void* d_x, int32_t n, float* d_q, int32_t* d_argmax,
+                               dqn_stream_t stream) {
+  DQN_REQUIRE(h && d_x, DQN_ERR_INVALID, "forward: NULL argument");
+  DQN_REQUIRE(which == DQN_BUF_ONLINE || which == DQN_BUF_TARGET, DQN_ERR_INVALID, "forward: which must be online or target");
+  DQN_REQUIRE(n >= 1 && n <= h->MB, DQN_ERR_INVALID, "forward: n=%d outside [1, max_batch=%d]", n, h->MB);
+  DeviceGuard g(h->device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const float* params = which == DQN_BUF_ONLINE ? h->online : h->target;
+  if (h->arch == DQN_ARCH_SIMPLE) {
+    const int blocks = (n + 7) / 8;
+    const size_t smem = (size_t)h->mo.total * 4;
+    if (h->in_dtype == DQN_F64)
+      mlp_forward_kernel<double><<<blocks, 256, smem, st>>>(static_cast<const double*>(d_x), n, h->in_dim, h->A, h->mo, params, d_q, d_argmax);
+    else
+      mlp_forward_kernel<float><<<blocks, 256, smem, st>>>(static_cast<const float*>(d_x), n, h->in_dim, h->A, h->mo, params, d_q, d_argmax);
+  } else {
+    const int pass = which == DQN_BUF_ONLINE ? 0 : 1;
+    const void* xs[2] = {d_x, d_x};
+    const float* ps[2] = {params, params};
+    const int ids[2] = {pass, pass};
+    int rc = run_trunk(h, 1, xs, ps, ids, n, st);
+    if (rc) return rc;
+    head_forward_kernel<<<(n + 7) / 8, 256, 0, st>>>(h->act[pass][3], params + h->tensors[8].off, params + h->tensors[9].off,
+                                                     n, h->F, h->A, d_q, d_argmax);
+  }
+  DQN_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Forward of both nets + TD + full backward.  mode 0: fused optimizer; 1: materialise flat gradient.
+static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, const int32_t* d_actions,
+                    const double* d_rewards, const uint8_t* d_term, int k, float* d_loss, float* d_q, int mode,
+                    int include_reg, cudaStream_t st) {
+  DQN_REQUIRE(d_states && d_next && d_actions && d_rewards && d_term, DQN_ERR_INVALID, "train: NULL batch pointer");
+  DQN_REQUIRE(k >= 1 && k <= h->MB, DQN_ERR_INVALID, "train: minibatch %d outside [1, max_batch=%d]", k, h->MB);
+  int nsplit[4] = {1, 1, 1, 1};
+  OptArgs oa;
+  if (h->arch == DQN_ARCH_SIMPLE) {
+    const size_t smem = (size_t)(2 + MLP_WARPS) * h->mo.total * 4;
+    if (h->in_dtype == DQN_F64)
+      mlp_backward_kernel<double><<<1, MLP_WARPS * 32, smem, st>>>(
+          static_cast<const double*>(d_states), static_cast<const double*>(d_next), d_actions, d_rewards, d_term, k,
+          h->in_dim, h->A, h->mo, h->online, h->target, h->hyper.gamma, h->hyper.loss, h->grad, d_q, h->se, h->step);
+    else
+      mlp_backward_kernel<float><<<1, MLP_WARPS * 32, smem, st>>>(
+          static_cast<const float*>(d_states), static_cast<const float*>(d_next), d_actions, d_rewards, d_term, k,
+          h->in_dim, h->A, h->mo, h->online, h->target, h->hyper.gamma, h->hyper.loss, h->grad, d_q, h->se, h->step);
+    DQN_CUDA(cudaGetLastError());
+    fill_segs(h, &oa, nsplit, true);
+    if (d_loss) loss_kernel<<<1, 256, 0, st>>>(oa, h->se, k, d_loss);
+    if (mode == 1 && include_reg) {
+      // grad already holds the data term; add reg*w in place through the reduce kernel (partial == grad)
+      dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
+      reduce_grad_kernel<<<grid, 256, 0, st>>>(oa, h->grad, h->hyper.reg_param);
+    }
+  } else {
+    const bool nat = h->arch == DQN_ARCH_NATURE;
+    const bool u8 = h->in_dtype == DQN_U8;
+    const void* xs[2] = {d_states, d_next};
+    const float* ps[2] = {h->online, h->target};
+    const int ids[2] = {0, 1};
+    int rc = run_trunk(h, 2, xs, ps, ids, k, st);
+    if (rc) return rc;
+    const float* w5 = h->online + h->tensors[8].off;
+    td_head_kernel<<<(k + 7) / 8, 256, 0, st>>>(h->act[0][3], h->act[1][3], w5, h->online + h->tensors[9].off,
+                                                h->target + h->tensors[8].off, h->target + h->tensors[9].off, d_actions,
+                                                d_rewards, d_term, k, h->F, h->A, h->hyper.gamma, h->hyper.loss, d_q,
+                                                h->se, h->g, h->dact[3], h->step);
+    head_wgrad_kernel<<<((h->F + 1) * h->A + 255) / 256, 256, 0, st>>>(h->act[0][3], h->g, d_actions, k, h->F, h->A,
+                                                                       h->head_partial);
+    if (d_loss) {
+      fill_segs(h, &oa, nsplit, false);
+      loss_kernel<<<1, 256, 0, st>>>(oa, h->se, k, d_loss);
+    }
+    if (nat) {
+      launch_wgrad<NF, float>(h, 3, h->act[0][2], k, st, &nsplit[3]); launch_dgrad<NF>(h, 3, k, st);
+      launch_wgrad<N3, float>(h, 2, h->act[0][1], k, st, &nsplit[2]); launch_dgrad<N3>(h, 2, k, st);
+      launch_wgrad<N2, float>(h, 1, h->act[0][0], k, st, &nsplit[1]); launch_dgrad<N2>(h, 1, k, st);
+      if (u8) launch_wgrad<N1, uint8_t>(h, 0, d_states, k, st, &nsplit[0]);
+      else launch_wgrad<N1, float>(h, 0, d_states, k, st, &nsplit[0]);
+    } else {
+      launch_wgrad<F4, float>(h, 3, h->act[0][2], k, st, &nsplit[3]); launch_dgrad<F4>(h, 3, k, st);
+      launch_wgrad<C3, float>(h, 2, h->act[0][1], k, st, &nsplit[2]); launch_dgrad<C3>(h, 2, k, st);
+      launch_wgrad<C2, float>(h, 1, h->act[0][0], k, st, &nsplit[1]); launch_dgrad<C2>(h, 1, k, st);
+      if (u8) launch_wgrad<C1, uint8_t>(h, 0, d_states, k, st, &nsplit[0]);
+      else launch_wgrad<C1, float>(h, 0, d_states, k, st, &nsplit[0]);
+    }
+    DQN_CUDA(cudaGetLastError());
+    fill_segs(h, &oa, nsplit, false);
+    if (mode == 1) {
+      dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
+      reduce_grad_kernel<<<grid, 256, 0, st>>>(oa, h->grad, include_reg ? h->hyper.reg_param : 0.f);
+    }
+  }
+  if (mode == 0) {
+    dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
+    optimizer_kernel<<<grid, 256, 0, st>>>(oa);
+  }
+  DQN_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dqn_net_train_step(dqn_net_t h, const void* d_states, const void* d_next_states, const int32_t* d_actions,
+                                  const double* d_rewards, const uint8_t* d_terminals, int32_t k, float* d_loss,
+                                  float* d_q, dqn_stream_t stream) {
+  DQN_REQUIRE(h, DQN_ERR_INVALID, "train_step: NULL handle");
+  DeviceGuard g(h->device);
+  return run_step(h, d_states, d_next_states, d_actions, d_rewards, d_terminals, k, d_loss, d_q, 0, 0,
+                  static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int dqn_net_backward(dqn_net_t h, const void* d_states, const void* d_next_states, const int32_t* d_actions,
+                                const double* d_rewards, const uint8_t* d_terminals, int32_t k, float* d_loss, float* d_q,
+                                int32_t include_reg, dqn_stream_t stream) {
+  DQN_REQUIRE(h, DQN_ERR_INVALID, "backward: NULL handle");
+  DeviceGuard g(h->device);
+  return run_step(h, d_states, d_next_states, d_actions, d_rewards, d_terminals, k, d_loss, d_q, 1, include_reg,
+                  static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int dqn_net_apply(dqn_net_t h, dqn_stream_t stream) {
+  DQN_REQUIRE(h, DQN_ERR_INVALID, "apply: NULL handle");
+  DeviceGuard g(h->device);
+  const int nsplit[4] = {1, 1, 1, 1};
+  OptArgs oa;
+  fill_segs(h, &oa, nsplit, true);
+  dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
+  optimizer_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(oa);
+  DQN_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dqn_net_target_sync(dqn_net_t h, dqn_stream_t stream) {
+  DQN_REQUIRE(h, DQN_ERR_INVALID, "target_sync: NULL handle");
+  DeviceGuard g(h->device);
+  DQN_CUDA(cudaMemcpyAsync(h->target, h->online, (size_t)h->P * 4, cudaMemcpyDeviceToDevice, static_cast<cudaStream_t>(stream)));
+  return 0;
+}
+
+extern "C" int dqn_train_step(dqn_net_t net, dqn_replay_t replay, const int32_t* d_logical_idx, int32_t k, float* d_loss,
+                              dqn_stream_t stream) {
+  DQN_REQUIRE(net && replay && d_logical_idx, DQN_ERR_INVALID, "dqn_train_step: NULL argument");
+  DQN_REQUIRE(k >= 1 && k <= net->MB, DQN_ERR_INVALID, "dqn_train_step: minibatch %d outside [1, max_batch=%d]", k, net->MB);
+  DQN_REQUIRE(dqn_replay_device_(replay) == net->device, DQN_ERR_INVALID, "replay and net live on different devices");
+  RingView rv;
+  dqn_replay_view_(replay, &rv);
+  DQN_REQUIRE((size_t)rv.frame_bytes * rv.frames_per_state == net->state_bytes, DQN_ERR_INVALID,
+              "replay stacks are %d bytes but the net expects %zu", rv.frame_bytes * rv.frames_per_state, net->state_bytes);
+  int rc = dqn_replay_gather(replay, d_logical_idx, k, net->st_states, net->st_next, net->st_actions, net->st_rewards,
+                             net->st_term, stream);
+  if (rc) return rc;
+  DeviceGuard g(net->device);
+  return run_step(net, net->st_states, net->st_next, net->st_actions, net->st_rewards, net->st_term, k, d_loss, nullptr, 0,
+                  0, static_cast<cudaStream_t>(stream));
+}
