@@ -64,6 +64,11 @@ SIGNATURES = {
     "dqn_net_apply": (C.c_int, [c_vp, c_vp]),
     "dqn_net_target_sync": (C.c_int, [c_vp, c_vp]),
     "dqn_train_step": (C.c_int, [c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
+    "dqn_launch_count": (c_i64, []),
+    "dqn_net_set_timing": (C.c_int, [c_vp, c_i32]),
+    "dqn_net_timing_collect": (C.c_int, [c_vp]),
+    "dqn_net_timing_read": (C.c_int, [c_vp, c_i32, C.POINTER(c_f64), C.POINTER(c_i32)]),
+    "dqn_stage_name": (C.c_char_p, [c_i32]),
 }
 
 for _name, (_res, _args) in SIGNATURES.items():

@@ -41,6 +41,10 @@ struct DeviceGuard {
 
 static inline int64_t round_up(int64_t v, int64_t m) { return (v + m - 1) / m * m; }
 
+// Process-wide count of kernels this library has launched (bench.py's gpu_launches evidence).
+void count_launch();
+int64_t launch_count();
+
 // Ring view passed to kernels that read the replay ring (replay.cu, and the fused step).
 struct RingView {
   const uint8_t* frames;   // frame_capacity x pitch bytes
@@ -55,6 +59,15 @@ struct RingView {
 };
 
 }  // namespace dqn
+
+// Stage ids of the per-kernel timing hooks (dqn_net_set_timing); names in net.cu.
+enum {
+  DQN_STAGE_GATHER = 0, DQN_STAGE_FWD_CONV1, DQN_STAGE_FWD_CONV2, DQN_STAGE_FWD_CONV3, DQN_STAGE_FWD_FC,
+  DQN_STAGE_TD_HEAD, DQN_STAGE_HEAD_WGRAD, DQN_STAGE_LOSS, DQN_STAGE_WGRAD_FC, DQN_STAGE_DGRAD_FC,
+  DQN_STAGE_WGRAD_CONV3, DQN_STAGE_DGRAD_CONV3, DQN_STAGE_WGRAD_CONV2, DQN_STAGE_DGRAD_CONV2, DQN_STAGE_WGRAD_CONV1,
+  DQN_STAGE_REDUCE_GRAD, DQN_STAGE_OPTIMIZER, DQN_STAGE_MLP_BACKWARD, DQN_STAGE_MLP_FORWARD, DQN_STAGE_HEAD_FORWARD,
+  DQN_NUM_STAGES
+};
 
 // Internal cross-file hooks (not part of the public ABI).
 int dqn_replay_view_(dqn_replay_t h, dqn::RingView* out);

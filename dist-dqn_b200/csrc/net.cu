@@ -435,7 +435,32 @@ struct dqn_net_s {
   dqn_hyper_t hyper;
   MlpOff mo;
   std::vector<void*> allocs;
+  // optional per-kernel timing (bench.py's roofline figures): one event pair per stage
+  bool timing = false;
+  cudaEvent_t ev0[DQN_NUM_STAGES] = {}, ev1[DQN_NUM_STAGES] = {};
+  bool stage_used[DQN_NUM_STAGES] = {};
+  double stage_ms[DQN_NUM_STAGES] = {};
+  int stage_count[DQN_NUM_STAGES] = {};
 };
+
+namespace {
+// Brackets one kernel launch: counts it and, in timing mode, records its event pair.
+struct StageScope {
+  dqn_net_s* h; int id; cudaStream_t st;
+  StageScope(dqn_net_s* h_, int id_, cudaStream_t st_) : h(h_), id(id_), st(st_) {
+    dqn::count_launch();
+    if (h->timing) cudaEventRecord(h->ev0[id], st);
+  }
+  ~StageScope() {
+    if (h->timing) { cudaEventRecord(h->ev1[id], st); h->stage_used[id] = true; }
+  }
+};
+}  // namespace
+
+static const char* kStageNames[DQN_NUM_STAGES] = {
+    "gather", "fwd_conv1", "fwd_conv2", "fwd_conv3", "fwd_fc", "td_head", "head_wgrad", "loss",
+    "wgrad_fc", "dgrad_fc", "wgrad_conv3", "dgrad_conv3", "wgrad_conv2", "dgrad_conv2", "wgrad_conv1",
+    "reduce_grad", "optimizer", "mlp_backward", "mlp_forward", "head_forward"};
 
 static int dev_alloc(dqn_net_s* h, void** p, size_t bytes) {
   DQN_CUDA(cudaMalloc(p, bytes ? bytes : 16));
@@ -560,6 +585,10 @@ extern "C" int dqn_net_destroy(dqn_net_t h) {
   DeviceGuard g(h->device);
   cudaDeviceSynchronize();
   for (void* p : h->allocs) cudaFree(p);
+  for (int i = 0; i < DQN_NUM_STAGES; ++i) {
+    if (h->ev0[i]) cudaEventDestroy(h->ev0[i]);
+    if (h->ev1[i]) cudaEventDestroy(h->ev1[i]);
+  }
   delete h;
   return 0;
 }
@@ -666,7 +695,10 @@ static void launch_wgrad(dqn_net_s* h, int l, const void* x, int B, cudaStream_t
   ns = (tiles + per - 1) / per;
   WgradArgs a{x, h->dact[l], h->act[0][l], l < 3 ? h->arg[0][l] : nullptr, L.partial, B, per * BK};
   dim3 grid(G::K / BM, G::COUT / BN, ns);
-  conv_wgrad_kernel<G, TIn><<<grid, NT, 0, st>>>(a);
+  {
+    StageScope sc(h, DQN_STAGE_WGRAD_FC + 2 * (3 - l), st);
+    conv_wgrad_kernel<G, TIn><<<grid, NT, 0, st>>>(a);
+  }
   *nsplit_out = ns;
 }
 
@@ -674,6 +706,7 @@ template <class G>
 static void launch_dgrad(dqn_net_s* h, int l, int B, cudaStream_t st) {
   DgradArgs a{h->online + h->tensors[2 * l].off, h->dact[l], h->act[0][l], l < 3 ? h->arg[0][l] : nullptr, h->dact[l - 1], B};
   dim3 grid((unsigned)((B * G::IH * G::IW + BM - 1) / BM), G::CIN / BN, 1);
+  StageScope sc(h, DQN_STAGE_DGRAD_FC + 2 * (3 - l), st);
   conv_dgrad_kernel<G><<<grid, NT, 0, st>>>(a);
 }
 
@@ -698,6 +731,7 @@ static int run_trunk(dqn_net_s* h, int npass, const void* const x[2], const floa
     for (int p = 0; p < npass; ++p)
       a.p[p] = make_pass(h, params[p], pass_id[p], l, l == 0 ? x[p] : (const void*)h->act[pass_id[p]][l - 1]);
     if (npass == 1) a.p[1] = a.p[0];
+    StageScope sc(h, DQN_STAGE_FWD_CONV1 + l, st);
     switch (l) {
       case 0:
         if (nat) { if (u8) launch_fwd<N1, uint8_t>(a, npass, st); else launch_fwd<N1, float>(a, npass, st); }
@@ -757,6 +791,7 @@ extern "C" int dqn_net_forward(dqn_net_t h, int32_t which, const void* d_x, int3
   if (h->arch == DQN_ARCH_SIMPLE) {
     const int blocks = (n + 7) / 8;
     const size_t smem = (size_t)h->mo.total * 4;
+    StageScope sc(h, DQN_STAGE_MLP_FORWARD, st);
     if (h->in_dtype == DQN_F64)
       mlp_forward_kernel<double><<<blocks, 256, smem, st>>>(static_cast<const double*>(d_x), n, h->in_dim, h->A, h->mo, params, d_q, d_argmax);
     else
@@ -768,6 +803,7 @@ extern "C" int dqn_net_forward(dqn_net_t h, int32_t which, const void* d_x, int3
     const int ids[2] = {pass, pass};
     int rc = run_trunk(h, 1, xs, ps, ids, n, st);
     if (rc) return rc;
+    StageScope sc(h, DQN_STAGE_HEAD_FORWARD, st);
     head_forward_kernel<<<(n + 7) / 8, 256, 0, st>>>(h->act[pass][3], params + h->tensors[8].off, params + h->tensors[9].off,
                                                      n, h->F, h->A, d_q, d_argmax);
   }
@@ -785,6 +821,8 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
   OptArgs oa;
   if (h->arch == DQN_ARCH_SIMPLE) {
     const size_t smem = (size_t)(2 + MLP_WARPS) * h->mo.total * 4;
+    {
+    StageScope sc(h, DQN_STAGE_MLP_BACKWARD, st);
     if (h->in_dtype == DQN_F64)
       mlp_backward_kernel<double><<<1, MLP_WARPS * 32, smem, st>>>(
           static_cast<const double*>(d_states), static_cast<const double*>(d_next), d_actions, d_rewards, d_term, k,
@@ -793,12 +831,17 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       mlp_backward_kernel<float><<<1, MLP_WARPS * 32, smem, st>>>(
           static_cast<const float*>(d_states), static_cast<const float*>(d_next), d_actions, d_rewards, d_term, k,
           h->in_dim, h->A, h->mo, h->online, h->target, h->hyper.gamma, h->hyper.loss, h->grad, d_q, h->se, h->step);
+    }
     DQN_CUDA(cudaGetLastError());
     fill_segs(h, &oa, nsplit, true);
-    if (d_loss) loss_kernel<<<1, 256, 0, st>>>(oa, h->se, k, d_loss);
+    if (d_loss) {
+      StageScope sc(h, DQN_STAGE_LOSS, st);
+      loss_kernel<<<1, 256, 0, st>>>(oa, h->se, k, d_loss);
+    }
     if (mode == 1 && include_reg) {
       // grad already holds the data term; add reg*w in place through the reduce kernel (partial == grad)
       dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
+      StageScope sc(h, DQN_STAGE_REDUCE_GRAD, st);
       reduce_grad_kernel<<<grid, 256, 0, st>>>(oa, h->grad, h->hyper.reg_param);
     }
   } else {
@@ -810,14 +853,21 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
     int rc = run_trunk(h, 2, xs, ps, ids, k, st);
     if (rc) return rc;
     const float* w5 = h->online + h->tensors[8].off;
+    {
+    StageScope sc(h, DQN_STAGE_TD_HEAD, st);
     td_head_kernel<<<(k + 7) / 8, 256, 0, st>>>(h->act[0][3], h->act[1][3], w5, h->online + h->tensors[9].off,
                                                 h->target + h->tensors[8].off, h->target + h->tensors[9].off, d_actions,
                                                 d_rewards, d_term, k, h->F, h->A, h->hyper.gamma, h->hyper.loss, d_q,
                                                 h->se, h->g, h->dact[3], h->step);
+    }
+    {
+    StageScope sc(h, DQN_STAGE_HEAD_WGRAD, st);
     head_wgrad_kernel<<<((h->F + 1) * h->A + 255) / 256, 256, 0, st>>>(h->act[0][3], h->g, d_actions, k, h->F, h->A,
                                                                        h->head_partial);
+    }
     if (d_loss) {
       fill_segs(h, &oa, nsplit, false);
+      StageScope sc(h, DQN_STAGE_LOSS, st);
       loss_kernel<<<1, 256, 0, st>>>(oa, h->se, k, d_loss);
     }
     if (nat) {
@@ -837,11 +887,13 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
     fill_segs(h, &oa, nsplit, false);
     if (mode == 1) {
       dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
+      StageScope sc(h, DQN_STAGE_REDUCE_GRAD, st);
       reduce_grad_kernel<<<grid, 256, 0, st>>>(oa, h->grad, include_reg ? h->hyper.reg_param : 0.f);
     }
   }
   if (mode == 0) {
     dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
+    StageScope sc(h, DQN_STAGE_OPTIMIZER, st);
     optimizer_kernel<<<grid, 256, 0, st>>>(oa);
   }
   DQN_CUDA(cudaGetLastError());
@@ -873,7 +925,10 @@ extern "C" int dqn_net_apply(dqn_net_t h, dqn_stream_t stream) {
   OptArgs oa;
   fill_segs(h, &oa, nsplit, true);
   dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
-  optimizer_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(oa);
+  {
+    StageScope sc(h, DQN_STAGE_OPTIMIZER, static_cast<cudaStream_t>(stream));
+    optimizer_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(oa);
+  }
   DQN_CUDA(cudaGetLastError());
   return 0;
 }
@@ -894,10 +949,59 @@ extern "C" int dqn_train_step(dqn_net_t net, dqn_replay_t replay, const int32_t*
   dqn_replay_view_(replay, &rv);
   DQN_REQUIRE((size_t)rv.frame_bytes * rv.frames_per_state == net->state_bytes, DQN_ERR_INVALID,
               "replay stacks are %d bytes but the net expects %zu", rv.frame_bytes * rv.frames_per_state, net->state_bytes);
-  int rc = dqn_replay_gather(replay, d_logical_idx, k, net->st_states, net->st_next, net->st_actions, net->st_rewards,
-                             net->st_term, stream);
-  if (rc) return rc;
   DeviceGuard g(net->device);
+  int rc;
+  {
+    if (net->timing) cudaEventRecord(net->ev0[DQN_STAGE_GATHER], static_cast<cudaStream_t>(stream));
+    rc = dqn_replay_gather(replay, d_logical_idx, k, net->st_states, net->st_next, net->st_actions, net->st_rewards,
+                           net->st_term, stream);
+    if (net->timing) { cudaEventRecord(net->ev1[DQN_STAGE_GATHER], static_cast<cudaStream_t>(stream)); net->stage_used[DQN_STAGE_GATHER] = true; }
+  }
+  if (rc) return rc;
   return run_step(net, net->st_states, net->st_next, net->st_actions, net->st_rewards, net->st_term, k, d_loss, nullptr, 0,
                   0, static_cast<cudaStream_t>(stream));
+}
+
+// ---------------------------------------------------------------------------------------------- instrumentation
+extern "C" int64_t dqn_launch_count(void) { return dqn::launch_count(); }
+
+extern "C" const char* dqn_stage_name(int32_t stage) {
+  return (stage >= 0 && stage < DQN_NUM_STAGES) ? kStageNames[stage] : "";
+}
+
+extern "C" int dqn_net_set_timing(dqn_net_t h, int32_t enable) {
+  DQN_REQUIRE(h, DQN_ERR_INVALID, "set_timing: NULL handle");
+  DeviceGuard g(h->device);
+  if (enable && !h->ev0[0]) {
+    for (int i = 0; i < DQN_NUM_STAGES; ++i) {
+      DQN_CUDA(cudaEventCreate(&h->ev0[i]));
+      DQN_CUDA(cudaEventCreate(&h->ev1[i]));
+    }
+  }
+  h->timing = enable != 0;
+  for (int i = 0; i < DQN_NUM_STAGES; ++i) h->stage_used[i] = false;
+  if (enable == 2) for (int i = 0; i < DQN_NUM_STAGES; ++i) { h->stage_ms[i] = 0.0; h->stage_count[i] = 0; }
+  return 0;
+}
+
+extern "C" int dqn_net_timing_collect(dqn_net_t h) {
+  DQN_REQUIRE(h && h->timing, DQN_ERR_STATE, "timing_collect: timing is not enabled");
+  DeviceGuard g(h->device);
+  DQN_CUDA(cudaDeviceSynchronize());
+  for (int i = 0; i < DQN_NUM_STAGES; ++i) {
+    if (!h->stage_used[i]) continue;
+    float ms = 0.f;
+    DQN_CUDA(cudaEventElapsedTime(&ms, h->ev0[i], h->ev1[i]));
+    h->stage_ms[i] += ms;
+    h->stage_count[i] += 1;
+    h->stage_used[i] = false;
+  }
+  return 0;
+}
+
+extern "C" int dqn_net_timing_read(dqn_net_t h, int32_t stage, double* total_ms, int32_t* count) {
+  DQN_REQUIRE(h && stage >= 0 && stage < DQN_NUM_STAGES, DQN_ERR_INVALID, "timing_read: bad argument");
+  if (total_ms) *total_ms = h->stage_ms[stage];
+  if (count) *count = h->stage_count[stage];
+  return 0;
 }

@@ -13,6 +13,7 @@
 // A stack that "ends at position p" is frames p-(S-1) .. p (ring positions, slot = p % frame_capacity).
 #include "common.cuh"
 
+#include <atomic>
 #include <new>
 #include <vector>
 
@@ -27,6 +28,10 @@ int set_err(int code, const char* fmt, ...) {
   va_end(ap);
   return code;
 }
+
+static std::atomic<long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+int64_t launch_count() { return g_launches.load(std::memory_order_relaxed); }
 
 struct __align__(16) TransitionRec {
   int64_t state_pos;
@@ -478,6 +483,7 @@ extern "C" int dqn_replay_gather(dqn_replay_t h, const int32_t* d_logical_idx, i
           rv, d_logical_idx, k, elems, static_cast<uint64_t*>(d_states), static_cast<uint64_t*>(d_next_states),
           d_actions, d_rewards, d_terminals);
   }
+  count_launch();
   DQN_CUDA(cudaGetLastError());
   return 0;
 }

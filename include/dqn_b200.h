@@ -181,6 +181,21 @@ int dqn_net_target_sync(dqn_net_t h, dqn_stream_t stream);
 int dqn_train_step(dqn_net_t net, dqn_replay_t replay, const int32_t* d_logical_idx, int32_t k, float* d_loss,
                    dqn_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Instrumentation (no reference counterpart: the reference's only throughput signal is the
+ * Supervisor's global_step/sec log line, main.py:136-143).
+ * ------------------------------------------------------------------------------------------------ */
+/* Kernels launched by this library in this process so far (eager launches; a replayed CUDA graph
+ * launches the kernels that were counted when it was captured). */
+int64_t dqn_launch_count(void);
+/* enable=1: every kernel of the following eager steps is bracketed by a CUDA event pair on the
+ * caller's stream; enable=2 additionally zeroes the accumulated totals; 0 switches it off. */
+int dqn_net_set_timing(dqn_net_t h, int32_t enable);
+/* Synchronises the device and adds the last step's per-kernel durations to the totals. */
+int dqn_net_timing_collect(dqn_net_t h);
+int dqn_net_timing_read(dqn_net_t h, int32_t stage, double* total_ms, int32_t* count);
+const char* dqn_stage_name(int32_t stage); /* "" beyond the last stage */
+
 #ifdef __cplusplus
 }
 #endif
