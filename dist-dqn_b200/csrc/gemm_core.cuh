@@ -8,16 +8,27 @@
 //   wgrad   : i = (ky,kx,c),                        j = out channel, r = output pixel
 //   dgrad   : i = input pixel,                      j = in channel,  r = (ky,kx,n)
 // Layer geometry is a compile-time struct so every index decomposition is a multiply-shift.
+//
+// Small batches (B=32) leave the deeper layers with a handful of output tiles and a long serial
+// reduction, so forward and dgrad split the reduction over a THREAD-BLOCK CLUSTER: the S CTAs of a
+// cluster each take 1/S of the chunks of one output tile, park their partial accumulators in their
+// own shared memory, and rank 0 adds them up through distributed shared memory before the fused
+// epilogue (deterministic order, no global scratch, no atomics).
 #pragma once
 #include <cstdint>
+#include <cooperative_groups.h>
 #include <cuda_runtime.h>
 
 namespace dqn {
 
+namespace cg = cooperative_groups;
+
 constexpr int BM = 64;   // tile rows    (i)
 constexpr int BN = 32;   // tile columns (j)
-constexpr int BK = 16;   // reduction chunk (r)
+constexpr int BK = 32;   // reduction chunk (r)
 constexpr int NT = 128;  // threads per CTA; each owns a 4x4 micro-tile
+constexpr int MAX_CLUSTER = 8;
+static_assert(BK * BM >= BM * BN, "the A tile is reused as the cluster-reduction buffer");
 
 template <int IH_, int IW_, int CIN_, int KS_, int ST_, int PADH_, int PADW_, int OH_, int OW_, int COUT_, bool POOL_>
 struct Geo {
@@ -130,6 +141,33 @@ __device__ __forceinline__ void tile_fma(const float (*As)[BM], const float (*Bs
   }
 }
 
+// Split-K epilogue: ranks > 0 park their 4x4 accumulators in their shared memory, rank 0 adds them
+// (in rank order) through DSMEM.  Returns true on the CTA that owns the final sum.
+__device__ __forceinline__ bool cluster_reduce(float* red, float acc[4][4], int tid) {
+  cg::cluster_group cluster = cg::this_cluster();
+  const unsigned S = cluster.num_blocks();
+  if (S == 1) return true;
+  const unsigned rank = cluster.block_rank();
+  float4* mine = reinterpret_cast<float4*>(red) + tid * 4;
+  if (rank != 0) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) mine[i] = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+  }
+  cluster.sync();
+  if (rank == 0) {
+    for (unsigned r = 1; r < S; ++r) {
+      const float4* rem = reinterpret_cast<const float4*>(cluster.map_shared_rank(red, r)) + tid * 4;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float4 v = rem[i];
+        acc[i][0] += v.x; acc[i][1] += v.y; acc[i][2] += v.z; acc[i][3] += v.w;
+      }
+    }
+  }
+  cluster.sync();          // nobody leaves while its shared memory may still be read
+  return rank == 0;
+}
+
 // ------------------------------------------------------------------------------------------------
 // Forward: out = pool(relu(conv(x, w) + bias)); blockIdx.z selects the pass (online net on the
 // states / target net on the next states) so both forwards of a training step share one launch.
@@ -150,31 +188,42 @@ template <class G, typename TIn>
 __global__ void __launch_bounds__(NT) conv_fwd_kernel(FwdArgs a) {
   __shared__ __align__(16) float As[BK][BM];
   __shared__ __align__(16) float Bs[BK][BN];
-  const FwdPass P = a.p[blockIdx.z];
+  const unsigned S = cg::this_cluster().num_blocks();          // cluster = (1,1,S): split of the reduction
+  const unsigned rank = cg::this_cluster().block_rank();
+  const FwdPass P = a.p[blockIdx.z / S];
   const TIn* __restrict__ x = static_cast<const TIn*>(P.x);
   const int tid = threadIdx.x;
   const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
-  const int am = tid % BM, akq = tid / BM;          // this thread gathers quads akq and akq+2 of row am
+  const int am = tid % BM, akq = tid / BM;          // this thread gathers quads akq, akq+2, akq+4, akq+6 of row am
   const Row row = decode_row<G>(m0 + am, a.B);
-  const int bkk = tid >> 3, bnq = tid & 7;
+  const int bkk = tid >> 3, bnq = tid & 7;           // weight rows bkk and bkk+16
   const int ti = tid >> 3, tj = tid & 7;
+  constexpr int T = G::K / BK;
+  const int it0 = (int)(T * rank / S), it1 = (int)(T * (rank + 1) / S);
   float acc[4][4] = {};
-  float4 ra0, ra1, rb;
+  float4 ra[4], rb[2];
   auto fetch = [&](int k0) {
-    ra0 = load_x_quad<G, TIn>(x, row, (k0 >> 2) + akq);
-    ra1 = load_x_quad<G, TIn>(x, row, (k0 >> 2) + akq + 2);
-    rb = __ldg(reinterpret_cast<const float4*>(P.w + (size_t)(k0 + bkk) * G::COUT + n0 + bnq * 4));
+#pragma unroll
+    for (int q = 0; q < 4; ++q) ra[q] = load_x_quad<G, TIn>(x, row, (k0 >> 2) + akq + 2 * q);
+#pragma unroll
+    for (int q = 0; q < 2; ++q)
+      rb[q] = __ldg(reinterpret_cast<const float4*>(P.w + (size_t)(k0 + bkk + 16 * q) * G::COUT + n0 + bnq * 4));
   };
-  fetch(0);
-  for (int k0 = 0; k0 < G::K; k0 += BK) {
-    As[akq * 4 + 0][am] = ra0.x; As[akq * 4 + 1][am] = ra0.y; As[akq * 4 + 2][am] = ra0.z; As[akq * 4 + 3][am] = ra0.w;
-    As[akq * 4 + 8][am] = ra1.x; As[akq * 4 + 9][am] = ra1.y; As[akq * 4 + 10][am] = ra1.z; As[akq * 4 + 11][am] = ra1.w;
-    *reinterpret_cast<float4*>(&Bs[bkk][bnq * 4]) = rb;
+  if (it0 < it1) fetch(it0 * BK);
+  for (int it = it0; it < it1; ++it) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int kk = (akq + 2 * q) * 4;
+      As[kk + 0][am] = ra[q].x; As[kk + 1][am] = ra[q].y; As[kk + 2][am] = ra[q].z; As[kk + 3][am] = ra[q].w;
+    }
+#pragma unroll
+    for (int q = 0; q < 2; ++q) *reinterpret_cast<float4*>(&Bs[bkk + 16 * q][bnq * 4]) = rb[q];
     __syncthreads();
-    if (k0 + BK < G::K) fetch(k0 + BK);
+    if (it + 1 < it1) fetch((it + 1) * BK);
     tile_fma(As, Bs, ti, tj, acc);
     __syncthreads();
   }
+  if (!cluster_reduce(&As[0][0], acc, tid)) return;
   const int n = n0 + tj * 4;
   const float4 bias = __ldg(reinterpret_cast<const float4*>(P.bias + n));
   const float bv[4] = {bias.x, bias.y, bias.z, bias.w};
@@ -238,26 +287,32 @@ __global__ void __launch_bounds__(NT) conv_wgrad_kernel(WgradArgs a) {
   const int R = a.B * G::ROWS;
   const int r_begin = blockIdx.z * a.rows_per_split;
   const int r_end = min(R, r_begin + a.rows_per_split);
-  const int aiq = tid & 15, ar = tid >> 4;          // gathers k-quad aiq of rows ar and ar+8
+  const int aiq = tid & 15, ar = tid >> 4;          // gathers k-quad aiq of rows ar, ar+8, ar+16, ar+24
   const int kquad = (i0 >> 2) + aiq;
-  const int br = tid >> 3, bnq = tid & 7;           // dz quad bnq of row br
+  const int br = tid >> 3, bnq = tid & 7;           // dz quad bnq of rows br and br+16
   const int ti = tid >> 3, tj = tid & 7;
   float acc[4][4] = {};
   float bsum = 0.f;                                  // bias gradient, threads 0..31 of the first row-tile
-  float4 ra0, ra1, rb;
+  float4 ra[4], rb[2];
   auto fetch = [&](int r0) {
-    const Row q0 = decode_row<G>(r0 + ar, a.B);
-    const Row q1 = decode_row<G>(r0 + ar + 8, a.B);
-    ra0 = load_x_quad<G, TIn>(x, q0, kquad);
-    ra1 = load_x_quad<G, TIn>(x, q1, kquad);
-    const Row qb = decode_row<G>(r0 + br, a.B);
-    rb = qb.valid ? load_dz_quad<G>(a.dact, a.act, a.arg, qb.pidx, qb.win, n0 + bnq * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const Row qa = decode_row<G>(r0 + ar + 8 * q, a.B);
+      ra[q] = load_x_quad<G, TIn>(x, qa, kquad);
+    }
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      const Row qb = decode_row<G>(r0 + br + 16 * q, a.B);
+      rb[q] = qb.valid ? load_dz_quad<G>(a.dact, a.act, a.arg, qb.pidx, qb.win, n0 + bnq * 4)
+                       : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
   };
   if (r_begin < r_end) fetch(r_begin);
   for (int r0 = r_begin; r0 < r_end; r0 += BK) {
-    *reinterpret_cast<float4*>(&As[ar][aiq * 4]) = ra0;
-    *reinterpret_cast<float4*>(&As[ar + 8][aiq * 4]) = ra1;
-    *reinterpret_cast<float4*>(&Bs[br][bnq * 4]) = rb;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) *reinterpret_cast<float4*>(&As[ar + 8 * q][aiq * 4]) = ra[q];
+#pragma unroll
+    for (int q = 0; q < 2; ++q) *reinterpret_cast<float4*>(&Bs[br + 16 * q][bnq * 4]) = rb[q];
     __syncthreads();
     if (r0 + BK < r_end) fetch(r0 + BK);
     tile_fma(As, Bs, ti, tj, acc);
@@ -305,10 +360,14 @@ __global__ void __launch_bounds__(NT) conv_dgrad_kernel(DgradArgs a) {
   const int rem = m - b * (G::IH * G::IW);
   const int iy = rem / G::IW, ix = rem - iy * G::IW;
   const bool mvalid = m < M;
-  const int brq = tid & 3, bc = tid >> 2;           // w quad (4 consecutive n) brq for input channel c0+bc
+  const int brq = tid & 7, bc = tid >> 3;           // w quad (4 consecutive n) brq for input channels c0+bc, c0+bc+16
   const int ti = tid >> 3, tj = tid & 7;
+  const unsigned S = cg::this_cluster().num_blocks();
+  const unsigned rank = cg::this_cluster().block_rank();
+  constexpr int T = KD / BK;
+  const int it0 = (int)(T * rank / S), it1 = (int)(T * (rank + 1) / S);
   float acc[4][4] = {};
-  float4 ra0, ra1, rb;
+  float4 ra[4], rb[2];
   auto dz_at = [&](int kq) -> float4 {
     const int nq = kq % NQ;
     const int t = kq / NQ;
@@ -328,22 +387,32 @@ __global__ void __launch_bounds__(NT) conv_dgrad_kernel(DgradArgs a) {
     return load_dz_quad<G>(a.dact, a.act, a.arg, pidx, win, nq * 4);
   };
   auto fetch = [&](int k0) {
-    ra0 = dz_at((k0 >> 2) + akq);
-    ra1 = dz_at((k0 >> 2) + akq + 2);
-    const int kq = (k0 >> 2) + brq;                  // all 4 quads of a chunk share (ky,kx): COUT % BK == 0
+#pragma unroll
+    for (int q = 0; q < 4; ++q) ra[q] = dz_at((k0 >> 2) + akq + 2 * q);
+    const int kq = (k0 >> 2) + brq;                  // all 8 quads of a chunk share (ky,kx): COUT % BK == 0
     const int nq = kq % NQ, t = kq / NQ;
-    rb = __ldg(reinterpret_cast<const float4*>(a.w + ((size_t)t * G::CIN + c0 + bc) * G::COUT + nq * 4));
+#pragma unroll
+    for (int q = 0; q < 2; ++q)
+      rb[q] = __ldg(reinterpret_cast<const float4*>(a.w + ((size_t)t * G::CIN + c0 + bc + 16 * q) * G::COUT + nq * 4));
   };
-  fetch(0);
-  for (int k0 = 0; k0 < KD; k0 += BK) {
-    As[akq * 4 + 0][am] = ra0.x; As[akq * 4 + 1][am] = ra0.y; As[akq * 4 + 2][am] = ra0.z; As[akq * 4 + 3][am] = ra0.w;
-    As[akq * 4 + 8][am] = ra1.x; As[akq * 4 + 9][am] = ra1.y; As[akq * 4 + 10][am] = ra1.z; As[akq * 4 + 11][am] = ra1.w;
-    Bs[brq * 4 + 0][bc] = rb.x; Bs[brq * 4 + 1][bc] = rb.y; Bs[brq * 4 + 2][bc] = rb.z; Bs[brq * 4 + 3][bc] = rb.w;
+  if (it0 < it1) fetch(it0 * BK);
+  for (int it = it0; it < it1; ++it) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int kk = (akq + 2 * q) * 4;
+      As[kk + 0][am] = ra[q].x; As[kk + 1][am] = ra[q].y; As[kk + 2][am] = ra[q].z; As[kk + 3][am] = ra[q].w;
+    }
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      Bs[brq * 4 + 0][bc + 16 * q] = rb[q].x; Bs[brq * 4 + 1][bc + 16 * q] = rb[q].y;
+      Bs[brq * 4 + 2][bc + 16 * q] = rb[q].z; Bs[brq * 4 + 3][bc + 16 * q] = rb[q].w;
+    }
     __syncthreads();
-    if (k0 + BK < KD) fetch(k0 + BK);
+    if (it + 1 < it1) fetch((it + 1) * BK);
     tile_fma(As, Bs, ti, tj, acc);
     __syncthreads();
   }
+  if (!cluster_reduce(&As[0][0], acc, tid)) return;
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const int mm = m0 + ti * 4 + i;

@@ -542,8 +542,8 @@ extern "C" int dqn_net_create(dqn_net_t* out, int32_t arch, const int32_t* in_sh
       GemmLayer& l = h->L[i];
       l.K = K; l.N = N; l.rows = rows; l.in_elems = in_e; l.out_elems = out_e; l.w_tensor = 2 * i;
       const int base = (K / BM) * (N / BN);
-      int ms = (2 * h->num_sms + base - 1) / base;
-      l.maxsplit = ms < 1 ? 1 : (ms > 64 ? 64 : ms);
+      int ms = (3 * h->num_sms + base - 1) / base;
+      l.maxsplit = ms < 1 ? 1 : (ms > 96 ? 96 : ms);
     };
     if (!nat) {
       setL(0, C1::K, C1::COUT, C1::ROWS, 84 * 84 * 4, C1::OUT_PER_SAMPLE);
@@ -679,10 +679,38 @@ extern "C" int dqn_net_global_step(dqn_net_t h, int64_t* step, dqn_stream_t stre
 }
 
 // ---------------------------------------------------------------------------------------------- launch helpers
+// Cluster size (split of the reduction) for a launch with `tiles` output tiles and `chunks` reduction chunks:
+// enough CTAs to cover the SMs, at least 2 chunks per CTA, at most the portable cluster limit.
+static int pick_split(int tiles, int chunks, int num_sms) {
+  int s = (num_sms + tiles - 1) / tiles;
+  if (s > chunks / 2) s = chunks / 2;
+  if (s > MAX_CLUSTER) s = MAX_CLUSTER;
+  return s < 1 ? 1 : s;
+}
+
+template <typename Kern, typename Args>
+static void launch_clustered(Kern kern, dim3 grid, int split, const Args& args, cudaStream_t st) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = dim3(NT, 1, 1);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 1;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = (unsigned)split;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  cudaLaunchKernelEx(&cfg, kern, args);
+}
+
 template <class G, typename TIn>
-static void launch_fwd(const FwdArgs& a, int npass, cudaStream_t st) {
-  dim3 grid((unsigned)((a.B * G::ROWS + BM - 1) / BM), G::COUT / BN, npass);
-  conv_fwd_kernel<G, TIn><<<grid, NT, 0, st>>>(a);
+static void launch_fwd(const FwdArgs& a, int npass, int num_sms, cudaStream_t st) {
+  const int mt = (a.B * G::ROWS + BM - 1) / BM, nt = G::COUT / BN;
+  const int split = pick_split(mt * nt * npass, G::K / BK, num_sms);
+  dim3 grid((unsigned)mt, (unsigned)nt, (unsigned)(npass * split));
+  launch_clustered(conv_fwd_kernel<G, TIn>, grid, split, a, st);
 }
 
 template <class G, typename TIn>
@@ -705,9 +733,11 @@ static void launch_wgrad(dqn_net_s* h, int l, const void* x, int B, cudaStream_t
 template <class G>
 static void launch_dgrad(dqn_net_s* h, int l, int B, cudaStream_t st) {
   DgradArgs a{h->online + h->tensors[2 * l].off, h->dact[l], h->act[0][l], l < 3 ? h->arg[0][l] : nullptr, h->dact[l - 1], B};
-  dim3 grid((unsigned)((B * G::IH * G::IW + BM - 1) / BM), G::CIN / BN, 1);
+  const int mt = (B * G::IH * G::IW + BM - 1) / BM, nt = G::CIN / BN;
+  const int split = pick_split(mt * nt, G::KS * G::KS * G::COUT / BK, h->num_sms);
+  dim3 grid((unsigned)mt, (unsigned)nt, (unsigned)split);
   StageScope sc(h, DQN_STAGE_DGRAD_FC + 2 * (3 - l), st);
-  conv_dgrad_kernel<G><<<grid, NT, 0, st>>>(a);
+  launch_clustered(conv_dgrad_kernel<G>, grid, split, a, st);
 }
 
 static FwdPass make_pass(dqn_net_s* h, const float* params, int pass, int l, const void* x) {
@@ -734,12 +764,12 @@ static int run_trunk(dqn_net_s* h, int npass, const void* const x[2], const floa
     StageScope sc(h, DQN_STAGE_FWD_CONV1 + l, st);
     switch (l) {
       case 0:
-        if (nat) { if (u8) launch_fwd<N1, uint8_t>(a, npass, st); else launch_fwd<N1, float>(a, npass, st); }
-        else     { if (u8) launch_fwd<C1, uint8_t>(a, npass, st); else launch_fwd<C1, float>(a, npass, st); }
+        if (nat) { if (u8) launch_fwd<N1, uint8_t>(a, npass, h->num_sms, st); else launch_fwd<N1, float>(a, npass, h->num_sms, st); }
+        else     { if (u8) launch_fwd<C1, uint8_t>(a, npass, h->num_sms, st); else launch_fwd<C1, float>(a, npass, h->num_sms, st); }
         break;
-      case 1: if (nat) launch_fwd<N2, float>(a, npass, st); else launch_fwd<C2, float>(a, npass, st); break;
-      case 2: if (nat) launch_fwd<N3, float>(a, npass, st); else launch_fwd<C3, float>(a, npass, st); break;
-      case 3: if (nat) launch_fwd<NF, float>(a, npass, st); else launch_fwd<F4, float>(a, npass, st); break;
+      case 1: if (nat) launch_fwd<N2, float>(a, npass, h->num_sms, st); else launch_fwd<C2, float>(a, npass, h->num_sms, st); break;
+      case 2: if (nat) launch_fwd<N3, float>(a, npass, h->num_sms, st); else launch_fwd<C3, float>(a, npass, h->num_sms, st); break;
+      case 3: if (nat) launch_fwd<NF, float>(a, npass, h->num_sms, st); else launch_fwd<F4, float>(a, npass, h->num_sms, st); break;
     }
   }
   DQN_CUDA(cudaGetLastError());
