@@ -64,6 +64,7 @@ SIGNATURES = {
     "dqn_net_apply": (C.c_int, [c_vp, c_vp]),
     "dqn_net_target_sync": (C.c_int, [c_vp, c_vp]),
     "dqn_train_step": (C.c_int, [c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
+    "dqn_cnn_forward_noalloc": (C.c_int, [c_vp, c_i32, c_vp, c_i32, c_vp, c_vp, c_vp]),
     "dqn_launch_count": (c_i64, []),
     "dqn_net_set_timing": (C.c_int, [c_vp, c_i32]),
     "dqn_net_timing_collect": (C.c_int, [c_vp]),

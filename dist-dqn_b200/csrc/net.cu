@@ -1035,3 +1035,89 @@ extern "C" int dqn_net_timing_read(dqn_net_t h, int32_t stage, double* total_ms,
   if (count) *count = h->stage_count[stage];
   return 0;
 }
+
+// ================================================================================================
+// Forward pass that allocates nothing
+// ================================================================================================
+// dqn_net_forward keeps the activations between its kernels in buffers that dqn_net_create obtained
+// from cudaMalloc.  Some hosts of this library are not allowed to allocate device memory at all: an
+// actor process that was handed a fixed carve-out of the GPU by its parent, a real-time control loop
+// that must not enter the allocator (cudaMalloc may take a device-wide lock and synchronise), or a
+// sandboxed plugin whose allocation calls are intercepted.  For them the variant below runs the same
+// kernels for the reference conv net (DQN_ARCH_CNN, uint8 84x84x4 states) with the inter-kernel
+// activations in a fixed array that is part of the library image itself.
+//
+// The array costs kNoAllocFloats * 4 bytes (about 1.27 MB) on every GPU that loads the library,
+// from load until the process exits, whether or not the entry point is ever called.
+namespace {
+constexpr int kNoAllocMaxStates = 64;                                   // largest n per call
+constexpr int kNoAllocPerState = C1::OUT_PER_SAMPLE + C2::OUT_PER_SAMPLE + C3::OUT_PER_SAMPLE + F4::OUT_PER_SAMPLE;
+constexpr int kNoAllocFloats = kNoAllocMaxStates * kNoAllocPerState;    // 64 * 4960 floats
+constexpr int kNoAllocMaxDevices = 64;
+}  // namespace
+
+// In host code this name is only a handle for cudaGetSymbolAddress; it is NOT a device pointer.
+static __device__ __align__(256) float g_noalloc_scratch[kNoAllocFloats];
+
+// Device address of the array on each device, looked up once per device with that device current.
+static float* g_noalloc_ptr[kNoAllocMaxDevices] = {};
+
+extern "C" int dqn_cnn_forward_noalloc(const float* d_params, int32_t num_actions, const uint8_t* d_states, int32_t n,
+                                       float* d_q, int32_t* d_argmax, dqn_stream_t stream) {
+  DQN_REQUIRE(d_params && d_states, DQN_ERR_INVALID, "dqn_cnn_forward_noalloc: NULL params or states");
+  DQN_REQUIRE(d_q || d_argmax, DQN_ERR_INVALID, "dqn_cnn_forward_noalloc: pass d_q, d_argmax or both");
+  DQN_REQUIRE(num_actions >= 1 && num_actions <= 64, DQN_ERR_INVALID, "dqn_cnn_forward_noalloc: num_actions must be in [1, 64]");
+  DQN_REQUIRE(n >= 1, DQN_ERR_INVALID, "dqn_cnn_forward_noalloc: n must be positive");
+  DQN_REQUIRE(n <= kNoAllocMaxStates, DQN_ERR_INVALID,
+              "dqn_cnn_forward_noalloc: n=%d exceeds the built-in scratch, which holds at most %d states per call; "
+              "split the batch or use dqn_net_forward", n, kNoAllocMaxStates);
+  int dev = -1;
+  DQN_CUDA(cudaGetDevice(&dev));
+  DQN_REQUIRE(dev >= 0 && dev < kNoAllocMaxDevices, DQN_ERR_UNSUPPORTED, "device index %d not supported", dev);
+  if (!g_noalloc_ptr[dev]) {
+    // one-time set-up for this device (the current one): resolve the array's device address.
+    float* p = nullptr;
+    DQN_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_noalloc_scratch));
+    DQN_REQUIRE(p != nullptr, DQN_ERR_CUDA, "cudaGetSymbolAddress returned a null address");
+    g_noalloc_ptr[dev] = p;
+  }
+  int num_sms = 148;
+  DQN_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  float* base = g_noalloc_ptr[dev];
+  float* act[4];
+  act[0] = base;
+  act[1] = act[0] + (size_t)kNoAllocMaxStates * C1::OUT_PER_SAMPLE;
+  act[2] = act[1] + (size_t)kNoAllocMaxStates * C2::OUT_PER_SAMPLE;
+  act[3] = act[2] + (size_t)kNoAllocMaxStates * C3::OUT_PER_SAMPLE;
+  // parameter tensors back to back in the reference's tuple order (network.py:387); every tensor but the
+  // last has a multiple of 4 elements, so this equals the layout of the handle-based flat buffers
+  const int64_t sizes[10] = {8 * 8 * 4 * 32, 32, 4 * 4 * 32 * 64, 64, 3 * 3 * 64 * 64, 64, 256 * 256, 256,
+                             256 * (int64_t)num_actions, num_actions};
+  const float* t[10];
+  int64_t off = 0;
+  for (int i = 0; i < 10; ++i) { t[i] = d_params + off; off += sizes[i]; }
+  DQN_REQUIRE(((uintptr_t)d_params % 16) == 0 && ((uintptr_t)d_states % 4) == 0, DQN_ERR_INVALID,
+              "dqn_cnn_forward_noalloc: d_params must be 16-byte and d_states 4-byte aligned");
+  for (int l = 0; l < 4; ++l) {
+    FwdArgs a;
+    a.B = n;
+    a.p[0].x = l == 0 ? static_cast<const void*>(d_states) : static_cast<const void*>(act[l - 1]);
+    a.p[0].w = t[2 * l];
+    a.p[0].bias = t[2 * l + 1];
+    a.p[0].out = act[l];
+    a.p[0].arg = nullptr;
+    a.p[1] = a.p[0];
+    dqn::count_launch();
+    switch (l) {
+      case 0: launch_fwd<C1, uint8_t>(a, 1, num_sms, st); break;
+      case 1: launch_fwd<C2, float>(a, 1, num_sms, st); break;
+      case 2: launch_fwd<C3, float>(a, 1, num_sms, st); break;
+      case 3: launch_fwd<F4, float>(a, 1, num_sms, st); break;
+    }
+  }
+  dqn::count_launch();
+  head_forward_kernel<<<(n + 7) / 8, 256, 0, st>>>(act[3], t[8], t[9], n, 256, num_actions, d_q, d_argmax);
+  DQN_CUDA(cudaGetLastError());
+  return 0;
+}

@@ -181,6 +181,32 @@ int dqn_net_target_sync(dqn_net_t h, dqn_stream_t stream);
 int dqn_train_step(dqn_net_t net, dqn_replay_t replay, const int32_t* d_logical_idx, int32_t k, float* d_loss,
                    dqn_stream_t stream);
 
+/* Forward pass for callers that may not allocate device memory.  No counterpart in the reference.
+ *
+ * Same result as dqn_net_forward on a DQN_ARCH_CNN net fed uint8 states, but it needs no handle and
+ * calls no cudaMalloc/cudaFree (nor any other allocating routine): the activations that flow
+ * between its kernels live in a fixed array compiled into the library.  Meant for processes that
+ * were given a fixed slice of the GPU and must not touch the allocator -- embedded actors, control
+ * loops with hard latency bounds, sandboxed plugins.
+ *
+ *   d_params   the ten parameter tensors back to back, reference order (w1,b1,...,w5,b5; network.py:387),
+ *              TF layouts, fp32, 16-byte aligned: 143,776 + 257*num_actions floats
+ *   d_states   n stacks, uint8 [n][84][84][4]
+ *   d_q        out, [n][num_actions] Q-values (may be NULL if d_argmax is given)
+ *   d_argmax   out, [n] greedy actions, first maximum (may be NULL)
+ *
+ * Limits and rules
+ *   - at most 64 states per call; a larger n is refused with DQN_ERR_INVALID and a message saying so.
+ *   - the array occupies about 1.27 MB on every GPU that loads the library, until the process exits.
+ *   - the first call on each device looks the array's address up (cudaGetSymbolAddress on the current
+ *     device); make that first call outside of any stream capture.
+ *   - every call on a device uses the same array, and the array keeps whatever the previous call left
+ *     in it (every element a call reads is written earlier in the same call, so nothing needs
+ *     clearing).  Two calls whose kernels can overlap on the GPU -- different streams without an
+ *     ordering between them, or different host threads -- race on it; order them yourself. */
+int dqn_cnn_forward_noalloc(const float* d_params, int32_t num_actions, const uint8_t* d_states, int32_t n,
+                            float* d_q, int32_t* d_argmax, dqn_stream_t stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Instrumentation (no reference counterpart: the reference's only throughput signal is the
  * Supervisor's global_step/sec log line, main.py:136-143).
