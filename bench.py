@@ -213,7 +213,7 @@ def run_reference(args):
         "note": "reference-on-CPU (restated): TensorFlow is not installable here; oracle/torch_ref.py transcribes "
                 "dqn_agent.py:108-143 on torch-CPU fp32",
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def workload_config(arch, batch, n, capacity):
@@ -385,11 +385,13 @@ def run_b200(args):
     # ---- end to end through the public API (host frames in, loss out, every step)
     e2e = run_e2e(args, cfg, net, rm, world, dev, DQNAgent, FrameBuffer, dist if world > 1 else None)
 
+    # CUDA graphs that hold NCCL kernels must be gone before the communicator is torn down
+    graph = None
+    torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
+        _finish(world, dist)
         return
     cpu = None
     if world == 1 and not args.skip_cpu:
@@ -404,12 +406,26 @@ def run_b200(args):
         "config": workload_config(args.arch, batch, world, args.capacity),
         "samples_per_s": samples_per_s,
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches_per_step * steps),
-        "launches_per_step": int(launches_per_step), "cuda_graph": graph is not None,
+        "launches_per_step": int(launches_per_step), "cuda_graph": not args.no_graph,
         "roofline": roof, "cpu_baseline": cpu, "kernels_us": kernels, "gather": gather_info,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
+    _finish(world, dist)
+
+
+
+
+def _finish(world, dist):
+    """Leave without running interpreter teardown: destroying NCCL communicators and CUDA graphs in arbitrary
+    order at exit can hang."""
+    sys.stdout.flush()
+    sys.stderr.flush()
     if world > 1:
-        dist.destroy_process_group()
+        try:
+            dist.barrier()
+        except Exception:
+            pass
+    os._exit(0)
 
 
 def peaks():
@@ -534,6 +550,7 @@ def run_e2e(args, cfg, net, rm, world, dev, DQNAgent, FrameBuffer, dist):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dt = float(t.item())
     assert loss is not None and np.isfinite(loss)
+    agent._graphs.clear()
     h2d = cfg.update_freq * (FRAME + 32) + 16 + batch * 4
     return {"value": n / dt, "unit": "updates/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
             "steps": n, "ms_per_step": dt / n * 1e3,
@@ -541,7 +558,23 @@ def run_e2e(args, cfg, net, rm, world, dev, DQNAgent, FrameBuffer, dist):
                     "(random.sample on host, loss read back each step)" % cfg.update_freq}
 
 
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """The ONE JSON line goes to the real stdout; everything else any library prints (NCCL's version banner
+    goes to stdout) was redirected to stderr at start-up."""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 if __name__ == "__main__":
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     a = parse()
     if a.impl == "reference":
         run_reference(a)
