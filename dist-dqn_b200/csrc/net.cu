@@ -13,6 +13,7 @@
 //   mlp_*_kernel        the 4-20-20-A tanh net of SimpleNetwork as warp-level kernels (network.py:258-313)
 #include "common.cuh"
 #include "gemm_core.cuh"
+#include "umma_core.cuh"
 
 #include <cmath>
 #include <new>
@@ -64,7 +65,7 @@ td_head_kernel(const float* __restrict__ h_on, const float* __restrict__ h_tg, c
                const int32_t* __restrict__ actions, const double* __restrict__ rewards,
                const uint8_t* __restrict__ terminals, int B, int F, int A, double gamma, int loss_kind,
                float* __restrict__ qout, float* __restrict__ se, float* __restrict__ g, float* __restrict__ dh,
-               long long* __restrict__ step) {
+               __nv_bfloat16* __restrict__ dh_bf, long long* __restrict__ step) {
   const int lane = threadIdx.x & 31;
   const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (blockIdx.x == 0 && threadIdx.x == 0) *step += 1;      // global_step (network.py:83, 198-202)
@@ -88,7 +89,11 @@ td_head_kernel(const float* __restrict__ h_on, const float* __restrict__ h_tg, c
   float e, gg;
   td_terms(q_sel, maxq, rewards[b], terminals[b] != 0, gamma, B, loss_kind, &e, &gg);
   if (lane == 0) { se[b] = e; g[b] = gg; }
-  for (int j = lane; j < F; j += 32) dh[(size_t)b * F + j] = gg * w_on[j * A + act];
+  for (int j = lane; j < F; j += 32) {
+    const float d = gg * w_on[j * A + act];
+    dh[(size_t)b * F + j] = d;
+    if (dh_bf) dh_bf[(size_t)b * F + j] = __float2bfloat16_rn(d);
+  }
 }
 
 // out[(F+1)*A]: rows 0..F-1 = dL/dw5 (data term), row F = dL/db5.
@@ -263,6 +268,24 @@ __global__ void fill_kernel(float* p, long long n, float v) {
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) p[i] = v;
 }
 
+// bf16 copies of one layer's weights for the tensor-core path: wt[n][k] (forward: B operand, K-major) and
+// wd[c][(ky,kx,n)] (dgrad).  w is the fp32 master in TF layout [k=(ky,kx,c)][n].
+struct CvtLayer { const float* w; __nv_bfloat16* wt; __nv_bfloat16* wd; int K, N, CIN; };
+struct CvtArgs { CvtLayer l[4]; };
+__global__ void __launch_bounds__(256) weights_to_bf16_kernel(CvtArgs a) {
+  const CvtLayer L = a.l[blockIdx.y];
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= L.K * L.N) return;
+  const int k = i / L.N, n = i - k * L.N;
+  const __nv_bfloat16 v = __float2bfloat16_rn(L.w[i]);
+  L.wt[(size_t)n * L.K + k] = v;
+  if (L.wd) {
+    const int t = k / L.CIN, c = k - t * L.CIN;
+    const int taps = L.K / L.CIN;
+    L.wd[((size_t)c * taps + t) * L.N + n] = v;
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // SimpleNetwork (network.py:258-313): lane j of a warp owns hidden unit j of both hidden layers.
 // ------------------------------------------------------------------------------------------------
@@ -435,6 +458,13 @@ struct dqn_net_s {
   dqn_hyper_t hyper;
   MlpOff mo;
   std::vector<void*> allocs;
+  // bf16 tensor-core mode (precision == 1; DQN_ARCH_CNN only)
+  int precision = 0;
+  __nv_bfloat16* act_bf[2][4] = {};
+  __nv_bfloat16* dact_bf[4] = {};
+  __nv_bfloat16* wt_bf[2] = {};       // per parameter set: the 4 layers' transposed weights back to back
+  __nv_bfloat16* wd_bf = nullptr;     // online only: permuted weights for dgrad (layers 1..3)
+  size_t wt_off[4] = {}, wd_off[4] = {}, wt_total = 0, wd_total = 0;
   // optional per-kernel timing (bench.py's roofline figures): one event pair per stage
   bool timing = false;
   cudaEvent_t ev0[DQN_NUM_STAGES] = {}, ev1[DQN_NUM_STAGES] = {};
@@ -461,6 +491,8 @@ static const char* kStageNames[DQN_NUM_STAGES] = {
     "gather", "fwd_conv1", "fwd_conv2", "fwd_conv3", "fwd_fc", "td_head", "head_wgrad", "loss",
     "wgrad_fc", "dgrad_fc", "wgrad_conv3", "dgrad_conv3", "wgrad_conv2", "dgrad_conv2", "wgrad_conv1",
     "reduce_grad", "optimizer", "mlp_backward", "mlp_forward", "head_forward"};
+
+static int refresh_bf16_weights(dqn_net_s* h, int set, cudaStream_t st);
 
 static int dev_alloc(dqn_net_s* h, void** p, size_t bytes) {
   DQN_CUDA(cudaMalloc(p, bytes ? bytes : 16));
@@ -634,6 +666,11 @@ extern "C" int dqn_net_upload(dqn_net_t h, int32_t which, const float* host, int
   DeviceGuard g(h->device);
   DQN_CUDA(cudaDeviceSynchronize());
   DQN_CUDA(cudaMemcpy(buf_of(h, which), host, (size_t)floats * 4, cudaMemcpyHostToDevice));
+  if (h->precision == 1 && (which == DQN_BUF_ONLINE || which == DQN_BUF_TARGET)) {
+    int rc = refresh_bf16_weights(h, which == DQN_BUF_ONLINE ? 0 : 1, nullptr);
+    if (rc) return rc;
+    DQN_CUDA(cudaDeviceSynchronize());
+  }
   return 0;
 }
 
@@ -776,6 +813,99 @@ static int run_trunk(dqn_net_s* h, int npass, const void* const x[2], const floa
   return 0;
 }
 
+// ---------------------------------------------------------------------------------------------- bf16 tensor-core path
+template <typename Kern>
+static void set_smem(Kern kern, size_t bytes) {
+  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+}
+static size_t tc_smem(int ntile) { return 2 * (size_t)umma::A_STAGE_BYTES + 2 * (size_t)ntile * umma::TK * 2; }
+
+template <class G, typename TIn, int NTILE>
+static void launch_fwd_tc(const umma::FwdArgsT& a, int npass, cudaStream_t st) {
+  static bool once = (set_smem(umma::umma_fwd_kernel<G, TIn, NTILE>, tc_smem(NTILE)), true);
+  (void)once;
+  dim3 grid((unsigned)((a.B * G::ROWS + umma::TM - 1) / umma::TM), G::COUT / NTILE, npass);
+  umma::umma_fwd_kernel<G, TIn, NTILE><<<grid, umma::TT, tc_smem(NTILE), st>>>(a);
+}
+
+template <class G, typename TIn, int NTILE>
+static void launch_wgrad_tc(dqn_net_s* h, int l, const void* x, int B, cudaStream_t st, int* nsplit_out) {
+  static bool once = (set_smem(umma::umma_wgrad_kernel<G, TIn, NTILE>, tc_smem(NTILE)), true);
+  (void)once;
+  const GemmLayer& L = h->L[l];
+  const int R = B * G::ROWS;
+  const int tiles = (R + umma::TK - 1) / umma::TK;
+  int ns = L.maxsplit < tiles ? L.maxsplit : tiles;
+  const int per = (tiles + ns - 1) / ns;
+  ns = (tiles + per - 1) / per;
+  umma::WgradArgsT a{x, h->dact_bf[l], h->act_bf[0][l], l < 3 ? h->arg[0][l] : nullptr, L.partial, B, per * umma::TK};
+  dim3 grid((G::K + umma::TM - 1) / umma::TM, G::COUT / NTILE, ns);
+  {
+    StageScope sc(h, DQN_STAGE_WGRAD_FC + 2 * (3 - l), st);
+    umma::umma_wgrad_kernel<G, TIn, NTILE><<<grid, umma::TT, tc_smem(NTILE), st>>>(a);
+  }
+  *nsplit_out = ns;
+}
+
+template <class G, int NTILE>
+static void launch_dgrad_tc(dqn_net_s* h, int l, int B, cudaStream_t st) {
+  static bool once = (set_smem(umma::umma_dgrad_kernel<G, NTILE>, tc_smem(NTILE)), true);
+  (void)once;
+  umma::DgradArgsT a{h->wd_bf + h->wd_off[l], h->dact_bf[l], h->act_bf[0][l], l < 3 ? h->arg[0][l] : nullptr,
+                     h->dact_bf[l - 1], B};
+  dim3 grid((unsigned)((B * G::IH * G::IW + umma::TM - 1) / umma::TM), G::CIN / NTILE, 1);
+  StageScope sc(h, DQN_STAGE_DGRAD_FC + 2 * (3 - l), st);
+  umma::umma_dgrad_kernel<G, NTILE><<<grid, umma::TT, tc_smem(NTILE), st>>>(a);
+}
+
+// fp32 master weights of one parameter set -> bf16 operand copies
+static int refresh_bf16_weights(dqn_net_s* h, int set, cudaStream_t st) {
+  CvtArgs c;
+  const float* base = set == 0 ? h->online : h->target;
+  int maxn = 0;
+  for (int l = 0; l < 4; ++l) {
+    const GemmLayer& L = h->L[l];
+    c.l[l].w = base + h->tensors[2 * l].off;
+    c.l[l].wt = h->wt_bf[set] + h->wt_off[l];
+    c.l[l].wd = (set == 0 && l >= 1) ? h->wd_bf + h->wd_off[l] : nullptr;
+    c.l[l].K = L.K; c.l[l].N = L.N;
+    c.l[l].CIN = l == 0 ? 4 : (l == 1 ? 32 : (l == 2 ? 64 : L.K));
+    maxn = L.K * L.N > maxn ? L.K * L.N : maxn;
+  }
+  dim3 grid((maxn + 255) / 256, 4);
+  dqn::count_launch();
+  weights_to_bf16_kernel<<<grid, 256, 0, st>>>(c);
+  DQN_CUDA(cudaGetLastError());
+  return 0;
+}
+
+static int run_trunk_tc(dqn_net_s* h, int npass, const void* const x[2], const int pass_id[2], int B, cudaStream_t st) {
+  for (int l = 0; l < 4; ++l) {
+    umma::FwdArgsT a;
+    a.B = B;
+    for (int p = 0; p < npass; ++p) {
+      const int id = pass_id[p];
+      const float* params = id == 0 ? h->online : h->target;
+      a.p[p].x = l == 0 ? x[p] : (const void*)h->act_bf[id][l - 1];
+      a.p[p].wt = h->wt_bf[id] + h->wt_off[l];
+      a.p[p].bias = params + h->tensors[2 * l + 1].off;
+      a.p[p].out = h->act_bf[id][l];
+      a.p[p].out_f32 = l == 3 ? h->act[id][3] : nullptr;
+      a.p[p].arg = l < 3 ? h->arg[id][l] : nullptr;
+    }
+    if (npass == 1) a.p[1] = a.p[0];
+    StageScope sc(h, DQN_STAGE_FWD_CONV1 + l, st);
+    switch (l) {
+      case 0: launch_fwd_tc<C1, uint8_t, 32>(a, npass, st); break;
+      case 1: launch_fwd_tc<C2, __nv_bfloat16, 64>(a, npass, st); break;
+      case 2: launch_fwd_tc<C3, __nv_bfloat16, 64>(a, npass, st); break;
+      case 3: launch_fwd_tc<F4, __nv_bfloat16, 256>(a, npass, st); break;
+    }
+  }
+  DQN_CUDA(cudaGetLastError());
+  return 0;
+}
+
 static void fill_segs(dqn_net_s* h, OptArgs* o, const int nsplit[4], bool from_flat_grad) {
   memset(o, 0, sizeof(*o));
   if (h->arch == DQN_ARCH_SIMPLE) {
@@ -831,7 +961,7 @@ extern "C" int dqn_net_forward(dqn_net_t h, int32_t which, const void* d_x, int3
     const void* xs[2] = {d_x, d_x};
     const float* ps[2] = {params, params};
     const int ids[2] = {pass, pass};
-    int rc = run_trunk(h, 1, xs, ps, ids, n, st);
+    int rc = h->precision == 1 ? run_trunk_tc(h, 1, xs, ids, n, st) : run_trunk(h, 1, xs, ps, ids, n, st);
     if (rc) return rc;
     StageScope sc(h, DQN_STAGE_HEAD_FORWARD, st);
     head_forward_kernel<<<(n + 7) / 8, 256, 0, st>>>(h->act[pass][3], params + h->tensors[8].off, params + h->tensors[9].off,
@@ -880,7 +1010,7 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
     const void* xs[2] = {d_states, d_next};
     const float* ps[2] = {h->online, h->target};
     const int ids[2] = {0, 1};
-    int rc = run_trunk(h, 2, xs, ps, ids, k, st);
+    int rc = h->precision == 1 ? run_trunk_tc(h, 2, xs, ids, k, st) : run_trunk(h, 2, xs, ps, ids, k, st);
     if (rc) return rc;
     const float* w5 = h->online + h->tensors[8].off;
     {
@@ -888,7 +1018,8 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
     td_head_kernel<<<(k + 7) / 8, 256, 0, st>>>(h->act[0][3], h->act[1][3], w5, h->online + h->tensors[9].off,
                                                 h->target + h->tensors[8].off, h->target + h->tensors[9].off, d_actions,
                                                 d_rewards, d_term, k, h->F, h->A, h->hyper.gamma, h->hyper.loss, d_q,
-                                                h->se, h->g, h->dact[3], h->step);
+                                                h->se, h->g, h->dact[3], h->precision == 1 ? h->dact_bf[3] : nullptr,
+                                                h->step);
     }
     {
     StageScope sc(h, DQN_STAGE_HEAD_WGRAD, st);
@@ -900,7 +1031,12 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       StageScope sc(h, DQN_STAGE_LOSS, st);
       loss_kernel<<<1, 256, 0, st>>>(oa, h->se, k, d_loss);
     }
-    if (nat) {
+    if (h->precision == 1) {
+      launch_wgrad_tc<F4, __nv_bfloat16, 256>(h, 3, h->act_bf[0][2], k, st, &nsplit[3]); launch_dgrad_tc<F4, 256>(h, 3, k, st);
+      launch_wgrad_tc<C3, __nv_bfloat16, 64>(h, 2, h->act_bf[0][1], k, st, &nsplit[2]); launch_dgrad_tc<C3, 64>(h, 2, k, st);
+      launch_wgrad_tc<C2, __nv_bfloat16, 64>(h, 1, h->act_bf[0][0], k, st, &nsplit[1]); launch_dgrad_tc<C2, 32>(h, 1, k, st);
+      launch_wgrad_tc<C1, uint8_t, 32>(h, 0, d_states, k, st, &nsplit[0]);
+    } else if (nat) {
       launch_wgrad<NF, float>(h, 3, h->act[0][2], k, st, &nsplit[3]); launch_dgrad<NF>(h, 3, k, st);
       launch_wgrad<N3, float>(h, 2, h->act[0][1], k, st, &nsplit[2]); launch_dgrad<N3>(h, 2, k, st);
       launch_wgrad<N2, float>(h, 1, h->act[0][0], k, st, &nsplit[1]); launch_dgrad<N2>(h, 1, k, st);
@@ -923,8 +1059,11 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
   }
   if (mode == 0) {
     dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
-    StageScope sc(h, DQN_STAGE_OPTIMIZER, st);
-    optimizer_kernel<<<grid, 256, 0, st>>>(oa);
+    {
+      StageScope sc(h, DQN_STAGE_OPTIMIZER, st);
+      optimizer_kernel<<<grid, 256, 0, st>>>(oa);
+    }
+    if (h->precision == 1) { int rc = refresh_bf16_weights(h, 0, st); if (rc) return rc; }
   }
   DQN_CUDA(cudaGetLastError());
   return 0;
@@ -959,6 +1098,7 @@ extern "C" int dqn_net_apply(dqn_net_t h, dqn_stream_t stream) {
     StageScope sc(h, DQN_STAGE_OPTIMIZER, static_cast<cudaStream_t>(stream));
     optimizer_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(oa);
   }
+  if (h->precision == 1) { int rc = refresh_bf16_weights(h, 0, static_cast<cudaStream_t>(stream)); if (rc) return rc; }
   DQN_CUDA(cudaGetLastError());
   return 0;
 }
@@ -967,6 +1107,8 @@ extern "C" int dqn_net_target_sync(dqn_net_t h, dqn_stream_t stream) {
   DQN_REQUIRE(h, DQN_ERR_INVALID, "target_sync: NULL handle");
   DeviceGuard g(h->device);
   DQN_CUDA(cudaMemcpyAsync(h->target, h->online, (size_t)h->P * 4, cudaMemcpyDeviceToDevice, static_cast<cudaStream_t>(stream)));
+  if (h->precision == 1)
+    DQN_CUDA(cudaMemcpyAsync(h->wt_bf[1], h->wt_bf[0], h->wt_total * 2, cudaMemcpyDeviceToDevice, static_cast<cudaStream_t>(stream)));
   return 0;
 }
 
@@ -990,6 +1132,37 @@ extern "C" int dqn_train_step(dqn_net_t net, dqn_replay_t replay, const int32_t*
   if (rc) return rc;
   return run_step(net, net->st_states, net->st_next, net->st_actions, net->st_rewards, net->st_term, k, d_loss, nullptr, 0,
                   0, static_cast<cudaStream_t>(stream));
+}
+
+// ---------------------------------------------------------------------------------------------- precision mode
+extern "C" int dqn_net_set_precision(dqn_net_t h, int32_t precision) {
+  DQN_REQUIRE(h, DQN_ERR_INVALID, "set_precision: NULL handle");
+  DQN_REQUIRE(precision == 0 || precision == 1, DQN_ERR_INVALID, "precision must be 0 (fp32) or 1 (bf16 tensor cores)");
+  if (precision == 1) {
+    DQN_REQUIRE(h->arch == DQN_ARCH_CNN && h->in_dtype == DQN_U8, DQN_ERR_UNSUPPORTED,
+                "the bf16 tensor-core path covers the reference conv net (DQN_ARCH_CNN) fed uint8 frames");
+    DeviceGuard g(h->device);
+    if (!h->wt_bf[0]) {
+      size_t wt = 0, wd = 0;
+      for (int l = 0; l < 4; ++l) {
+        h->wt_off[l] = wt; wt += (size_t)h->L[l].K * h->L[l].N;
+        h->wd_off[l] = wd; if (l >= 1) wd += (size_t)h->L[l].K * h->L[l].N;
+      }
+      h->wt_total = wt; h->wd_total = wd;
+      NET_ALLOC(h->wt_bf[0], wt * 2); NET_ALLOC(h->wt_bf[1], wt * 2); NET_ALLOC(h->wd_bf, wd * 2);
+      for (int p = 0; p < 2; ++p)
+        for (int l = 0; l < 4; ++l) NET_ALLOC(h->act_bf[p][l], (size_t)h->MB * h->L[l].out_elems * 2);
+      for (int l = 0; l < 4; ++l) NET_ALLOC(h->dact_bf[l], (size_t)h->MB * h->L[l].out_elems * 2);
+    }
+    h->precision = 1;
+    int rc = refresh_bf16_weights(h, 0, nullptr);
+    if (!rc) rc = refresh_bf16_weights(h, 1, nullptr);
+    if (rc) return rc;
+    DQN_CUDA(cudaDeviceSynchronize());
+  } else {
+    h->precision = 0;
+  }
+  return 0;
 }
 
 // ---------------------------------------------------------------------------------------------- instrumentation

@@ -98,6 +98,11 @@ class Network(object):
             shp = (_c.c_i64 * 4)()
             _c.check(_c.lib.dqn_net_tensor_info(h, i, _c.C.byref(off), _c.C.byref(numel), _c.C.byref(rank), shp))
             self.tensors.append((off.value, numel.value, tuple(shp[:rank.value])))
+        self.precision = getattr(config, 'precision', None) or 'fp32'
+        if self.precision not in ('fp32', 'bf16'):
+            raise RuntimeError('Unsupported precision {}'.format(self.precision))
+        if self.precision == 'bf16':
+            _c.check(_c.lib.dqn_net_set_precision(h, 1), type(self).__name__)
         self.set_hyper(config, reset_slots=True)
         seed = getattr(config, 'seed', None)
         self.set_params(self._initial_params(np.random.default_rng(seed)))

@@ -179,13 +179,30 @@ def pool_bwd(dp, arg, L):
     return dap[:, :L["oh"], :L["ow"], :]
 
 
+# ----------------------------------------------------------------------------- bf16 emulation
+def bf16_round(a):
+    """Round to the nearest bfloat16 (ties to even), returned in the input's float type.  Used to restate
+    where the bf16 tensor-core mode of the CUDA path rounds: GEMM operands (weights, stored activations,
+    propagated gradients); accumulation, bias, ReLU, pooling and the head stay in full precision."""
+    a = np.asarray(a)
+    f = a.astype(np.float32)
+    u = f.view(np.uint32).astype(np.uint64)
+    u = (u + 0x7FFF + ((u >> 16) & 1)) & 0xFFFF0000
+    return u.astype(np.uint32).view(np.float32).astype(a.dtype if a.dtype.kind == "f" else np.float64)
+
+
+def _ident(a):
+    return a
+
+
 # ----------------------------------------------------------------------------- forward / backward
-def forward(arch, params, x, input_shape=None, keep=False):
+def forward(arch, params, x, input_shape=None, keep=False, bf16=False):
     """Q-values [B, A] (network.py:303-308 / 389-404).  x: [B]+input_shape, any dtype (cast, no /255)."""
     spec = ARCHS[arch]
     dt = params[0].dtype
     x = np.asarray(x).astype(dt)
     cache = {}
+    Q = bf16_round if bf16 else _ident
     if spec["kind"] == "mlp":
         w1, b1, w2, b2, w3, b3 = params
         a1 = np.tanh(x @ w1 + b1)
@@ -198,31 +215,35 @@ def forward(arch, params, x, input_shape=None, keep=False):
     a = x
     per = []
     for i, L in enumerate(layers):
-        w, b = params[2 * i], params[2 * i + 1]
+        w, b = Q(params[2 * i]), params[2 * i + 1]
         z, cols = conv_fwd(a, w, L)
         r = np.maximum(z + b, 0.0)
         if L["pool"]:
             p, arg = pool_fwd(r, L)
         else:
             p, arg = r, None
+        p = Q(p)                                  # stored activation (bf16 mode rounds here)
         if keep:
-            per.append(dict(cols=cols, r=r, arg=arg, L=L))
+            per.append(dict(cols=cols, gate=(p > 0), arg=arg, L=L, wq=w))
         a = p
     n = len(layers)
     w4, b4, w5, b5 = params[2 * n:2 * n + 4]
     a3 = a.reshape(a.shape[0], flat)             # NHWC flatten: (y*W+x)*C+c  (network.py:401)
-    a4 = np.maximum(a3 @ w4 + b4, 0.0)
+    w4q = Q(w4)
+    a4 = np.maximum(a3 @ w4q + b4, 0.0)          # the head reads this in full precision in both modes
     q = a4 @ w5 + b5
     if keep:
-        cache = dict(per=per, a3=a3, a4=a4, pooled_shape=a.shape)
+        cache = dict(per=per, a3=a3, a4=a4, a4_gate=(Q(a4) > 0), w4q=w4q, pooled_shape=a.shape)
         return q, cache
     return q
 
 
-def loss_and_grads(arch, params, x, y, actions, reg_param, input_shape=None):
-    """loss (network.py:149-152) and dL/dparam in tuple order.  actions: int [B]."""
+def loss_and_grads(arch, params, x, y, actions, reg_param, input_shape=None, bf16=False):
+    """loss (network.py:149-152) and dL/dparam in tuple order.  actions: int [B].
+    bf16=True restates the rounding points of the CUDA path's bf16 tensor-core mode (see bf16_round)."""
     spec = ARCHS[arch]
-    q, c = forward(arch, params, x, input_shape, keep=True)
+    Q = bf16_round if bf16 else _ident
+    q, c = forward(arch, params, x, input_shape, keep=True, bf16=bf16)
     B, A = q.shape
     actions = np.asarray(actions, np.int64)
     y = np.asarray(y).astype(q.dtype)
@@ -249,19 +270,19 @@ def loss_and_grads(arch, params, x, y, actions, reg_param, input_shape=None):
         w4, b4, w5, b5 = params[2 * n:2 * n + 4]
         grads[2 * n + 2] = c["a4"].T @ dq
         grads[2 * n + 3] = dq.sum(0)
-        d4 = (dq @ w5.T) * (c["a4"] > 0)
+        d4 = Q(dq @ w5.T) * c["a4_gate"]
         grads[2 * n] = c["a3"].T @ d4
         grads[2 * n + 1] = d4.sum(0)
-        da = (d4 @ w4.T).reshape(c["pooled_shape"])
+        da = Q(d4 @ c["w4q"].T).reshape(c["pooled_shape"])
         for i in range(n - 1, -1, -1):
             P = c["per"][i]
             L = P["L"]
-            dr = pool_bwd(da, P["arg"], L) if L["pool"] else da
-            dz = dr * (P["r"] > 0)
-            dw, dx = conv_bwd(dz, P["cols"], params[2 * i], L, need_dx=(i > 0))
+            # gate on the POOLED activation: identical to relu'(r) at the arg-max position
+            dz = pool_bwd(da * P["gate"], P["arg"], L) if L["pool"] else da * P["gate"]
+            dw, dx = conv_bwd(dz, P["cols"], P["wq"], L, need_dx=(i > 0))
             grads[2 * i] = dw
             grads[2 * i + 1] = dz.sum((0, 1, 2))
-            da = dx
+            da = Q(dx) if dx is not None else None
     for i in reg_indices(arch):
         grads[i] = grads[i] + reg_param * params[i]
     return loss, q, grads
@@ -351,7 +372,8 @@ class RefTrainer:
 
     def __init__(self, arch, input_shape, num_actions, optimizer="rmsprop", lr=0.00025, reg_param=0.001,
                  gamma=0.99, momentum=0.9, rmsprop_decay=0.95, target_update_freq=10000, seed=0,
-                 dtype=np.float64, params=None):
+                 dtype=np.float64, params=None, bf16=False):
+        self.bf16 = bf16        # restate the rounding points of the CUDA bf16 tensor-core mode
         self.arch, self.input_shape, self.num_actions = arch, tuple(input_shape), num_actions
         self.opt, self.lr, self.reg, self.gamma = optimizer, lr, reg_param, gamma
         self.momentum, self.decay, self.tfreq = momentum, rmsprop_decay, target_update_freq
@@ -362,12 +384,12 @@ class RefTrainer:
         self.training_steps = 0
 
     def q_values(self, x, use_target=False):
-        return forward(self.arch, self.target if use_target else self.params, x, self.input_shape)
+        return forward(self.arch, self.target if use_target else self.params, x, self.input_shape, bf16=self.bf16)
 
     def train(self, states, actions, rewards, next_states, terminals):
         y = td_targets(rewards, terminals, self.q_values(next_states, True), self.gamma)
         loss, q, grads = loss_and_grads(self.arch, self.params, states, y.astype(np.float64), actions,
-                                        self.reg, self.input_shape)
+                                        self.reg, self.input_shape, bf16=self.bf16)
         self.training_steps += 1
         apply_optimizer(self.opt, self.params, grads, self.slots, self.training_steps, self.lr,
                         self.momentum, self.decay)
