@@ -16,6 +16,7 @@
 #include "umma_core.cuh"
 
 #include <cmath>
+#include <cstdlib>
 #include <new>
 #include <vector>
 
@@ -92,7 +93,7 @@ td_head_kernel(const float* __restrict__ h_on, const float* __restrict__ h_tg, c
   for (int j = lane; j < F; j += 32) {
     const float d = gg * w_on[j * A + act];
     dh[(size_t)b * F + j] = d;
-    if (dh_bf) dh_bf[(size_t)b * F + j] = __float2bfloat16_rn(d);
+    if (dh_bf) dh_bf[(size_t)b * F + j] = __float2bfloat16_rn(x[j] > 0.f ? d : 0.f);   // ReLU-gated for the tensor-core path
   }
 }
 
@@ -818,19 +819,20 @@ template <typename Kern>
 static void set_smem(Kern kern, size_t bytes) {
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
 }
-static size_t tc_smem(int ntile) { return 2 * (size_t)umma::A_STAGE_BYTES + 2 * (size_t)ntile * umma::TK * 2; }
 
 template <class G, typename TIn, int NTILE>
 static void launch_fwd_tc(const umma::FwdArgsT& a, int npass, cudaStream_t st) {
-  static bool once = (set_smem(umma::umma_fwd_kernel<G, TIn, NTILE>, tc_smem(NTILE)), true);
+  constexpr size_t smem = umma::fwd_smem_bytes<TIn, NTILE>();
+  static bool once = (set_smem(umma::umma_fwd_kernel<G, TIn, NTILE>, smem), true);
   (void)once;
   dim3 grid((unsigned)((a.B * G::ROWS + umma::TM - 1) / umma::TM), G::COUT / NTILE, npass);
-  umma::umma_fwd_kernel<G, TIn, NTILE><<<grid, umma::TT, tc_smem(NTILE), st>>>(a);
+  umma::umma_fwd_kernel<G, TIn, NTILE><<<grid, umma::TT, smem, st>>>(a);
 }
 
 template <class G, typename TIn, int NTILE>
 static void launch_wgrad_tc(dqn_net_s* h, int l, const void* x, int B, cudaStream_t st, int* nsplit_out) {
-  static bool once = (set_smem(umma::umma_wgrad_kernel<G, TIn, NTILE>, tc_smem(NTILE)), true);
+  constexpr size_t smem = umma::wgrad_smem_bytes<G, TIn, NTILE>();
+  static bool once = (set_smem(umma::umma_wgrad_kernel<G, TIn, NTILE>, smem), true);
   (void)once;
   const GemmLayer& L = h->L[l];
   const int R = B * G::ROWS;
@@ -838,24 +840,25 @@ static void launch_wgrad_tc(dqn_net_s* h, int l, const void* x, int B, cudaStrea
   int ns = L.maxsplit < tiles ? L.maxsplit : tiles;
   const int per = (tiles + ns - 1) / ns;
   ns = (tiles + per - 1) / per;
-  umma::WgradArgsT a{x, h->dact_bf[l], h->act_bf[0][l], l < 3 ? h->arg[0][l] : nullptr, L.partial, B, per * umma::TK};
+  umma::WgradArgsT a{x, h->dact_bf[l], l < 3 ? h->arg[0][l] : nullptr, L.partial, B, per * umma::TK};
   dim3 grid((G::K + umma::TM - 1) / umma::TM, G::COUT / NTILE, ns);
   {
     StageScope sc(h, DQN_STAGE_WGRAD_FC + 2 * (3 - l), st);
-    umma::umma_wgrad_kernel<G, TIn, NTILE><<<grid, umma::TT, tc_smem(NTILE), st>>>(a);
+    umma::umma_wgrad_kernel<G, TIn, NTILE><<<grid, umma::TT, smem, st>>>(a);
   }
   *nsplit_out = ns;
 }
 
 template <class G, int NTILE>
 static void launch_dgrad_tc(dqn_net_s* h, int l, int B, cudaStream_t st) {
-  static bool once = (set_smem(umma::umma_dgrad_kernel<G, NTILE>, tc_smem(NTILE)), true);
+  constexpr size_t smem = umma::dgrad_smem_bytes<G, NTILE>();
+  static bool once = (set_smem(umma::umma_dgrad_kernel<G, NTILE>, smem), true);
   (void)once;
-  umma::DgradArgsT a{h->wd_bf + h->wd_off[l], h->dact_bf[l], h->act_bf[0][l], l < 3 ? h->arg[0][l] : nullptr,
+  umma::DgradArgsT a{h->wd_bf + h->wd_off[l], h->dact_bf[l], l < 3 ? h->arg[0][l] : nullptr, h->act_bf[0][l - 1],
                      h->dact_bf[l - 1], B};
   dim3 grid((unsigned)((B * G::IH * G::IW + umma::TM - 1) / umma::TM), G::CIN / NTILE, 1);
   StageScope sc(h, DQN_STAGE_DGRAD_FC + 2 * (3 - l), st);
-  umma::umma_dgrad_kernel<G, NTILE><<<grid, umma::TT, tc_smem(NTILE), st>>>(a);
+  umma::umma_dgrad_kernel<G, NTILE><<<grid, umma::TT, smem, st>>>(a);
 }
 
 // fp32 master weights of one parameter set -> bf16 operand copies

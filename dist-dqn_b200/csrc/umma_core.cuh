@@ -10,8 +10,12 @@
 //     reduction-index r) lives at   K-major : (i/8)*1024 + (r/8)*128 + (i%8)*16      (forward, dgrad)
 //                                   MN-major: (i/8)*1024 + (r/8)*128 + (r%8)*16      (wgrad: both operands)
 //     so one 64-deep reduction stage is 1024 bytes per 8 mn-indices and UMMA_K=16 steps are 256 bytes apart.
+//   * the gather is asynchronous: every thread issues cp.async (16- or 8-byte, zero-filled outside the image)
+//     for stages i+1 and i+2 while stage i is consumed, into a 4-slot ring.  bf16 operands land directly in
+//     their canonical position; uint8 frames and pool-routed gradients land in a raw ring and are converted /
+//     masked shared->shared by the thread that fetched them, just before the MMA.
 //   * one thread issues 4 tcgen05.mma (M=128, N=tile width, K=16) per stage and commits them to an
-//     mbarrier; two stages ping-pong so the gather of stage i+1 overlaps the MMAs of stage i.
+//     mbarrier; slots are recycled when the MMAs of stage i-2 have completed.
 //   * 4 warps read the accumulator with tcgen05.ld (warp w owns TMEM lanes 32w..32w+31, lane = tile row)
 //     and run the epilogue: bias + ReLU + 2x2 max-pool across 4 neighbouring lanes (forward), fp32 partial
 //     sums (wgrad), bf16 gradient (dgrad).
@@ -26,7 +30,7 @@ namespace umma {
 
 constexpr int TM = 128;        // tile rows (UMMA M)
 constexpr int TK = 64;         // reduction elements per stage (4 x UMMA_K)
-constexpr int TT = 128;        // threads per CTA
+constexpr int TT = 512;        // threads per CTA: 16 warps gather operands, warp w reads TMEM lanes 32*(w%4)..
 constexpr uint32_t A_STAGE_BYTES = TM * TK * 2;   // 16 KB
 
 // ------------------------------------------------------------------------------------------------ PTX wrappers
@@ -129,66 +133,65 @@ __device__ __forceinline__ void issue_stage(uint32_t tmem_d, uint32_t a_addr, ui
   mma_commit(bar);
 }
 
-// 8 consecutive input channels (bf16) or 2 pixels x 4 channels (uint8 conv1) of the input pixel that reduction
-// chunk `kc8` (k = 8*kc8 .. 8*kc8+7 in (ky,kx,c) order) of output row `r` reads; zero outside the image.
+constexpr int RS = 4;          // ring slots
+// prefetch distance is 2 stages: slot (it+2)%4 was last read by the MMAs of stage it-2
+
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, bool valid) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(valid ? 16 : 0) : "memory");
+}
+__device__ __forceinline__ void cp_async8(uint32_t dst, const void* src, bool valid) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(dst), "l"(src), "r"(valid ? 8 : 0) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// Global address of the 8 input elements that reduction chunk `kc8` (k = 8*kc8.. in (ky,kx,c) order) of output
+// row `r` reads: 8 bf16 channels of one pixel, or 2 pixels x 4 uint8 frames for conv1.  nullptr = zero (outside the
+// image -- TF SAME padding --, beyond K, or an invalid row).
 template <class G, typename TIn>
-__device__ __forceinline__ uint4 load_x_chunk(const TIn* __restrict__ x, const Row& r, int kc8) {
-  uint4 v = make_uint4(0u, 0u, 0u, 0u);
-  if (kc8 * 8 >= G::K || !r.valid) return v;
+__device__ __forceinline__ const TIn* x_chunk_ptr(const TIn* __restrict__ x, const Row& r, int kc8) {
+  if (kc8 * 8 >= G::K || !r.valid) return nullptr;
+  int c0, t;
   if constexpr (sizeof(TIn) == 1) {
     static_assert(sizeof(TIn) != 1 || G::CIN == 4, "uint8 input is the 4-frame stack");
-    const int t = kc8 * 2;                                // first of two taps (pixels)
-    const int kx = t % G::KS, ky = t / G::KS;
-    const int iy = r.oy * G::ST - G::PADH + ky, ix = r.ox * G::ST - G::PADW + kx;   // ix even, pair never straddles the border
-    if ((unsigned)iy < (unsigned)G::IH && (unsigned)ix < (unsigned)G::IW) {
-      const uint2 u = __ldg(reinterpret_cast<const uint2*>(x + ((size_t)(r.b * G::IH + iy) * G::IW + ix) * 4));
-      v.x = pack_bf16((float)(u.x & 255u), (float)((u.x >> 8) & 255u));
-      v.y = pack_bf16((float)((u.x >> 16) & 255u), (float)(u.x >> 24));
-      v.z = pack_bf16((float)(u.y & 255u), (float)((u.y >> 8) & 255u));
-      v.w = pack_bf16((float)((u.y >> 16) & 255u), (float)(u.y >> 24));
-    }
+    c0 = 0;
+    t = kc8 * 2;                       // first of two taps; the pair never straddles the border (ix is even)
   } else {
-    constexpr int CC = G::CIN / 8;                        // chunks per tap
-    const int c0 = (kc8 % CC) * 8;
-    const int t = kc8 / CC;
-    const int kx = t % G::KS, ky = t / G::KS;
-    const int iy = r.oy * G::ST - G::PADH + ky, ix = r.ox * G::ST - G::PADW + kx;
-    if ((unsigned)iy < (unsigned)G::IH && (unsigned)ix < (unsigned)G::IW)
-      v = __ldg(reinterpret_cast<const uint4*>(x + ((size_t)(r.b * G::IH + iy) * G::IW + ix) * G::CIN + c0));
+    constexpr int CC = G::CIN / 8;
+    c0 = (kc8 % CC) * 8;
+    t = kc8 / CC;
   }
+  const int kx = t % G::KS, ky = t / G::KS;
+  const int iy = r.oy * G::ST - G::PADH + ky, ix = r.ox * G::ST - G::PADW + kx;
+  if ((unsigned)iy >= (unsigned)G::IH || (unsigned)ix >= (unsigned)G::IW) return nullptr;
+  return x + ((size_t)(r.b * G::IH + iy) * G::IW + ix) * G::CIN + c0;
+}
+
+__device__ __forceinline__ uint4 cvt_u8x8(uint2 u) {     // 8 uint8 -> 8 bf16 (exact)
+  uint4 v;
+  v.x = pack_bf16((float)(u.x & 255u), (float)((u.x >> 8) & 255u));
+  v.y = pack_bf16((float)((u.x >> 16) & 255u), (float)(u.x >> 24));
+  v.z = pack_bf16((float)(u.y & 255u), (float)((u.y >> 8) & 255u));
+  v.w = pack_bf16((float)((u.y >> 16) & 255u), (float)(u.y >> 24));
   return v;
 }
 
-// 8 consecutive channels of the gradient w.r.t. the conv output, rebuilt from the gradient of the pooled
-// activation (bf16), the pool arg-max and the ReLU gate; optionally adds them to 8 running column sums.
-template <class G>
-__device__ __forceinline__ uint4 load_dz_chunk(const __nv_bfloat16* __restrict__ dact, const __nv_bfloat16* __restrict__ act,
-                                               const uint8_t* __restrict__ arg, int pidx, int win, int n0, float* colsum) {
-  const size_t off = (size_t)pidx * G::COUT + n0;
-  uint4 d = *reinterpret_cast<const uint4*>(dact + off);
-  const uint4 p = *reinterpret_cast<const uint4*>(act + off);
+// Pool routing of 8 (already ReLU-gated) gradient values: keep element e iff the window's arg-max is `win`.
+__device__ __forceinline__ uint4 route_chunk(uint4 d, uint2 arg, int win) {
   uint32_t dw[4] = {d.x, d.y, d.z, d.w};
-  const uint32_t pw[4] = {p.x, p.y, p.z, p.w};
-  uint32_t aw[2] = {0u, 0u};
-  if constexpr (G::POOL) {
-    const uint2 a = *reinterpret_cast<const uint2*>(arg + off);
-    aw[0] = a.x; aw[1] = a.y;
-  }
+  const uint32_t aw[2] = {arg.x, arg.y};
 #pragma unroll
   for (int q = 0; q < 4; ++q) {
-    // bf16 > 0  <=>  sign bit clear and magnitude non-zero
-    const bool lo_on = ((pw[q] & 0x7FFFu) != 0u) && !(pw[q] & 0x8000u);
-    const bool hi_on = ((pw[q] & 0x7FFF0000u) != 0u) && !(pw[q] & 0x80000000u);
-    bool lo = lo_on, hi = hi_on;
-    if constexpr (G::POOL) {
-      const uint32_t a2 = (aw[q >> 1] >> ((q & 1) * 16)) & 0xFFFFu;
-      lo = lo && ((a2 & 255u) == (uint32_t)win);
-      hi = hi && ((a2 >> 8) == (uint32_t)win);
-    }
+    const uint32_t a2 = (aw[q >> 1] >> ((q & 1) * 16)) & 0xFFFFu;
+    const bool lo = (a2 & 255u) == (uint32_t)win, hi = (a2 >> 8) == (uint32_t)win;
     dw[q] = (lo ? (dw[q] & 0xFFFFu) : 0u) | (hi ? (dw[q] & 0xFFFF0000u) : 0u);
-    if (colsum) { colsum[2 * q] += bf16_lo(dw[q]); colsum[2 * q + 1] += bf16_hi(dw[q]); }
   }
   return make_uint4(dw[0], dw[1], dw[2], dw[3]);
+}
+__device__ __forceinline__ void add_chunk(float* cs, const uint4& d) {
+  cs[0] += bf16_lo(d.x); cs[1] += bf16_hi(d.x); cs[2] += bf16_lo(d.y); cs[3] += bf16_hi(d.y);
+  cs[4] += bf16_lo(d.z); cs[5] += bf16_hi(d.z); cs[6] += bf16_lo(d.w); cs[7] += bf16_hi(d.w);
 }
 
 // Common prologue: barriers + TMEM allocation.  Returns the TMEM base address.
@@ -228,85 +231,108 @@ struct FwdArgsT {
   int B;
 };
 
+template <typename TIn, int NTILE>
+__host__ __device__ constexpr uint32_t fwd_smem_bytes() {
+  return (sizeof(TIn) == 1 ? RS * 8192u + 2u * A_STAGE_BYTES : RS * A_STAGE_BYTES) + RS * (uint32_t)NTILE * 128u;
+}
+
 template <class G, typename TIn, int NTILE>
 __global__ void __launch_bounds__(TT) umma_fwd_kernel(FwdArgsT a) {
   extern __shared__ __align__(1024) uint8_t smem[];
-  constexpr uint32_t B_STAGE = NTILE * TK * 2;
+  constexpr bool U8 = sizeof(TIn) == 1;
+  constexpr uint32_t B_STAGE = NTILE * 128;
+  constexpr uint32_t RAW_A = 8192;                                   // 128 rows x 64 uint8
+  constexpr uint32_t OFF_OPA = U8 ? RS * RAW_A : 0;                  // converted A tiles (uint8 input only), 2 slots
+  constexpr uint32_t OFF_B = U8 ? RS * RAW_A + 2 * A_STAGE_BYTES : RS * A_STAGE_BYTES;
   __shared__ uint64_t bars[2];
   __shared__ uint32_t tmem_slot;
+  __shared__ float bias_sm[NTILE];
   const FwdPassT P = a.p[blockIdx.z];
   const TIn* __restrict__ x = static_cast<const TIn*>(P.x);
   const int tid = threadIdx.x;
   const int m0 = blockIdx.x * TM, n0 = blockIdx.y * NTILE;
+  for (int j = tid; j < NTILE; j += TT) bias_sm[j] = __ldg(P.bias + n0 + j);
   const uint32_t tmem = setup(bars, &tmem_slot, tmem_cols(NTILE));
-  const uint32_t sA = smem_u32(smem), sB = sA + 2 * A_STAGE_BYTES;
-  const Row row = decode_row<G>(m0 + tid, a.B);
+  const uint32_t sbase = smem_u32(smem);
+  const int arow = tid & (TM - 1), ac0 = (tid >> 7) * 2;   // this thread gathers chunks ac0, ac0+1 of tile row arow
+  const Row row = decode_row<G>(m0 + arow, a.B);
   constexpr int T = (G::K + TK - 1) / TK;
-  constexpr int BCH = NTILE * 8 / TT;                 // weight chunks per thread per stage
+  constexpr int BCH = (NTILE * 8 + TT - 1) / TT;      // weight chunks per thread per stage
   constexpr uint32_t idesc = make_idesc(TM, NTILE, false, false);
-  uint4 ra[8], rb[BCH];
-  auto fetch = [&](int it) {
+  auto issue = [&](int it) {
+    if (it < T) {
+      const int slot = it & (RS - 1);
 #pragma unroll
-    for (int c = 0; c < 8; ++c) ra[c] = load_x_chunk<G, TIn>(x, row, it * 8 + c);
+      for (int cc = 0; cc < 2; ++cc) {
+        const int c = ac0 + cc;
+        const TIn* src = x_chunk_ptr<G, TIn>(x, row, it * 8 + c);
+        if constexpr (U8) cp_async8(sbase + slot * RAW_A + arow * 64 + c * 8, src ? src : x, src != nullptr);
+        else cp_async16(sbase + slot * A_STAGE_BYTES + kmajor_off(arow, c), src ? src : x, src != nullptr);
+      }
 #pragma unroll
-    for (int q = 0; q < BCH; ++q) {
-      const int ch = tid + TT * q, n = ch >> 3, kc = ch & 7;
-      const int k = it * TK + kc * 8;
-      rb[q] = (k < G::K) ? __ldg(reinterpret_cast<const uint4*>(P.wt + (size_t)(n0 + n) * G::K + k)) : make_uint4(0u, 0u, 0u, 0u);
+      for (int q = 0; q < BCH; ++q) {
+        const int ch = tid + TT * q, n = ch >> 3, kc = ch & 7;
+        const int k = it * TK + kc * 8;
+        if (ch < NTILE * 8)
+          cp_async16(sbase + OFF_B + slot * B_STAGE + kmajor_off(n, kc), P.wt + (size_t)(n0 + n) * G::K + (k < G::K ? k : 0),
+                     k < G::K);
+      }
     }
+    cp_async_commit();
   };
-  fetch(0);
+  issue(0);
+  issue(1);
   for (int it = 0; it < T; ++it) {
-    const int s = it & 1;
-    if (it >= 2) mbar_wait(&bars[s], ((it >> 1) - 1) & 1);     // MMAs of iteration it-2 have drained stage s
-    uint8_t* A = smem + s * A_STAGE_BYTES;
-    uint8_t* Bm = smem + 2 * A_STAGE_BYTES + s * B_STAGE;
-#pragma unroll
-    for (int c = 0; c < 8; ++c) *reinterpret_cast<uint4*>(A + kmajor_off(tid, c)) = ra[c];
-#pragma unroll
-    for (int q = 0; q < BCH; ++q) {
-      const int ch = tid + TT * q;
-      *reinterpret_cast<uint4*>(Bm + kmajor_off(ch >> 3, ch & 7)) = rb[q];
+    const int slot = it & (RS - 1), par = it & 1;
+    if (it >= 2) mbar_wait(&bars[par], ((it >> 1) - 1) & 1);   // MMAs of stage it-2 are done: their slots are free
+    issue(it + 2);
+    cp_async_wait<2>();                                         // this thread's copies for stage `it` have landed
+    uint32_t a_addr;
+    if constexpr (U8) {
+      uint8_t* opa = smem + OFF_OPA + par * A_STAGE_BYTES;
+      const uint4 u = *reinterpret_cast<const uint4*>(smem + slot * RAW_A + arow * 64 + ac0 * 8);   // this thread's 2 chunks
+      *reinterpret_cast<uint4*>(opa + kmajor_off(arow, ac0)) = cvt_u8x8(make_uint2(u.x, u.y));
+      *reinterpret_cast<uint4*>(opa + kmajor_off(arow, ac0 + 1)) = cvt_u8x8(make_uint2(u.z, u.w));
+      a_addr = sbase + OFF_OPA + par * A_STAGE_BYTES;
+    } else {
+      a_addr = sbase + slot * A_STAGE_BYTES;
     }
     fence_async_proxy();
     __syncthreads();
-    if (tid == 0) issue_stage(tmem, sA + s * A_STAGE_BYTES, sB + s * B_STAGE, idesc, it == 0, &bars[s]);
-    if (it + 1 < T) fetch(it + 1);
+    if (tid == 0) issue_stage(tmem, a_addr, sbase + OFF_B + slot * B_STAGE, idesc, it == 0, &bars[par]);
   }
   // the last commit covers every MMA issued before it
   mbar_wait(&bars[(T - 1) & 1], ((T - 1) >> 1) & 1);
   tc_fence_after();
   const int warp = tid >> 5, lane = tid & 31;
-  const uint32_t trow = tmem + ((uint32_t)(warp * 32) << 16);
+  const uint32_t trow = tmem + ((uint32_t)((warp & 3) * 32) << 16);    // tile row = arow (same for warps w and w+4k)
   const bool row_in = row.valid;
 #pragma unroll 1
-  for (int c0 = 0; c0 < NTILE; c0 += 32) {
+  for (int c0 = (warp >> 2) * 32; c0 < NTILE; c0 += 128) {             // the 4 warps of a lane group split the columns
     float v[32];
     tmem_ld32(trow + c0, v);
     const int n = n0 + c0;
 #pragma unroll
-    for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j] + __ldg(P.bias + n + j), 0.f);
+    for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j] + bias_sm[c0 + j], 0.f);
     if constexpr (G::POOL) {
-      // rows 4q..4q+3 (= lanes) are one pool window; invalid rows never win; first maximum wins ties
-      uint32_t idx[32];
+      // Lanes 4q..4q+3 hold the 4 conv outputs of one pool window.  Values are >= 0 after ReLU, so their float bits
+      // order like unsigned integers: pack (value with the 2 lowest mantissa bits replaced by 3-win) into one key and
+      // take the maximum over the window -- largest value wins, ties go to the first window element, rows outside
+      // the image (key 0) never beat a positive value.  The 2 dropped bits are far below bf16 resolution.
+      uint32_t key[32];
 #pragma unroll
       for (int j = 0; j < 32; ++j) {
-        float best = row_in ? v[j] : -1.f;
-        uint32_t bi = (uint32_t)(lane & 3);
-#pragma unroll
-        for (int sft = 1; sft <= 2; sft <<= 1) {
-          const float ov = __shfl_xor_sync(0xffffffffu, best, sft);
-          const uint32_t oi = __shfl_xor_sync(0xffffffffu, bi, sft);
-          if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
-        }
-        v[j] = best;
-        idx[j] = bi;
+        uint32_t kj = row_in ? ((__float_as_uint(v[j]) & ~3u) | (3u - (uint32_t)(lane & 3))) : 0u;
+        kj = max(kj, __shfl_xor_sync(0xffffffffu, kj, 1));
+        kj = max(kj, __shfl_xor_sync(0xffffffffu, kj, 2));
+        key[j] = kj;
       }
       if ((lane & 3) == 0 && row.b < a.B) {
         const size_t off = (size_t)row.pidx * G::COUT + n;
         uint32_t pk[16];
 #pragma unroll
-        for (int j = 0; j < 16; ++j) pk[j] = pack_bf16(v[2 * j], v[2 * j + 1]);
+        for (int j = 0; j < 16; ++j)
+          pk[j] = pack_bf16(__uint_as_float(key[2 * j] & ~3u), __uint_as_float(key[2 * j + 1] & ~3u));
 #pragma unroll
         for (int j = 0; j < 4; ++j)
           *reinterpret_cast<uint4*>(P.out + off + 8 * j) = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
@@ -314,7 +340,8 @@ __global__ void __launch_bounds__(TT) umma_fwd_kernel(FwdArgsT a) {
           uint32_t ak[8];
 #pragma unroll
           for (int j = 0; j < 8; ++j)
-            ak[j] = idx[4 * j] | (idx[4 * j + 1] << 8) | (idx[4 * j + 2] << 16) | (idx[4 * j + 3] << 24);
+            ak[j] = (3u - (key[4 * j] & 3u)) | ((3u - (key[4 * j + 1] & 3u)) << 8) | ((3u - (key[4 * j + 2] & 3u)) << 16) |
+                    ((3u - (key[4 * j + 3] & 3u)) << 24);
           *reinterpret_cast<uint4*>(P.arg + off) = make_uint4(ak[0], ak[1], ak[2], ak[3]);
           *reinterpret_cast<uint4*>(P.arg + off + 16) = make_uint4(ak[4], ak[5], ak[6], ak[7]);
         }
@@ -340,95 +367,148 @@ __global__ void __launch_bounds__(TT) umma_fwd_kernel(FwdArgsT a) {
 }
 
 // ------------------------------------------------------------------------------------------------ weight gradient
+// dactg is the gradient w.r.t. the layer's pooled output, ALREADY multiplied by the ReLU gate (act > 0) by the
+// kernel that produced it (td_head / umma_dgrad); only the pool routing (arg-max == window position) remains.
 struct WgradArgsT {
   const void* x;                  // layer input: uint8 stacks (conv1) or bf16 activations
-  const __nv_bfloat16* dact;      // gradient of the layer's pooled output
-  const __nv_bfloat16* act;       // the layer's pooled output
-  const uint8_t* arg;
+  const __nv_bfloat16* dactg;
+  const uint8_t* arg;             // pool arg-max (POOL layers)
   float* partial;                 // [nsplit][(K+1)*COUT] fp32
   int B;
   int rows_per_split;             // multiple of TK
 };
 
 template <class G, typename TIn, int NTILE>
+__host__ __device__ constexpr uint32_t wgrad_smem_bytes() {
+  constexpr uint32_t a = sizeof(TIn) == 1 ? RS * 8192u + 2u * A_STAGE_BYTES : RS * A_STAGE_BYTES;
+  constexpr uint32_t nchunk = 64u * (uint32_t)NTILE / 8u;                 // dZ chunks per stage
+  constexpr uint32_t b = G::POOL ? RS * nchunk * 24u + 2u * (uint32_t)NTILE * 128u : RS * (uint32_t)NTILE * 128u;
+  return a + b;
+}
+
+template <class G, typename TIn, int NTILE>
 __global__ void __launch_bounds__(TT) umma_wgrad_kernel(WgradArgsT a) {
   extern __shared__ __align__(1024) uint8_t smem[];
-  constexpr uint32_t B_STAGE = NTILE * TK * 2;
+  constexpr bool U8 = sizeof(TIn) == 1;
+  constexpr uint32_t B_STAGE = NTILE * 128;
+  constexpr uint32_t RAW_A = 8192;                                   // 64 rows x 128 uint8
+  constexpr uint32_t OFF_OPA = U8 ? RS * RAW_A : 0;
+  constexpr uint32_t OFF_B = U8 ? RS * RAW_A + 2 * A_STAGE_BYTES : RS * A_STAGE_BYTES;
+  constexpr uint32_t NCH = 64 * NTILE / 8;                           // dZ chunks per stage
+  constexpr uint32_t RAW_BD = NCH * 16, RAW_BA = NCH * 8;            // raw gradient / raw arg-max per stage
+  constexpr uint32_t OFF_RAWA2 = OFF_B + RS * RAW_BD;                // (POOL) arg ring
+  constexpr uint32_t OFF_OPB = OFF_RAWA2 + RS * RAW_BA;              // (POOL) routed B tiles, 2 slots
   __shared__ uint64_t bars[2];
   __shared__ uint32_t tmem_slot;
   __shared__ float bias_sm[NTILE];
   const TIn* __restrict__ x = static_cast<const TIn*>(a.x);
   const int tid = threadIdx.x;
   const int i0 = blockIdx.x * TM, n0 = blockIdx.y * NTILE;     // i = (ky,kx,c) index, rows of the output tile
+  for (int j = tid; j < NTILE; j += TT) bias_sm[j] = 0.f;
   const uint32_t tmem = setup(bars, &tmem_slot, tmem_cols(NTILE));
-  const uint32_t sA = smem_u32(smem), sB = sA + 2 * A_STAGE_BYTES;
+  const uint32_t sbase = smem_u32(smem);
   const int R = a.B * G::ROWS;
   const int r_begin = blockIdx.z * a.rows_per_split;
   const int r_end = min(R, r_begin + a.rows_per_split);
   const int T = (r_end - r_begin + TK - 1) / TK;
   const bool do_bias = blockIdx.x == 0;
-  for (int j = tid; j < NTILE; j += TT) bias_sm[j] = 0.f;
-  __syncthreads();
   constexpr uint32_t idesc = make_idesc(TM, NTILE, true, true);
-  // A: 64 rows x 16 chunks (of 8 k) per stage -> 8 per thread; B: 64 rows x NTILE/8 chunks -> NTILE/16 per thread
-  constexpr int BCH = NTILE / 16;
-  const int am = tid & 63, ag0 = tid >> 6;            // A chunks g = ag0 + 2q of row am
-  uint4 ra[8], rb[BCH];
-  float colsum[BCH][8];
-#pragma unroll
-  for (int q = 0; q < BCH; ++q)
-#pragma unroll
-    for (int e = 0; e < 8; ++e) colsum[q][e] = 0.f;
-  // B chunk assignment: chunk id = tid + TT*q ; row = id / (NTILE/8), g = id % (NTILE/8)  (g is the same for every q
-  // when TT is a multiple of NTILE/8, so each thread owns fixed output columns for the bias sum)
+  // A: 64 rows x 16 chunks (8 k each) per stage -> 2 per thread (row am, chunks ag0, ag0+1)
+  // B: 64 rows x NTILE/8 chunks (chunk id = tid + TT*q: row id/GPR, column chunk bg = tid%GPR)
+  constexpr int BCH = (64 * NTILE / 8 + TT - 1) / TT;
   constexpr int GPR = NTILE / 8;
+  constexpr int NCHB = 64 * NTILE / 8;
+  const int am = tid & 63, ag0 = (tid >> 6) * 2;      // A chunks ag0, ag0+1 of reduction row am
   const int bg = tid % GPR;
-  auto fetch = [&](int it) {
-    const int rbase = r_begin + it * TK;
-    const Row ar = decode_row<G>(rbase + am, a.B);
-    const bool arow_ok = (rbase + am) < r_end;
+  float colsum[8];
 #pragma unroll
-    for (int q = 0; q < 8; ++q) {
-      const int g = ag0 + 2 * q;
-      ra[q] = arow_ok ? load_x_chunk<G, TIn>(x, ar, (i0 >> 3) + g) : make_uint4(0u, 0u, 0u, 0u);
-    }
+  for (int e = 0; e < 8; ++e) colsum[e] = 0.f;
+  auto issue = [&](int it) {
+    if (it < T) {
+      const int slot = it & (RS - 1);
+      const int rbase = r_begin + it * TK;
+      const Row ar = decode_row<G>(rbase + am, a.B);
+      const bool arow_ok = (rbase + am) < r_end;
 #pragma unroll
-    for (int q = 0; q < BCH; ++q) {
-      const int id = tid + TT * q;
-      const int rr = id / GPR;
-      const Row br = decode_row<G>(rbase + rr, a.B);
-      rb[q] = (br.valid && (rbase + rr) < r_end)
-                  ? load_dz_chunk<G>(a.dact, a.act, a.arg, br.pidx, br.win, n0 + bg * 8, do_bias ? colsum[q] : nullptr)
-                  : make_uint4(0u, 0u, 0u, 0u);
+      for (int q = 0; q < 2; ++q) {
+        const int g = ag0 + q;
+        const TIn* src = arow_ok ? x_chunk_ptr<G, TIn>(x, ar, (i0 >> 3) + g) : nullptr;
+        if constexpr (U8) cp_async8(sbase + slot * RAW_A + (am * 16 + g) * 8, src ? src : x, src != nullptr);
+        else cp_async16(sbase + slot * A_STAGE_BYTES + mnmajor_off(g, am), src ? src : x, src != nullptr);
+      }
+#pragma unroll
+      for (int q = 0; q < BCH; ++q) {
+        const int id = tid + TT * q, rr = id / GPR;
+        if (id >= NCHB) break;
+        const Row br = decode_row<G>(rbase + rr, a.B);
+        const bool ok = br.valid && (rbase + rr) < r_end;
+        const size_t off = (size_t)(ok ? br.pidx : 0) * G::COUT + n0 + bg * 8;
+        if constexpr (G::POOL) {
+          cp_async16(sbase + OFF_B + slot * RAW_BD + id * 16, a.dactg + off, ok);
+          cp_async8(sbase + OFF_RAWA2 + slot * RAW_BA + id * 8, a.arg + off, ok);
+        } else {
+          cp_async16(sbase + OFF_B + slot * B_STAGE + mnmajor_off(bg, rr), a.dactg + off, ok);
+        }
+      }
     }
+    cp_async_commit();
   };
-  if (T > 0) fetch(0);
+  issue(0);
+  issue(1);
   for (int it = 0; it < T; ++it) {
-    const int s = it & 1;
-    if (it >= 2) mbar_wait(&bars[s], ((it >> 1) - 1) & 1);
-    uint8_t* A = smem + s * A_STAGE_BYTES;
-    uint8_t* Bm = smem + 2 * A_STAGE_BYTES + s * B_STAGE;
+    const int slot = it & (RS - 1), par = it & 1;
+    if (it >= 2) mbar_wait(&bars[par], ((it >> 1) - 1) & 1);
+    issue(it + 2);
+    cp_async_wait<2>();
+    uint32_t a_addr, b_addr;
+    if constexpr (U8) {
+      uint8_t* opa = smem + OFF_OPA + par * A_STAGE_BYTES;
+      const uint4 u = *reinterpret_cast<const uint4*>(smem + slot * RAW_A + (am * 16 + ag0) * 8);   // this thread's 2 chunks
+      *reinterpret_cast<uint4*>(opa + mnmajor_off(ag0, am)) = cvt_u8x8(make_uint2(u.x, u.y));
+      *reinterpret_cast<uint4*>(opa + mnmajor_off(ag0 + 1, am)) = cvt_u8x8(make_uint2(u.z, u.w));
+      a_addr = sbase + OFF_OPA + par * A_STAGE_BYTES;
+    } else {
+      a_addr = sbase + slot * A_STAGE_BYTES;
+    }
+    if constexpr (G::POOL) {
+      uint8_t* opb = smem + OFF_OPB + par * B_STAGE;
+      const int rbase = r_begin + it * TK;
 #pragma unroll
-    for (int q = 0; q < 8; ++q) *reinterpret_cast<uint4*>(A + mnmajor_off(ag0 + 2 * q, am)) = ra[q];
+      for (int q = 0; q < BCH; ++q) {
+        const int id = tid + TT * q, rr = id / GPR;
+        if (id >= NCHB) break;
+        const int win = (rbase + rr) & 3;                               // pool-window position of this row
+        const uint4 d = *reinterpret_cast<const uint4*>(smem + OFF_B + slot * RAW_BD + id * 16);
+        const uint2 ag = *reinterpret_cast<const uint2*>(smem + OFF_RAWA2 + slot * RAW_BA + id * 8);
+        const uint4 z = route_chunk(d, ag, win);
+        *reinterpret_cast<uint4*>(opb + mnmajor_off(bg, rr)) = z;
+        if (do_bias) add_chunk(colsum, z);
+      }
+      b_addr = sbase + OFF_OPB + par * B_STAGE;
+    } else {
+      if (do_bias) {
 #pragma unroll
-    for (int q = 0; q < BCH; ++q) {
-      const int id = tid + TT * q;
-      *reinterpret_cast<uint4*>(Bm + mnmajor_off(bg, id / GPR)) = rb[q];
+        for (int q = 0; q < BCH; ++q) {
+          const int id = tid + TT * q, rr = id / GPR;
+          if (id >= NCHB) break;
+          add_chunk(colsum, *reinterpret_cast<const uint4*>(smem + OFF_B + slot * B_STAGE + mnmajor_off(bg, rr)));
+        }
+      }
+      b_addr = sbase + OFF_B + slot * B_STAGE;
     }
     fence_async_proxy();
     __syncthreads();
-    if (tid == 0) issue_stage(tmem, sA + s * A_STAGE_BYTES, sB + s * B_STAGE, idesc, it == 0, &bars[s]);
-    if (it + 1 < T) fetch(it + 1);
+    if (tid == 0) issue_stage(tmem, a_addr, b_addr, idesc, it == 0, &bars[par]);
   }
   float* out = a.partial + (size_t)blockIdx.z * ((size_t)(G::K + 1) * G::COUT);
   const int warp = tid >> 5, lane = tid & 31;
-  const int k = i0 + warp * 32 + lane;
+  const int k = i0 + (warp & 3) * 32 + lane;
   if (T > 0) {
     mbar_wait(&bars[(T - 1) & 1], ((T - 1) >> 1) & 1);
     tc_fence_after();
-    const uint32_t trow = tmem + ((uint32_t)(warp * 32) << 16);
+    const uint32_t trow = tmem + ((uint32_t)((warp & 3) * 32) << 16);
 #pragma unroll 1
-    for (int c0 = 0; c0 < NTILE; c0 += 32) {
+    for (int c0 = (warp >> 2) * 32; c0 < NTILE; c0 += 128) {
       float v[32];
       tmem_ld32(trow + c0, v);
       if (k < G::K) {
@@ -438,14 +518,14 @@ __global__ void __launch_bounds__(TT) umma_wgrad_kernel(WgradArgsT a) {
               make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
       }
     }
-  } else if (k < G::K) {
+  } else if (k < G::K && warp < 4) {
     for (int c = 0; c < NTILE; ++c) out[(size_t)k * G::COUT + n0 + c] = 0.f;
   }
   if (do_bias) {
+    if (tid < NCHB) {
 #pragma unroll
-    for (int q = 0; q < BCH; ++q)
-#pragma unroll
-      for (int e = 0; e < 8; ++e) atomicAdd(&bias_sm[bg * 8 + e], colsum[q][e]);
+      for (int e = 0; e < 8; ++e) atomicAdd(&bias_sm[bg * 8 + e], colsum[e]);
+    }
     __syncthreads();
     for (int j = tid; j < NTILE; j += TT) out[(size_t)G::K * G::COUT + n0 + j] = bias_sm[j];
   }
@@ -455,96 +535,138 @@ __global__ void __launch_bounds__(TT) umma_wgrad_kernel(WgradArgsT a) {
 // ------------------------------------------------------------------------------------------------ data gradient
 struct DgradArgsT {
   const __nv_bfloat16* wd;        // weights permuted to [CIN][KS*KS*COUT]
-  const __nv_bfloat16* dact;
-  const __nv_bfloat16* act;
+  const __nv_bfloat16* dactg;     // ReLU-gated gradient of this layer's pooled output
   const uint8_t* arg;
-  __nv_bfloat16* dx;              // [B, IH, IW, CIN] gradient of the previous layer's pooled activation
+  const __nv_bfloat16* act_prev;  // previous layer's pooled output: its ReLU gate is applied to dx here
+  __nv_bfloat16* dx;              // [B, IH, IW, CIN] gated gradient of the previous layer's pooled output
   int B;
 };
 
 template <class G, int NTILE>
+__host__ __device__ constexpr uint32_t dgrad_smem_bytes() {
+  constexpr uint32_t a = G::POOL ? RS * (1024u * 16u + 1024u * 8u + 1024u) + 2u * A_STAGE_BYTES : RS * A_STAGE_BYTES;
+  return a + RS * (uint32_t)NTILE * 128u;
+}
+
+template <class G, int NTILE>
 __global__ void __launch_bounds__(TT) umma_dgrad_kernel(DgradArgsT a) {
   extern __shared__ __align__(1024) uint8_t smem[];
-  constexpr uint32_t B_STAGE = NTILE * TK * 2;
+  constexpr uint32_t B_STAGE = NTILE * 128;
   constexpr int KD = G::KS * G::KS * G::COUT;
   constexpr int CC = G::COUT / 8;                     // chunks per filter tap
+  // POOL: raw rings (gradient chunks, arg-max chunks, window byte per chunk) + 2 routed A tiles; else direct A ring
+  constexpr uint32_t RAW_D = 1024 * 16, RAW_G = 1024 * 8, RAW_W = 1024;
+  constexpr uint32_t OFF_RG = RS * RAW_D, OFF_RW = OFF_RG + RS * RAW_G, OFF_OPA = OFF_RW + RS * RAW_W;
+  constexpr uint32_t OFF_B = G::POOL ? OFF_OPA + 2 * A_STAGE_BYTES : RS * A_STAGE_BYTES;
   __shared__ uint64_t bars[2];
   __shared__ uint32_t tmem_slot;
   const int tid = threadIdx.x;
   const int m0 = blockIdx.x * TM, c0t = blockIdx.y * NTILE;
   const uint32_t tmem = setup(bars, &tmem_slot, tmem_cols(NTILE));
-  const uint32_t sA = smem_u32(smem), sB = sA + 2 * A_STAGE_BYTES;
+  const uint32_t sbase = smem_u32(smem);
   const int M = a.B * G::IH * G::IW;
-  const int m = m0 + tid;
+  const int arow = tid & (TM - 1), ac0 = (tid >> 7) * 2;   // chunks ac0, ac0+1 of tile row arow
+  const int m = m0 + arow;
   const int b = m / (G::IH * G::IW);
   const int rem = m - b * (G::IH * G::IW);
   const int iy = rem / G::IW, ix = rem - iy * G::IW;
   const bool mvalid = m < M;
   constexpr int T = KD / TK;
   static_assert(KD % TK == 0, "dgrad reduction must be a multiple of the stage depth");
-  constexpr int BCH = NTILE * 8 / TT;
+  constexpr int BCH = (NTILE * 8 + TT - 1) / TT;
   constexpr uint32_t idesc = make_idesc(TM, NTILE, false, false);
-  uint4 ra[8], rb[BCH];
-  auto dz_at = [&](int kc8) -> uint4 {
-    const int nq = kc8 % CC, t = kc8 / CC;
-    const int kx = t % G::KS, ky = t / G::KS;
-    const int ty = iy + G::PADH - ky, tx = ix + G::PADW - kx;
-    if (!mvalid || ty < 0 || tx < 0 || (ty % G::ST) != 0 || (tx % G::ST) != 0) return make_uint4(0u, 0u, 0u, 0u);
-    const int oy = ty / G::ST, ox = tx / G::ST;
-    if (oy >= G::OH || ox >= G::OW) return make_uint4(0u, 0u, 0u, 0u);
-    int pidx, win;
-    if constexpr (G::POOL) {
-      pidx = (b * G::PH + (oy >> 1)) * G::PW + (ox >> 1);
-      win = (oy & 1) * 2 + (ox & 1);
-    } else {
-      pidx = (b * G::OH + oy) * G::OW + ox;
-      win = 0;
-    }
-    return load_dz_chunk<G>(a.dact, a.act, a.arg, pidx, win, nq * 8, nullptr);
-  };
-  auto fetch = [&](int it) {
+  auto issue = [&](int it) {
+    if (it < T) {
+      const int slot = it & (RS - 1);
 #pragma unroll
-    for (int c = 0; c < 8; ++c) ra[c] = dz_at(it * 8 + c);
+      for (int cc = 0; cc < 2; ++cc) {
+        const int c = ac0 + cc;
+        const int kc8 = it * 8 + c;
+        const int nq = kc8 % CC, t = kc8 / CC;
+        const int kx = t % G::KS, ky = t / G::KS;
+        const int ty = iy + G::PADH - ky, tx = ix + G::PADW - kx;
+        bool ok = mvalid && ty >= 0 && tx >= 0 && (ty % G::ST) == 0 && (tx % G::ST) == 0;
+        const int oy = ty / G::ST, ox = tx / G::ST;
+        ok = ok && oy < G::OH && ox < G::OW;
+        int pidx = 0, win = 0;
+        if (ok) {
+          if constexpr (G::POOL) {
+            pidx = (b * G::PH + (oy >> 1)) * G::PW + (ox >> 1);
+            win = (oy & 1) * 2 + (ox & 1);
+          } else {
+            pidx = (b * G::OH + oy) * G::OW + ox;
+          }
+        }
+        const size_t off = (size_t)pidx * G::COUT + nq * 8;
+        if constexpr (G::POOL) {
+          cp_async16(sbase + slot * RAW_D + (arow * 8 + c) * 16, a.dactg + off, ok);
+          cp_async8(sbase + OFF_RG + slot * RAW_G + (arow * 8 + c) * 8, a.arg + off, ok);
+          smem[OFF_RW + slot * RAW_W + arow * 8 + c] = (uint8_t)win;
+        } else {
+          cp_async16(sbase + slot * A_STAGE_BYTES + kmajor_off(arow, c), a.dactg + off, ok);
+        }
+      }
 #pragma unroll
-    for (int q = 0; q < BCH; ++q) {
-      const int ch = tid + TT * q, n = ch >> 3, kc = ch & 7;
-      rb[q] = __ldg(reinterpret_cast<const uint4*>(a.wd + (size_t)(c0t + n) * KD + it * TK + kc * 8));
+      for (int q = 0; q < BCH; ++q) {
+        const int ch = tid + TT * q, n = ch >> 3, kc = ch & 7;
+        if (ch < NTILE * 8)
+          cp_async16(sbase + OFF_B + slot * B_STAGE + kmajor_off(n, kc), a.wd + (size_t)(c0t + n) * KD + it * TK + kc * 8, true);
+      }
     }
+    cp_async_commit();
   };
-  fetch(0);
+  issue(0);
+  issue(1);
   for (int it = 0; it < T; ++it) {
-    const int s = it & 1;
-    if (it >= 2) mbar_wait(&bars[s], ((it >> 1) - 1) & 1);
-    uint8_t* A = smem + s * A_STAGE_BYTES;
-    uint8_t* Bm = smem + 2 * A_STAGE_BYTES + s * B_STAGE;
+    const int slot = it & (RS - 1), par = it & 1;
+    if (it >= 2) mbar_wait(&bars[par], ((it >> 1) - 1) & 1);
+    issue(it + 2);
+    cp_async_wait<2>();
+    uint32_t a_addr;
+    if constexpr (G::POOL) {
+      uint8_t* opa = smem + OFF_OPA + par * A_STAGE_BYTES;
 #pragma unroll
-    for (int c = 0; c < 8; ++c) *reinterpret_cast<uint4*>(A + kmajor_off(tid, c)) = ra[c];
-#pragma unroll
-    for (int q = 0; q < BCH; ++q) {
-      const int ch = tid + TT * q;
-      *reinterpret_cast<uint4*>(Bm + kmajor_off(ch >> 3, ch & 7)) = rb[q];
+      for (int cc = 0; cc < 2; ++cc) {
+        const int c = ac0 + cc;
+        const uint4 d = *reinterpret_cast<const uint4*>(smem + slot * RAW_D + (arow * 8 + c) * 16);
+        const uint2 ag = *reinterpret_cast<const uint2*>(smem + OFF_RG + slot * RAW_G + (arow * 8 + c) * 8);
+        const int win = (int)smem[OFF_RW + slot * RAW_W + arow * 8 + c];
+        *reinterpret_cast<uint4*>(opa + kmajor_off(arow, c)) = route_chunk(d, ag, win);
+      }
+      a_addr = sbase + OFF_OPA + par * A_STAGE_BYTES;
+    } else {
+      a_addr = sbase + slot * A_STAGE_BYTES;
     }
     fence_async_proxy();
     __syncthreads();
-    if (tid == 0) issue_stage(tmem, sA + s * A_STAGE_BYTES, sB + s * B_STAGE, idesc, it == 0, &bars[s]);
-    if (it + 1 < T) fetch(it + 1);
+    if (tid == 0) issue_stage(tmem, a_addr, sbase + OFF_B + slot * B_STAGE, idesc, it == 0, &bars[par]);
   }
   mbar_wait(&bars[(T - 1) & 1], ((T - 1) >> 1) & 1);
   tc_fence_after();
   const int warp = tid >> 5;
-  const uint32_t trow = tmem + ((uint32_t)(warp * 32) << 16);
+  const uint32_t trow = tmem + ((uint32_t)((warp & 3) * 32) << 16);
 #pragma unroll 1
-  for (int c0 = 0; c0 < NTILE; c0 += 32) {
+  for (int c0 = (warp >> 2) * 32; c0 < NTILE; c0 += 128) {
     float v[32];
     tmem_ld32(trow + c0, v);
     if (mvalid) {
+      const size_t off = (size_t)m * G::CIN + c0t + c0;
       uint32_t pk[16];
 #pragma unroll
-      for (int j = 0; j < 16; ++j) pk[j] = pack_bf16(v[2 * j], v[2 * j + 1]);
+      for (int j = 0; j < 4; ++j) {
+        // ReLU gate of the layer below: zero the gradient where its (pooled) output is not positive
+        const uint4 p = *reinterpret_cast<const uint4*>(a.act_prev + off + 8 * j);
+        const uint32_t pw[4] = {p.x, p.y, p.z, p.w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const bool lo = ((pw[q] & 0x7FFFu) != 0u) && !(pw[q] & 0x8000u);
+          const bool hi = ((pw[q] & 0x7FFF0000u) != 0u) && !(pw[q] & 0x80000000u);
+          pk[4 * j + q] = pack_bf16(lo ? v[8 * j + 2 * q] : 0.f, hi ? v[8 * j + 2 * q + 1] : 0.f);
+        }
+      }
 #pragma unroll
       for (int j = 0; j < 4; ++j)
-        *reinterpret_cast<uint4*>(a.dx + (size_t)m * G::CIN + c0t + c0 + 8 * j) =
-            make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+        *reinterpret_cast<uint4*>(a.dx + off + 8 * j) = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
     }
   }
   teardown(tmem, tmem_cols(NTILE));
