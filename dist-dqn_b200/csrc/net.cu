@@ -459,6 +459,10 @@ struct dqn_net_s {
   dqn_hyper_t hyper;
   MlpOff mo;
   std::vector<void*> allocs;
+  // weight-gradient kernels run on a forked stream, concurrently with the data-gradient chain (captured into the
+  // step's CUDA graph as a parallel branch)
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_fork[3] = {}, ev_join = nullptr;
   // bf16 tensor-core mode (precision == 1; DQN_ARCH_CNN only)
   int precision = 0;
   __nv_bfloat16* act_bf[2][4] = {};
@@ -608,6 +612,14 @@ extern "C" int dqn_net_create(dqn_net_t* out, int32_t arch, const int32_t* in_sh
       NET_ALLOC(h->L[l].partial, (size_t)h->L[l].maxsplit * (h->L[l].K + 1) * h->L[l].N * 4);
     }
     NET_ALLOC(h->head_partial, (size_t)(h->F + 1) * A * 4);
+    cudaError_t e = cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking);
+    for (int i = 0; i < 3 && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&h->ev_fork[i], cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming);
+    if (e != cudaSuccess) {
+      int rc = set_err(DQN_ERR_CUDA, "dqn_net_create: %s", cudaGetErrorString(e));
+      dqn_net_destroy(h);
+      return rc;
+    }
   }
   *out = h;
   return 0;
@@ -618,6 +630,9 @@ extern "C" int dqn_net_destroy(dqn_net_t h) {
   DeviceGuard g(h->device);
   cudaDeviceSynchronize();
   for (void* p : h->allocs) cudaFree(p);
+  if (h->side) cudaStreamDestroy(h->side);
+  for (int i = 0; i < 3; ++i) if (h->ev_fork[i]) cudaEventDestroy(h->ev_fork[i]);
+  if (h->ev_join) cudaEventDestroy(h->ev_join);
   for (int i = 0; i < DQN_NUM_STAGES; ++i) {
     if (h->ev0[i]) cudaEventDestroy(h->ev0[i]);
     if (h->ev1[i]) cudaEventDestroy(h->ev1[i]);
@@ -1024,34 +1039,52 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
                                                 h->se, h->g, h->dact[3], h->precision == 1 ? h->dact_bf[3] : nullptr,
                                                 h->step);
     }
+    // fork: head/fc/conv3/conv2 weight gradients on the side stream, data-gradient chain + conv1 wgrad on `st`
+    cudaStream_t sd = h->side;
+    DQN_CUDA(cudaEventRecord(h->ev_fork[0], st));
+    DQN_CUDA(cudaStreamWaitEvent(sd, h->ev_fork[0], 0));
     {
-    StageScope sc(h, DQN_STAGE_HEAD_WGRAD, st);
-    head_wgrad_kernel<<<((h->F + 1) * h->A + 255) / 256, 256, 0, st>>>(h->act[0][3], h->g, d_actions, k, h->F, h->A,
+    StageScope sc(h, DQN_STAGE_HEAD_WGRAD, sd);
+    head_wgrad_kernel<<<((h->F + 1) * h->A + 255) / 256, 256, 0, sd>>>(h->act[0][3], h->g, d_actions, k, h->F, h->A,
                                                                        h->head_partial);
     }
     if (d_loss) {
       fill_segs(h, &oa, nsplit, false);
-      StageScope sc(h, DQN_STAGE_LOSS, st);
-      loss_kernel<<<1, 256, 0, st>>>(oa, h->se, k, d_loss);
+      StageScope sc(h, DQN_STAGE_LOSS, sd);
+      loss_kernel<<<1, 256, 0, sd>>>(oa, h->se, k, d_loss);
     }
+    auto fork_after_dgrad = [&](int i) -> int {      // dact of the next layer down is ready on `st`
+      DQN_CUDA(cudaEventRecord(h->ev_fork[i], st));
+      DQN_CUDA(cudaStreamWaitEvent(sd, h->ev_fork[i], 0));
+      return 0;
+    };
     if (h->precision == 1) {
-      launch_wgrad_tc<F4, __nv_bfloat16, 256>(h, 3, h->act_bf[0][2], k, st, &nsplit[3]); launch_dgrad_tc<F4, 256>(h, 3, k, st);
-      launch_wgrad_tc<C3, __nv_bfloat16, 64>(h, 2, h->act_bf[0][1], k, st, &nsplit[2]); launch_dgrad_tc<C3, 64>(h, 2, k, st);
-      launch_wgrad_tc<C2, __nv_bfloat16, 64>(h, 1, h->act_bf[0][0], k, st, &nsplit[1]); launch_dgrad_tc<C2, 32>(h, 1, k, st);
+      launch_wgrad_tc<F4, __nv_bfloat16, 128>(h, 3, h->act_bf[0][2], k, sd, &nsplit[3]); launch_dgrad_tc<F4, 256>(h, 3, k, st);
+      if (fork_after_dgrad(1)) return DQN_ERR_CUDA;
+      launch_wgrad_tc<C3, __nv_bfloat16, 64>(h, 2, h->act_bf[0][1], k, sd, &nsplit[2]); launch_dgrad_tc<C3, 64>(h, 2, k, st);
+      if (fork_after_dgrad(2)) return DQN_ERR_CUDA;
+      launch_wgrad_tc<C2, __nv_bfloat16, 64>(h, 1, h->act_bf[0][0], k, sd, &nsplit[1]); launch_dgrad_tc<C2, 32>(h, 1, k, st);
       launch_wgrad_tc<C1, uint8_t, 32>(h, 0, d_states, k, st, &nsplit[0]);
     } else if (nat) {
-      launch_wgrad<NF, float>(h, 3, h->act[0][2], k, st, &nsplit[3]); launch_dgrad<NF>(h, 3, k, st);
-      launch_wgrad<N3, float>(h, 2, h->act[0][1], k, st, &nsplit[2]); launch_dgrad<N3>(h, 2, k, st);
-      launch_wgrad<N2, float>(h, 1, h->act[0][0], k, st, &nsplit[1]); launch_dgrad<N2>(h, 1, k, st);
+      launch_wgrad<NF, float>(h, 3, h->act[0][2], k, sd, &nsplit[3]); launch_dgrad<NF>(h, 3, k, st);
+      if (fork_after_dgrad(1)) return DQN_ERR_CUDA;
+      launch_wgrad<N3, float>(h, 2, h->act[0][1], k, sd, &nsplit[2]); launch_dgrad<N3>(h, 2, k, st);
+      if (fork_after_dgrad(2)) return DQN_ERR_CUDA;
+      launch_wgrad<N2, float>(h, 1, h->act[0][0], k, sd, &nsplit[1]); launch_dgrad<N2>(h, 1, k, st);
       if (u8) launch_wgrad<N1, uint8_t>(h, 0, d_states, k, st, &nsplit[0]);
       else launch_wgrad<N1, float>(h, 0, d_states, k, st, &nsplit[0]);
     } else {
-      launch_wgrad<F4, float>(h, 3, h->act[0][2], k, st, &nsplit[3]); launch_dgrad<F4>(h, 3, k, st);
-      launch_wgrad<C3, float>(h, 2, h->act[0][1], k, st, &nsplit[2]); launch_dgrad<C3>(h, 2, k, st);
-      launch_wgrad<C2, float>(h, 1, h->act[0][0], k, st, &nsplit[1]); launch_dgrad<C2>(h, 1, k, st);
+      launch_wgrad<F4, float>(h, 3, h->act[0][2], k, sd, &nsplit[3]); launch_dgrad<F4>(h, 3, k, st);
+      if (fork_after_dgrad(1)) return DQN_ERR_CUDA;
+      launch_wgrad<C3, float>(h, 2, h->act[0][1], k, sd, &nsplit[2]); launch_dgrad<C3>(h, 2, k, st);
+      if (fork_after_dgrad(2)) return DQN_ERR_CUDA;
+      launch_wgrad<C2, float>(h, 1, h->act[0][0], k, sd, &nsplit[1]); launch_dgrad<C2>(h, 1, k, st);
       if (u8) launch_wgrad<C1, uint8_t>(h, 0, d_states, k, st, &nsplit[0]);
       else launch_wgrad<C1, float>(h, 0, d_states, k, st, &nsplit[0]);
     }
+    // join
+    DQN_CUDA(cudaEventRecord(h->ev_join, sd));
+    DQN_CUDA(cudaStreamWaitEvent(st, h->ev_join, 0));
     DQN_CUDA(cudaGetLastError());
     fill_segs(h, &oa, nsplit, false);
     if (mode == 1) {

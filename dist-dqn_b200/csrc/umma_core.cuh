@@ -4,12 +4,15 @@
 // TF gradients of those ops); operands are bf16 (uint8 frames are exact in bf16), accumulation fp32.
 //
 // How a tile is computed
-//   * 128 threads gather the operands (im2col of NHWC activations, transposed weights, or the
-//     pool/ReLU-routed output gradient) as 16-byte chunks of 8 bf16 and store them into shared memory
-//     in the UMMA canonical NO-SWIZZLE layout: 8x16-byte core matrices; the chunk of (mn-index i,
-//     reduction-index r) lives at   K-major : (i/8)*1024 + (r/8)*128 + (i%8)*16      (forward, dgrad)
-//                                   MN-major: (i/8)*1024 + (r/8)*128 + (r%8)*16      (wgrad: both operands)
-//     so one 64-deep reduction stage is 1024 bytes per 8 mn-indices and UMMA_K=16 steps are 256 bytes apart.
+//   * 512 threads gather the operands (im2col of NHWC activations, transposed weights, or the pool-routed
+//     output gradient) as 16-byte chunks of 8 bf16.  Lanes run along the contiguous direction of global memory
+//     (8 lanes = one 128-byte run), so a warp touches a handful of lines instead of 32.
+//   * operands that need no arithmetic go straight into the UMMA SWIZZLE_128B K-major layout
+//     (row i at (i/8)*1024 + (i%8)*128, 16-byte chunk c at position c ^ (i%8)): forward A/B, dgrad B, fc dgrad A.
+//   * operands that need arithmetic (uint8 frames -> bf16, pool routing of gradients) or a transpose (wgrad, whose
+//     operands are MN-major) land in a padded raw ring and are rewritten shared->shared into the NO-SWIZZLE
+//     canonical layout (8x16-byte core matrices; K-major chunk (i,r/8) at (i/8)*1024 + (r/8)*128 + (i%8)*16,
+//     MN-major chunk (i/8, r) at (i/8)*1024 + (r/8)*128 + (r%8)*16).
 //   * the gather is asynchronous: every thread issues cp.async (16- or 8-byte, zero-filled outside the image)
 //     for stages i+1 and i+2 while stage i is consumed, into a 4-slot ring.  bf16 operands land directly in
 //     their canonical position; uint8 frames and pool-routed gradients land in a raw ring and are converted /
@@ -120,14 +123,23 @@ __device__ __forceinline__ uint32_t kmajor_off(int i, int rc) { return (uint32_t
 // byte offset of the 16-byte chunk (mn chunk g of 8, reduction index r) in an MN-major stage
 __device__ __forceinline__ uint32_t mnmajor_off(int g, int r) { return (uint32_t)(g * 1024 + (r >> 3) * 128 + (r & 7) * 16); }
 
-// issue the 4 MMAs of one stage (thread 0 only) and commit them to `bar`
+// SWIZZLE_128B K-major descriptor (layout_type 2; 8-row groups 1024 bytes apart; tile base 1024-byte aligned)
+__device__ __forceinline__ uint64_t make_desc_sw128(uint32_t saddr) {
+  return make_desc(saddr, 16, 1024) | ((uint64_t)2 << 61);
+}
+// byte offset of chunk c (8 reduction elements) of row i in a SWIZZLE_128B K-major stage
+__device__ __forceinline__ uint32_t sw128_off(int i, int c) { return (uint32_t)((i >> 3) * 1024 + (i & 7) * 128 + ((c ^ (i & 7)) << 4)); }
+
+// issue the 4 MMAs of one stage (thread 0 only) and commit them to `bar`.  *_SW: operand is in the swizzled
+// K-major layout (UMMA_K steps are 32 bytes apart) instead of the no-swizzle one (256 bytes apart).
+template <bool A_SW, bool B_SW>
 __device__ __forceinline__ void issue_stage(uint32_t tmem_d, uint32_t a_addr, uint32_t b_addr, uint32_t idesc, bool first,
                                             uint64_t* bar) {
   tc_fence_after();
 #pragma unroll
   for (int j = 0; j < TK / 16; ++j) {
-    const uint64_t ad = make_desc(a_addr + j * 256, 128, 1024);
-    const uint64_t bd = make_desc(b_addr + j * 256, 128, 1024);
+    const uint64_t ad = A_SW ? make_desc_sw128(a_addr + j * 32) : make_desc(a_addr + j * 256, 128, 1024);
+    const uint64_t bd = B_SW ? make_desc_sw128(b_addr + j * 32) : make_desc(b_addr + j * 256, 128, 1024);
     mma_bf16(tmem_d, ad, bd, idesc, (first && j == 0) ? 0u : 1u);
   }
   mma_commit(bar);
@@ -216,6 +228,12 @@ __device__ __forceinline__ void teardown(uint32_t tmem_base, uint32_t ncols) {
   if (threadIdx.x < 32) tmem_dealloc(tmem_base, ncols);
 }
 __host__ __device__ constexpr uint32_t tmem_cols(int n) { return n <= 32 ? 32u : (n <= 64 ? 64u : (n <= 128 ? 128u : 256u)); }
+// dynamic shared memory is re-based to a 1024-byte boundary inside the kernels (swizzled tiles need it)
+constexpr uint32_t SMEM_SLACK = 1024;
+__device__ __forceinline__ uint8_t* align_smem(uint8_t* p) {
+  const uint32_t a = smem_u32(p);
+  return p + (((a + 1023u) & ~1023u) - a);
+}
 
 // ------------------------------------------------------------------------------------------------ forward
 struct FwdPassT {
@@ -231,19 +249,21 @@ struct FwdArgsT {
   int B;
 };
 
+constexpr uint32_t FWD_RAW_PITCH = 80;                       // 64 uint8 of one tile row + pad (keeps 16-byte alignment)
+constexpr uint32_t FWD_RAW_A = 128 * FWD_RAW_PITCH;          // 10 KB
 template <typename TIn, int NTILE>
 __host__ __device__ constexpr uint32_t fwd_smem_bytes() {
-  return (sizeof(TIn) == 1 ? RS * 8192u + 2u * A_STAGE_BYTES : RS * A_STAGE_BYTES) + RS * (uint32_t)NTILE * 128u;
+  return SMEM_SLACK + (sizeof(TIn) == 1 ? RS * FWD_RAW_A + 2u * A_STAGE_BYTES : RS * A_STAGE_BYTES) + RS * (uint32_t)NTILE * 128u;
 }
 
 template <class G, typename TIn, int NTILE>
 __global__ void __launch_bounds__(TT) umma_fwd_kernel(FwdArgsT a) {
-  extern __shared__ __align__(1024) uint8_t smem[];
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align_smem(smem_raw);
   constexpr bool U8 = sizeof(TIn) == 1;
   constexpr uint32_t B_STAGE = NTILE * 128;
-  constexpr uint32_t RAW_A = 8192;                                   // 128 rows x 64 uint8
-  constexpr uint32_t OFF_OPA = U8 ? RS * RAW_A : 0;                  // converted A tiles (uint8 input only), 2 slots
-  constexpr uint32_t OFF_B = U8 ? RS * RAW_A + 2 * A_STAGE_BYTES : RS * A_STAGE_BYTES;
+  constexpr uint32_t OFF_OPA = U8 ? RS * FWD_RAW_A : 0;              // converted A tiles (uint8 input only), 2 slots
+  constexpr uint32_t OFF_B = U8 ? RS * FWD_RAW_A + 2 * A_STAGE_BYTES : RS * A_STAGE_BYTES;
   __shared__ uint64_t bars[2];
   __shared__ uint32_t tmem_slot;
   __shared__ float bias_sm[NTILE];
@@ -254,8 +274,11 @@ __global__ void __launch_bounds__(TT) umma_fwd_kernel(FwdArgsT a) {
   for (int j = tid; j < NTILE; j += TT) bias_sm[j] = __ldg(P.bias + n0 + j);
   const uint32_t tmem = setup(bars, &tmem_slot, tmem_cols(NTILE));
   const uint32_t sbase = smem_u32(smem);
-  const int arow = tid & (TM - 1), ac0 = (tid >> 7) * 2;   // this thread gathers chunks ac0, ac0+1 of tile row arow
-  const Row row = decode_row<G>(m0 + arow, a.B);
+  // gather mapping (lanes along the contiguous k direction): chunk id = tid + 512*q -> row id>>3, chunk id&7
+  const Row grow0 = decode_row<G>(m0 + (tid >> 3), a.B), grow1 = decode_row<G>(m0 + 64 + (tid >> 3), a.B);
+  const int gc = tid & 7;
+  // convert / epilogue mapping: tile row tid&127
+  const int arow = tid & (TM - 1), ac0 = (tid >> 7) * 2;
   constexpr int T = (G::K + TK - 1) / TK;
   constexpr int BCH = (NTILE * 8 + TT - 1) / TT;      // weight chunks per thread per stage
   constexpr uint32_t idesc = make_idesc(TM, NTILE, false, false);
@@ -263,18 +286,18 @@ __global__ void __launch_bounds__(TT) umma_fwd_kernel(FwdArgsT a) {
     if (it < T) {
       const int slot = it & (RS - 1);
 #pragma unroll
-      for (int cc = 0; cc < 2; ++cc) {
-        const int c = ac0 + cc;
-        const TIn* src = x_chunk_ptr<G, TIn>(x, row, it * 8 + c);
-        if constexpr (U8) cp_async8(sbase + slot * RAW_A + arow * 64 + c * 8, src ? src : x, src != nullptr);
-        else cp_async16(sbase + slot * A_STAGE_BYTES + kmajor_off(arow, c), src ? src : x, src != nullptr);
+      for (int q = 0; q < 2; ++q) {
+        const int r = (tid >> 3) + 64 * q;
+        const TIn* src = x_chunk_ptr<G, TIn>(x, q ? grow1 : grow0, it * 8 + gc);
+        if constexpr (U8) cp_async8(sbase + slot * FWD_RAW_A + r * FWD_RAW_PITCH + gc * 8, src ? src : x, src != nullptr);
+        else cp_async16(sbase + slot * A_STAGE_BYTES + sw128_off(r, gc), src ? src : x, src != nullptr);
       }
 #pragma unroll
       for (int q = 0; q < BCH; ++q) {
         const int ch = tid + TT * q, n = ch >> 3, kc = ch & 7;
         const int k = it * TK + kc * 8;
         if (ch < NTILE * 8)
-          cp_async16(sbase + OFF_B + slot * B_STAGE + kmajor_off(n, kc), P.wt + (size_t)(n0 + n) * G::K + (k < G::K ? k : 0),
+          cp_async16(sbase + OFF_B + slot * B_STAGE + sw128_off(n, kc), P.wt + (size_t)(n0 + n) * G::K + (k < G::K ? k : 0),
                      k < G::K);
       }
     }
@@ -289,8 +312,9 @@ __global__ void __launch_bounds__(TT) umma_fwd_kernel(FwdArgsT a) {
     cp_async_wait<2>();                                         // this thread's copies for stage `it` have landed
     uint32_t a_addr;
     if constexpr (U8) {
+      __syncthreads();                                          // ... and everybody else's
       uint8_t* opa = smem + OFF_OPA + par * A_STAGE_BYTES;
-      const uint4 u = *reinterpret_cast<const uint4*>(smem + slot * RAW_A + arow * 64 + ac0 * 8);   // this thread's 2 chunks
+      const uint4 u = *reinterpret_cast<const uint4*>(smem + slot * FWD_RAW_A + arow * FWD_RAW_PITCH + ac0 * 8);
       *reinterpret_cast<uint4*>(opa + kmajor_off(arow, ac0)) = cvt_u8x8(make_uint2(u.x, u.y));
       *reinterpret_cast<uint4*>(opa + kmajor_off(arow, ac0 + 1)) = cvt_u8x8(make_uint2(u.z, u.w));
       a_addr = sbase + OFF_OPA + par * A_STAGE_BYTES;
@@ -299,11 +323,12 @@ __global__ void __launch_bounds__(TT) umma_fwd_kernel(FwdArgsT a) {
     }
     fence_async_proxy();
     __syncthreads();
-    if (tid == 0) issue_stage(tmem, a_addr, sbase + OFF_B + slot * B_STAGE, idesc, it == 0, &bars[par]);
+    if (tid == 0) issue_stage<!U8, true>(tmem, a_addr, sbase + OFF_B + slot * B_STAGE, idesc, it == 0, &bars[par]);
   }
   // the last commit covers every MMA issued before it
   mbar_wait(&bars[(T - 1) & 1], ((T - 1) >> 1) & 1);
   tc_fence_after();
+  const Row row = decode_row<G>(m0 + arow, a.B);
   const int warp = tid >> 5, lane = tid & 31;
   const uint32_t trow = tmem + ((uint32_t)((warp & 3) * 32) << 16);    // tile row = arow (same for warps w and w+4k)
   const bool row_in = row.valid;
@@ -369,6 +394,8 @@ __global__ void __launch_bounds__(TT) umma_fwd_kernel(FwdArgsT a) {
 // ------------------------------------------------------------------------------------------------ weight gradient
 // dactg is the gradient w.r.t. the layer's pooled output, ALREADY multiplied by the ReLU gate (act > 0) by the
 // kernel that produced it (td_head / umma_dgrad); only the pool routing (arg-max == window position) remains.
+// Both operands are MN-major (the reduction runs over output pixels), so both go through a raw ring and are
+// transposed into the no-swizzle MN-major layout shared->shared.
 struct WgradArgsT {
   const void* x;                  // layer input: uint8 stacks (conv1) or bf16 activations
   const __nv_bfloat16* dactg;
@@ -378,26 +405,30 @@ struct WgradArgsT {
   int rows_per_split;             // multiple of TK
 };
 
+template <typename TIn>
+__host__ __device__ constexpr uint32_t wg_a_pitch() { return sizeof(TIn) == 1 ? 144u : 272u; }   // 16 chunks of 8 / 16 bytes + pad
+template <int NTILE>
+__host__ __device__ constexpr uint32_t wg_bd_pitch() { return (uint32_t)NTILE * 2u + 16u; }       // gradient row + pad
+template <int NTILE>
+__host__ __device__ constexpr uint32_t wg_ba_pitch() { return (uint32_t)NTILE + 8u; }             // arg-max row + pad
+__host__ __device__ constexpr uint32_t round1k(uint32_t v) { return (v + 1023u) & ~1023u; }
 template <class G, typename TIn, int NTILE>
 __host__ __device__ constexpr uint32_t wgrad_smem_bytes() {
-  constexpr uint32_t a = sizeof(TIn) == 1 ? RS * 8192u + 2u * A_STAGE_BYTES : RS * A_STAGE_BYTES;
-  constexpr uint32_t nchunk = 64u * (uint32_t)NTILE / 8u;                 // dZ chunks per stage
-  constexpr uint32_t b = G::POOL ? RS * nchunk * 24u + 2u * (uint32_t)NTILE * 128u : RS * (uint32_t)NTILE * 128u;
-  return a + b;
+  return SMEM_SLACK + RS * round1k(64u * wg_a_pitch<TIn>()) + RS * round1k(64u * wg_bd_pitch<NTILE>()) +
+         (G::POOL ? RS * round1k(64u * wg_ba_pitch<NTILE>()) : 0u) + 2u * A_STAGE_BYTES + 2u * (uint32_t)NTILE * 128u;
 }
 
 template <class G, typename TIn, int NTILE>
 __global__ void __launch_bounds__(TT) umma_wgrad_kernel(WgradArgsT a) {
-  extern __shared__ __align__(1024) uint8_t smem[];
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align_smem(smem_raw);
   constexpr bool U8 = sizeof(TIn) == 1;
   constexpr uint32_t B_STAGE = NTILE * 128;
-  constexpr uint32_t RAW_A = 8192;                                   // 64 rows x 128 uint8
-  constexpr uint32_t OFF_OPA = U8 ? RS * RAW_A : 0;
-  constexpr uint32_t OFF_B = U8 ? RS * RAW_A + 2 * A_STAGE_BYTES : RS * A_STAGE_BYTES;
-  constexpr uint32_t NCH = 64 * NTILE / 8;                           // dZ chunks per stage
-  constexpr uint32_t RAW_BD = NCH * 16, RAW_BA = NCH * 8;            // raw gradient / raw arg-max per stage
-  constexpr uint32_t OFF_RAWA2 = OFF_B + RS * RAW_BD;                // (POOL) arg ring
-  constexpr uint32_t OFF_OPB = OFF_RAWA2 + RS * RAW_BA;              // (POOL) routed B tiles, 2 slots
+  constexpr uint32_t PA = wg_a_pitch<TIn>(), PBD = wg_bd_pitch<NTILE>(), PBA = wg_ba_pitch<NTILE>();
+  constexpr uint32_t RAW_A = round1k(64 * PA), RAW_BD = round1k(64 * PBD), RAW_BA = G::POOL ? round1k(64 * PBA) : 0;
+  constexpr uint32_t OFF_RBD = RS * RAW_A, OFF_RBA = OFF_RBD + RS * RAW_BD, OFF_OPA = OFF_RBA + RS * RAW_BA;
+  constexpr uint32_t OFF_OPB = OFF_OPA + 2 * A_STAGE_BYTES;
+  constexpr int ACB = U8 ? 8 : 16;                                   // bytes of one A chunk in the raw ring
   __shared__ uint64_t bars[2];
   __shared__ uint32_t tmem_slot;
   __shared__ float bias_sm[NTILE];
@@ -413,42 +444,41 @@ __global__ void __launch_bounds__(TT) umma_wgrad_kernel(WgradArgsT a) {
   const int T = (r_end - r_begin + TK - 1) / TK;
   const bool do_bias = blockIdx.x == 0;
   constexpr uint32_t idesc = make_idesc(TM, NTILE, true, true);
-  // A: 64 rows x 16 chunks (8 k each) per stage -> 2 per thread (row am, chunks ag0, ag0+1)
-  // B: 64 rows x NTILE/8 chunks (chunk id = tid + TT*q: row id/GPR, column chunk bg = tid%GPR)
-  constexpr int BCH = (64 * NTILE / 8 + TT - 1) / TT;
+  // gather mapping (lanes along contiguous memory): A chunk id = tid + 512*q -> reduction row id>>4, k-chunk id&15;
+  //                                                  B chunk id = tid + 512*q -> reduction row id/GPR, n-chunk id%GPR
+  // transpose mapping (lanes along the reduction row, conflict-free stores): row tid&63, chunks (tid>>6)*CPT ..
   constexpr int GPR = NTILE / 8;
-  constexpr int NCHB = 64 * NTILE / 8;
-  const int am = tid & 63, ag0 = (tid >> 6) * 2;      // A chunks ag0, ag0+1 of reduction row am
-  const int bg = tid % GPR;
-  float colsum[8];
+  constexpr int NCHB = 64 * GPR;
+  constexpr int BQ = (NCHB + TT - 1) / TT;
+  constexpr int CPT = GPR / 8 > 0 ? GPR / 8 : 1;                     // B chunks per transposing thread (GPR=4: half the threads idle)
+  const int tr = tid & 63, tg = tid >> 6;
+  float colsum[CPT][8];
 #pragma unroll
-  for (int e = 0; e < 8; ++e) colsum[e] = 0.f;
+  for (int q = 0; q < CPT; ++q)
+#pragma unroll
+    for (int e = 0; e < 8; ++e) colsum[q][e] = 0.f;
   auto issue = [&](int it) {
     if (it < T) {
       const int slot = it & (RS - 1);
       const int rbase = r_begin + it * TK;
-      const Row ar = decode_row<G>(rbase + am, a.B);
-      const bool arow_ok = (rbase + am) < r_end;
 #pragma unroll
       for (int q = 0; q < 2; ++q) {
-        const int g = ag0 + q;
-        const TIn* src = arow_ok ? x_chunk_ptr<G, TIn>(x, ar, (i0 >> 3) + g) : nullptr;
-        if constexpr (U8) cp_async8(sbase + slot * RAW_A + (am * 16 + g) * 8, src ? src : x, src != nullptr);
-        else cp_async16(sbase + slot * A_STAGE_BYTES + mnmajor_off(g, am), src ? src : x, src != nullptr);
+        const int id = tid + TT * q, rr = id >> 4, g = id & 15;
+        const Row ar = decode_row<G>(rbase + rr, a.B);
+        const TIn* src = (rbase + rr) < r_end ? x_chunk_ptr<G, TIn>(x, ar, (i0 >> 3) + g) : nullptr;
+        const uint32_t dst = sbase + slot * RAW_A + rr * PA + g * ACB;
+        if constexpr (U8) cp_async8(dst, src ? src : x, src != nullptr);
+        else cp_async16(dst, src ? src : x, src != nullptr);
       }
 #pragma unroll
-      for (int q = 0; q < BCH; ++q) {
-        const int id = tid + TT * q, rr = id / GPR;
+      for (int q = 0; q < BQ; ++q) {
+        const int id = tid + TT * q, rr = id / GPR, g = id % GPR;
         if (id >= NCHB) break;
         const Row br = decode_row<G>(rbase + rr, a.B);
         const bool ok = br.valid && (rbase + rr) < r_end;
-        const size_t off = (size_t)(ok ? br.pidx : 0) * G::COUT + n0 + bg * 8;
-        if constexpr (G::POOL) {
-          cp_async16(sbase + OFF_B + slot * RAW_BD + id * 16, a.dactg + off, ok);
-          cp_async8(sbase + OFF_RAWA2 + slot * RAW_BA + id * 8, a.arg + off, ok);
-        } else {
-          cp_async16(sbase + OFF_B + slot * B_STAGE + mnmajor_off(bg, rr), a.dactg + off, ok);
-        }
+        const size_t off = (size_t)(ok ? br.pidx : 0) * G::COUT + n0 + g * 8;
+        cp_async16(sbase + OFF_RBD + slot * RAW_BD + rr * PBD + g * 16, a.dactg + off, ok);
+        if constexpr (G::POOL) cp_async8(sbase + OFF_RBA + slot * RAW_BA + rr * PBA + g * 8, a.arg + off, ok);
       }
     }
     cp_async_commit();
@@ -460,45 +490,37 @@ __global__ void __launch_bounds__(TT) umma_wgrad_kernel(WgradArgsT a) {
     if (it >= 2) mbar_wait(&bars[par], ((it >> 1) - 1) & 1);
     issue(it + 2);
     cp_async_wait<2>();
-    uint32_t a_addr, b_addr;
-    if constexpr (U8) {
-      uint8_t* opa = smem + OFF_OPA + par * A_STAGE_BYTES;
-      const uint4 u = *reinterpret_cast<const uint4*>(smem + slot * RAW_A + (am * 16 + ag0) * 8);   // this thread's 2 chunks
-      *reinterpret_cast<uint4*>(opa + mnmajor_off(ag0, am)) = cvt_u8x8(make_uint2(u.x, u.y));
-      *reinterpret_cast<uint4*>(opa + mnmajor_off(ag0 + 1, am)) = cvt_u8x8(make_uint2(u.z, u.w));
-      a_addr = sbase + OFF_OPA + par * A_STAGE_BYTES;
-    } else {
-      a_addr = sbase + slot * A_STAGE_BYTES;
+    __syncthreads();
+    uint8_t* opa = smem + OFF_OPA + par * A_STAGE_BYTES;
+    uint8_t* opb = smem + OFF_OPB + par * B_STAGE;
+    {   // A: k-chunks 2*tg, 2*tg+1 of reduction row tr
+      const uint8_t* src = smem + slot * RAW_A + tr * PA + (2 * tg) * ACB;
+      if constexpr (U8) {
+        const uint4 u = *reinterpret_cast<const uint4*>(src);
+        *reinterpret_cast<uint4*>(opa + mnmajor_off(2 * tg, tr)) = cvt_u8x8(make_uint2(u.x, u.y));
+        *reinterpret_cast<uint4*>(opa + mnmajor_off(2 * tg + 1, tr)) = cvt_u8x8(make_uint2(u.z, u.w));
+      } else {
+        *reinterpret_cast<uint4*>(opa + mnmajor_off(2 * tg, tr)) = *reinterpret_cast<const uint4*>(src);
+        *reinterpret_cast<uint4*>(opa + mnmajor_off(2 * tg + 1, tr)) = *reinterpret_cast<const uint4*>(src + 16);
+      }
     }
-    if constexpr (G::POOL) {
-      uint8_t* opb = smem + OFF_OPB + par * B_STAGE;
-      const int rbase = r_begin + it * TK;
+    if (tg * CPT < GPR) {   // B: n-chunks tg*CPT .. of reduction row tr
+      const int win = (r_begin + it * TK + tr) & 3;                     // pool-window position of this row
 #pragma unroll
-      for (int q = 0; q < BCH; ++q) {
-        const int id = tid + TT * q, rr = id / GPR;
-        if (id >= NCHB) break;
-        const int win = (rbase + rr) & 3;                               // pool-window position of this row
-        const uint4 d = *reinterpret_cast<const uint4*>(smem + OFF_B + slot * RAW_BD + id * 16);
-        const uint2 ag = *reinterpret_cast<const uint2*>(smem + OFF_RAWA2 + slot * RAW_BA + id * 8);
-        const uint4 z = route_chunk(d, ag, win);
-        *reinterpret_cast<uint4*>(opb + mnmajor_off(bg, rr)) = z;
-        if (do_bias) add_chunk(colsum, z);
+      for (int q = 0; q < CPT; ++q) {
+        const int g = tg * CPT + q;
+        uint4 z = *reinterpret_cast<const uint4*>(smem + OFF_RBD + slot * RAW_BD + tr * PBD + g * 16);
+        if constexpr (G::POOL)
+          z = route_chunk(z, *reinterpret_cast<const uint2*>(smem + OFF_RBA + slot * RAW_BA + tr * PBA + g * 8), win);
+        *reinterpret_cast<uint4*>(opb + mnmajor_off(g, tr)) = z;
+        if (do_bias) add_chunk(colsum[q], z);
       }
-      b_addr = sbase + OFF_OPB + par * B_STAGE;
-    } else {
-      if (do_bias) {
-#pragma unroll
-        for (int q = 0; q < BCH; ++q) {
-          const int id = tid + TT * q, rr = id / GPR;
-          if (id >= NCHB) break;
-          add_chunk(colsum, *reinterpret_cast<const uint4*>(smem + OFF_B + slot * B_STAGE + mnmajor_off(bg, rr)));
-        }
-      }
-      b_addr = sbase + OFF_B + slot * B_STAGE;
     }
     fence_async_proxy();
     __syncthreads();
-    if (tid == 0) issue_stage(tmem, a_addr, b_addr, idesc, it == 0, &bars[par]);
+    if (tid == 0)
+      issue_stage<false, false>(tmem, sbase + OFF_OPA + par * A_STAGE_BYTES, sbase + OFF_OPB + par * B_STAGE, idesc, it == 0,
+                                &bars[par]);
   }
   float* out = a.partial + (size_t)blockIdx.z * ((size_t)(G::K + 1) * G::COUT);
   const int warp = tid >> 5, lane = tid & 31;
@@ -522,9 +544,17 @@ __global__ void __launch_bounds__(TT) umma_wgrad_kernel(WgradArgsT a) {
     for (int c = 0; c < NTILE; ++c) out[(size_t)k * G::COUT + n0 + c] = 0.f;
   }
   if (do_bias) {
-    if (tid < NCHB) {
+    // lanes of a warp hold the same columns (same tg) for different reduction rows: reduce in the warp first
+    if (tg * CPT < GPR) {
 #pragma unroll
-      for (int e = 0; e < 8; ++e) atomicAdd(&bias_sm[bg * 8 + e], colsum[e]);
+      for (int q = 0; q < CPT; ++q)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          float v = colsum[q][e];
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+          if (lane == 0) atomicAdd(&bias_sm[(tg * CPT + q) * 8 + e], v);
+        }
     }
     __syncthreads();
     for (int j = tid; j < NTILE; j += TT) out[(size_t)G::K * G::COUT + n0 + j] = bias_sm[j];
@@ -542,21 +572,23 @@ struct DgradArgsT {
   int B;
 };
 
+constexpr uint32_t DG_PD = 144, DG_PA = 72;                          // raw gradient / arg-max row pitches (8 chunks + pad)
+constexpr uint32_t DG_RAW_D = 128 * DG_PD, DG_RAW_A = 128 * DG_PA, DG_RAW_W = 1024;   // 18 KB, 9 KB, 1 KB
 template <class G, int NTILE>
 __host__ __device__ constexpr uint32_t dgrad_smem_bytes() {
-  constexpr uint32_t a = G::POOL ? RS * (1024u * 16u + 1024u * 8u + 1024u) + 2u * A_STAGE_BYTES : RS * A_STAGE_BYTES;
-  return a + RS * (uint32_t)NTILE * 128u;
+  return SMEM_SLACK + (G::POOL ? RS * (DG_RAW_D + DG_RAW_A + DG_RAW_W) + 2u * A_STAGE_BYTES : RS * A_STAGE_BYTES) +
+         RS * (uint32_t)NTILE * 128u;
 }
 
 template <class G, int NTILE>
 __global__ void __launch_bounds__(TT) umma_dgrad_kernel(DgradArgsT a) {
-  extern __shared__ __align__(1024) uint8_t smem[];
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align_smem(smem_raw);
   constexpr uint32_t B_STAGE = NTILE * 128;
   constexpr int KD = G::KS * G::KS * G::COUT;
   constexpr int CC = G::COUT / 8;                     // chunks per filter tap
   // POOL: raw rings (gradient chunks, arg-max chunks, window byte per chunk) + 2 routed A tiles; else direct A ring
-  constexpr uint32_t RAW_D = 1024 * 16, RAW_G = 1024 * 8, RAW_W = 1024;
-  constexpr uint32_t OFF_RG = RS * RAW_D, OFF_RW = OFF_RG + RS * RAW_G, OFF_OPA = OFF_RW + RS * RAW_W;
+  constexpr uint32_t OFF_RG = RS * DG_RAW_D, OFF_RW = OFF_RG + RS * DG_RAW_A, OFF_OPA = OFF_RW + RS * DG_RAW_W;
   constexpr uint32_t OFF_B = G::POOL ? OFF_OPA + 2 * A_STAGE_BYTES : RS * A_STAGE_BYTES;
   __shared__ uint64_t bars[2];
   __shared__ uint32_t tmem_slot;
@@ -565,11 +597,22 @@ __global__ void __launch_bounds__(TT) umma_dgrad_kernel(DgradArgsT a) {
   const uint32_t tmem = setup(bars, &tmem_slot, tmem_cols(NTILE));
   const uint32_t sbase = smem_u32(smem);
   const int M = a.B * G::IH * G::IW;
-  const int arow = tid & (TM - 1), ac0 = (tid >> 7) * 2;   // chunks ac0, ac0+1 of tile row arow
+  // gather mapping: chunk id = tid + 512*q -> tile row id>>3, reduction chunk id&7 (8 lanes = 128 contiguous bytes)
+  const int gc = tid & 7;
+  int gb[2], giy[2], gix[2];
+  bool gvalid[2];
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    const int mm = m0 + (tid >> 3) + 64 * q;
+    gb[q] = mm / (G::IH * G::IW);
+    const int rem = mm - gb[q] * (G::IH * G::IW);
+    giy[q] = rem / G::IW;
+    gix[q] = rem - giy[q] * G::IW;
+    gvalid[q] = mm < M;
+  }
+  // route / epilogue mapping: tile row tid&127
+  const int arow = tid & (TM - 1), ac0 = (tid >> 7) * 2;
   const int m = m0 + arow;
-  const int b = m / (G::IH * G::IW);
-  const int rem = m - b * (G::IH * G::IW);
-  const int iy = rem / G::IW, ix = rem - iy * G::IW;
   const bool mvalid = m < M;
   constexpr int T = KD / TK;
   static_assert(KD % TK == 0, "dgrad reduction must be a multiple of the stage depth");
@@ -578,39 +621,39 @@ __global__ void __launch_bounds__(TT) umma_dgrad_kernel(DgradArgsT a) {
   auto issue = [&](int it) {
     if (it < T) {
       const int slot = it & (RS - 1);
+      const int kc8 = it * 8 + gc;
+      const int nq = kc8 % CC, t = kc8 / CC;
+      const int kx = t % G::KS, ky = t / G::KS;
 #pragma unroll
-      for (int cc = 0; cc < 2; ++cc) {
-        const int c = ac0 + cc;
-        const int kc8 = it * 8 + c;
-        const int nq = kc8 % CC, t = kc8 / CC;
-        const int kx = t % G::KS, ky = t / G::KS;
-        const int ty = iy + G::PADH - ky, tx = ix + G::PADW - kx;
-        bool ok = mvalid && ty >= 0 && tx >= 0 && (ty % G::ST) == 0 && (tx % G::ST) == 0;
+      for (int q = 0; q < 2; ++q) {
+        const int r = (tid >> 3) + 64 * q;
+        const int ty = giy[q] + G::PADH - ky, tx = gix[q] + G::PADW - kx;
+        bool ok = gvalid[q] && ty >= 0 && tx >= 0 && (ty % G::ST) == 0 && (tx % G::ST) == 0;
         const int oy = ty / G::ST, ox = tx / G::ST;
         ok = ok && oy < G::OH && ox < G::OW;
         int pidx = 0, win = 0;
         if (ok) {
           if constexpr (G::POOL) {
-            pidx = (b * G::PH + (oy >> 1)) * G::PW + (ox >> 1);
+            pidx = (gb[q] * G::PH + (oy >> 1)) * G::PW + (ox >> 1);
             win = (oy & 1) * 2 + (ox & 1);
           } else {
-            pidx = (b * G::OH + oy) * G::OW + ox;
+            pidx = (gb[q] * G::OH + oy) * G::OW + ox;
           }
         }
         const size_t off = (size_t)pidx * G::COUT + nq * 8;
         if constexpr (G::POOL) {
-          cp_async16(sbase + slot * RAW_D + (arow * 8 + c) * 16, a.dactg + off, ok);
-          cp_async8(sbase + OFF_RG + slot * RAW_G + (arow * 8 + c) * 8, a.arg + off, ok);
-          smem[OFF_RW + slot * RAW_W + arow * 8 + c] = (uint8_t)win;
+          cp_async16(sbase + slot * DG_RAW_D + r * DG_PD + gc * 16, a.dactg + off, ok);
+          cp_async8(sbase + OFF_RG + slot * DG_RAW_A + r * DG_PA + gc * 8, a.arg + off, ok);
+          smem[OFF_RW + slot * DG_RAW_W + r * 8 + gc] = (uint8_t)win;
         } else {
-          cp_async16(sbase + slot * A_STAGE_BYTES + kmajor_off(arow, c), a.dactg + off, ok);
+          cp_async16(sbase + slot * A_STAGE_BYTES + sw128_off(r, gc), a.dactg + off, ok);
         }
       }
 #pragma unroll
       for (int q = 0; q < BCH; ++q) {
         const int ch = tid + TT * q, n = ch >> 3, kc = ch & 7;
         if (ch < NTILE * 8)
-          cp_async16(sbase + OFF_B + slot * B_STAGE + kmajor_off(n, kc), a.wd + (size_t)(c0t + n) * KD + it * TK + kc * 8, true);
+          cp_async16(sbase + OFF_B + slot * B_STAGE + sw128_off(n, kc), a.wd + (size_t)(c0t + n) * KD + it * TK + kc * 8, true);
       }
     }
     cp_async_commit();
@@ -624,13 +667,14 @@ __global__ void __launch_bounds__(TT) umma_dgrad_kernel(DgradArgsT a) {
     cp_async_wait<2>();
     uint32_t a_addr;
     if constexpr (G::POOL) {
+      __syncthreads();
       uint8_t* opa = smem + OFF_OPA + par * A_STAGE_BYTES;
 #pragma unroll
       for (int cc = 0; cc < 2; ++cc) {
         const int c = ac0 + cc;
-        const uint4 d = *reinterpret_cast<const uint4*>(smem + slot * RAW_D + (arow * 8 + c) * 16);
-        const uint2 ag = *reinterpret_cast<const uint2*>(smem + OFF_RG + slot * RAW_G + (arow * 8 + c) * 8);
-        const int win = (int)smem[OFF_RW + slot * RAW_W + arow * 8 + c];
+        const uint4 d = *reinterpret_cast<const uint4*>(smem + slot * DG_RAW_D + arow * DG_PD + c * 16);
+        const uint2 ag = *reinterpret_cast<const uint2*>(smem + OFF_RG + slot * DG_RAW_A + arow * DG_PA + c * 8);
+        const int win = (int)smem[OFF_RW + slot * DG_RAW_W + arow * 8 + c];
         *reinterpret_cast<uint4*>(opa + kmajor_off(arow, c)) = route_chunk(d, ag, win);
       }
       a_addr = sbase + OFF_OPA + par * A_STAGE_BYTES;
@@ -639,7 +683,7 @@ __global__ void __launch_bounds__(TT) umma_dgrad_kernel(DgradArgsT a) {
     }
     fence_async_proxy();
     __syncthreads();
-    if (tid == 0) issue_stage(tmem, a_addr, sbase + OFF_B + slot * B_STAGE, idesc, it == 0, &bars[par]);
+    if (tid == 0) issue_stage<!G::POOL, true>(tmem, a_addr, sbase + OFF_B + slot * B_STAGE, idesc, it == 0, &bars[par]);
   }
   mbar_wait(&bars[(T - 1) & 1], ((T - 1) >> 1) & 1);
   tc_fence_after();
