@@ -59,27 +59,37 @@ __device__ __forceinline__ void td_terms(float q_sel, float maxq, double reward,
   }
 }
 
-// One warp per sample.
+// One warp per sample; lane l owns hidden units l, l+32, ... (FPL per lane, kept in registers so every load of the
+// head weights is independent of the reductions).
+template <int FPL>
 __global__ void __launch_bounds__(256)
 td_head_kernel(const float* __restrict__ h_on, const float* __restrict__ h_tg, const float* __restrict__ w_on,
                const float* __restrict__ b_on, const float* __restrict__ w_tg, const float* __restrict__ b_tg,
                const int32_t* __restrict__ actions, const double* __restrict__ rewards,
-               const uint8_t* __restrict__ terminals, int B, int F, int A, double gamma, int loss_kind,
+               const uint8_t* __restrict__ terminals, int B, int A, double gamma, int loss_kind,
                float* __restrict__ qout, float* __restrict__ se, float* __restrict__ g, float* __restrict__ dh,
                __nv_bfloat16* __restrict__ dh_bf, long long* __restrict__ step) {
+  constexpr int F = FPL * 32;
   const int lane = threadIdx.x & 31;
   const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (blockIdx.x == 0 && threadIdx.x == 0) *step += 1;      // global_step (network.py:83, 198-202)
   if (b >= B) return;
-  const float* x = h_on + (size_t)b * F;
-  const float* xt = h_tg + (size_t)b * F;
+  float x[FPL], xt[FPL];
+#pragma unroll
+  for (int i = 0; i < FPL; ++i) {
+    x[i] = h_on[(size_t)b * F + lane + 32 * i];
+    xt[i] = h_tg[(size_t)b * F + lane + 32 * i];
+  }
   const int act = actions[b];
+  const double reward = rewards[b];
+  const bool terminal = terminals[b] != 0;
   float q_sel = 0.f, maxq = 0.f;
   for (int a = 0; a < A; ++a) {
     float s = 0.f, st = 0.f;
-    for (int j = lane; j < F; j += 32) {
-      s = fmaf(x[j], w_on[j * A + a], s);
-      st = fmaf(xt[j], w_tg[j * A + a], st);
+#pragma unroll
+    for (int i = 0; i < FPL; ++i) {
+      s = fmaf(x[i], __ldg(w_on + (lane + 32 * i) * A + a), s);
+      st = fmaf(xt[i], __ldg(w_tg + (lane + 32 * i) * A + a), st);
     }
     s = warp_sum(s) + b_on[a];
     st = warp_sum(st) + b_tg[a];
@@ -88,12 +98,14 @@ td_head_kernel(const float* __restrict__ h_on, const float* __restrict__ h_tg, c
     if (a == act) q_sel = s;
   }
   float e, gg;
-  td_terms(q_sel, maxq, rewards[b], terminals[b] != 0, gamma, B, loss_kind, &e, &gg);
+  td_terms(q_sel, maxq, reward, terminal, gamma, B, loss_kind, &e, &gg);
   if (lane == 0) { se[b] = e; g[b] = gg; }
-  for (int j = lane; j < F; j += 32) {
-    const float d = gg * w_on[j * A + act];
+#pragma unroll
+  for (int i = 0; i < FPL; ++i) {
+    const int j = lane + 32 * i;
+    const float d = gg * __ldg(w_on + j * A + act);
     dh[(size_t)b * F + j] = d;
-    if (dh_bf) dh_bf[(size_t)b * F + j] = __float2bfloat16_rn(x[j] > 0.f ? d : 0.f);   // ReLU-gated for the tensor-core path
+    if (dh_bf) dh_bf[(size_t)b * F + j] = __float2bfloat16_rn(x[i] > 0.f ? d : 0.f);   // ReLU-gated for the tensor-core path
   }
 }
 
@@ -104,13 +116,18 @@ head_wgrad_kernel(const float* __restrict__ h_on, const float* __restrict__ g, c
   const int o = blockIdx.x * blockDim.x + threadIdx.x;
   if (o >= (F + 1) * A) return;
   const int j = o / A, a = o - j * A;
-  float s = 0.f;
-  if (j < F) {
-    for (int b = 0; b < B; ++b) s += (actions[b] == a) ? h_on[(size_t)b * F + j] * g[b] : 0.f;
-  } else {
-    for (int b = 0; b < B; ++b) s += (actions[b] == a) ? g[b] : 0.f;
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};      // 4 independent chains; summed in a fixed order
+  const int jj = j < F ? j : 0;
+  int b = 0;
+  for (; b + 4 <= B; b += 4) {
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const float hv = j < F ? h_on[(size_t)(b + u) * F + jj] : 1.f;
+      acc[u] += (actions[b + u] == a) ? hv * g[b + u] : 0.f;
+    }
   }
-  out[o] = s;
+  for (; b < B; ++b) acc[0] += (actions[b] == a) ? (j < F ? h_on[(size_t)b * F + jj] : 1.f) * g[b] : 0.f;
+  out[o] = (acc[0] + acc[1]) + (acc[2] + acc[3]);
 }
 
 // Predict path (dqn_agent.py:176-189, 159-160): q = h @ w + b, optional row-wise arg-max (first maximum).
@@ -145,6 +162,10 @@ struct Seg {
   const float* partial;   // [nsplit][stride]
   int nsplit;
   long long stride;
+  // bf16 tensor-core mode: operand copies of the weight part, refreshed by the update itself
+  __nv_bfloat16* wt;      // [N][K]            (forward)
+  __nv_bfloat16* wd;      // [CIN][taps][N]    (dgrad), may be null
+  int K, N, CIN;
 };
 constexpr int MAX_SEGS = 6;
 struct OptArgs {
@@ -230,6 +251,15 @@ __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs a) {
     } break;
   }
   a.w[p] = w;
+  if (s.wt && i < s.K * s.N) {
+    const int k = i / s.N, n = i - k * s.N;
+    const __nv_bfloat16 v = __float2bfloat16_rn(w);
+    s.wt[(size_t)n * s.K + k] = v;
+    if (s.wd) {
+      const int t = k / s.CIN, c = k - t * s.CIN;
+      s.wd[((size_t)c * (s.K / s.CIN) + t) * s.N + n] = v;
+    }
+  }
 }
 
 // Materialises the flat gradient (data-parallel path and parity checks).
@@ -931,19 +961,26 @@ static void fill_segs(dqn_net_s* h, OptArgs* o, const int nsplit[4], bool from_f
     for (int i = 0; i < 3; ++i) {
       const Tensor& w = h->tensors[2 * i];
       const Tensor& b = h->tensors[2 * i + 1];
-      o->seg[i] = Seg{(long long)w.off, (int)(w.numel + b.numel), (int)w.numel, h->grad + w.off, 1, 0};
+      o->seg[i] = Seg{(long long)w.off, (int)(w.numel + b.numel), (int)w.numel, h->grad + w.off, 1, 0, nullptr, nullptr, 0, 0, 0};
     }
   } else {
     o->nseg = 5;
     for (int l = 0; l < 4; ++l) {
       const Tensor& w = h->tensors[2 * l];
       const GemmLayer& L = h->L[l];
-      Seg s{(long long)w.off, L.K * L.N + L.N, l == 3 ? L.K * L.N : 0, L.partial, nsplit[l], (long long)(L.K + 1) * L.N};
+      Seg s{(long long)w.off, L.K * L.N + L.N, l == 3 ? L.K * L.N : 0, L.partial, nsplit[l], (long long)(L.K + 1) * L.N,
+            nullptr, nullptr, 0, 0, 0};
       if (from_flat_grad) { s.partial = h->grad + w.off; s.nsplit = 1; s.stride = 0; }
+      if (h->precision == 1) {
+        s.wt = h->wt_bf[0] + h->wt_off[l];
+        s.wd = l >= 1 ? h->wd_bf + h->wd_off[l] : nullptr;
+        s.K = L.K; s.N = L.N;
+        s.CIN = l == 0 ? 4 : (l == 1 ? 32 : (l == 2 ? 64 : L.K));
+      }
       o->seg[l] = s;
     }
     const Tensor& w5 = h->tensors[8];
-    Seg s{(long long)w5.off, (h->F + 1) * h->A, h->F * h->A, h->head_partial, 1, 0};
+    Seg s{(long long)w5.off, (h->F + 1) * h->A, h->F * h->A, h->head_partial, 1, 0, nullptr, nullptr, 0, 0, 0};
     if (from_flat_grad) s.partial = h->grad + w5.off;
     o->seg[4] = s;
   }
@@ -1033,11 +1070,18 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
     const float* w5 = h->online + h->tensors[8].off;
     {
     StageScope sc(h, DQN_STAGE_TD_HEAD, st);
-    td_head_kernel<<<(k + 7) / 8, 256, 0, st>>>(h->act[0][3], h->act[1][3], w5, h->online + h->tensors[9].off,
-                                                h->target + h->tensors[8].off, h->target + h->tensors[9].off, d_actions,
-                                                d_rewards, d_term, k, h->F, h->A, h->hyper.gamma, h->hyper.loss, d_q,
-                                                h->se, h->g, h->dact[3], h->precision == 1 ? h->dact_bf[3] : nullptr,
-                                                h->step);
+    if (h->F == 256)
+      td_head_kernel<8><<<(k + 7) / 8, 256, 0, st>>>(h->act[0][3], h->act[1][3], w5, h->online + h->tensors[9].off,
+                                                     h->target + h->tensors[8].off, h->target + h->tensors[9].off,
+                                                     d_actions, d_rewards, d_term, k, h->A, h->hyper.gamma, h->hyper.loss,
+                                                     d_q, h->se, h->g, h->dact[3],
+                                                     h->precision == 1 ? h->dact_bf[3] : nullptr, h->step);
+    else
+      td_head_kernel<16><<<(k + 7) / 8, 256, 0, st>>>(h->act[0][3], h->act[1][3], w5, h->online + h->tensors[9].off,
+                                                      h->target + h->tensors[8].off, h->target + h->tensors[9].off,
+                                                      d_actions, d_rewards, d_term, k, h->A, h->hyper.gamma, h->hyper.loss,
+                                                      d_q, h->se, h->g, h->dact[3],
+                                                      h->precision == 1 ? h->dact_bf[3] : nullptr, h->step);
     }
     // fork: head/fc/conv3/conv2 weight gradients on the side stream, data-gradient chain + conv1 wgrad on `st`
     cudaStream_t sd = h->side;
@@ -1099,7 +1143,6 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       StageScope sc(h, DQN_STAGE_OPTIMIZER, st);
       optimizer_kernel<<<grid, 256, 0, st>>>(oa);
     }
-    if (h->precision == 1) { int rc = refresh_bf16_weights(h, 0, st); if (rc) return rc; }
   }
   DQN_CUDA(cudaGetLastError());
   return 0;
@@ -1134,7 +1177,6 @@ extern "C" int dqn_net_apply(dqn_net_t h, dqn_stream_t stream) {
     StageScope sc(h, DQN_STAGE_OPTIMIZER, static_cast<cudaStream_t>(stream));
     optimizer_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(oa);
   }
-  if (h->precision == 1) { int rc = refresh_bf16_weights(h, 0, static_cast<cudaStream_t>(stream)); if (rc) return rc; }
   DQN_CUDA(cudaGetLastError());
   return 0;
 }
