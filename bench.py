@@ -52,6 +52,8 @@ def parse():
     ap.add_argument("--batch", type=int, default=None, help="minibatch per GPU (default 32; 512 = large-batch sweep)")
     ap.add_argument("--capacity", type=int, default=1000000, help="replay transitions per GPU")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--dp", default="peer", choices=["peer", "nccl"],
+                    help="gradient exchange at N>1: fused into the optimizer over NVLink peer memory, or NCCL all-reduce")
     ap.add_argument("--precision", default="fp32", choices=["fp32", "bf16"],
                     help="fp32 = CUDA-core parity mode (1e-4); bf16 = tcgen05 tensor-core mode (2e-2)")
     ap.add_argument("--cpu-steps", type=int, default=20)
@@ -262,6 +264,8 @@ def run_b200(args):
         dist.broadcast(net.flat_buffer("online"), 0)
         net.sync_target()
         net.set_hyper(cfg, grad_scale=1.0 / world)
+        if args.dp == "peer":
+            net.connect_peers()
     rm = replay_memory.ReplayMemory(args.capacity, device=local, trusted=True)
     # create the ring through the shell (first add fixes shape/dtype), then bulk-fill it on the device
     seed_state = np.zeros((84, 84, 4), np.uint8)
@@ -284,6 +288,8 @@ def run_b200(args):
         def eager_step(want_loss=False):
             if world == 1:
                 net.train_step(rm, batch, d_indices=d_idx, want_loss=want_loss)
+            elif net.peers_connected:
+                net.dp_train_step(rm, batch, d_indices=d_idx, want_loss=want_loss)
             else:
                 b = rm.gather(d_idx)
                 net.backward_on_batch(b, want_loss=want_loss)
@@ -353,7 +359,7 @@ def run_b200(args):
             gather_ms = 0.0
             for i in range(nprof):
                 d_idx.copy_(idx_table[(warmup + i) % total_steps])
-                if world > 1:
+                if world > 1 and not net.peers_connected:
                     g_evt0.record()
                     b = rm.gather(d_idx)
                     g_evt1.record()
@@ -363,7 +369,7 @@ def run_b200(args):
                 else:
                     eager_step()
                 c.check(c.lib.dqn_net_timing_collect(net.handle))
-                if world > 1:
+                if world > 1 and not net.peers_connected:
                     gather_ms += g_evt0.elapsed_time(g_evt1)
             c.check(c.lib.dqn_net_set_timing(net.handle, 0))
             tot, cnt = c.c_f64(), c.c_i32()
@@ -376,7 +382,7 @@ def run_b200(args):
                 if cnt.value:
                     kernels[name.decode()] = tot.value / cnt.value * 1e3        # us per launch
                 s += 1
-            if world > 1:
+            if world > 1 and not net.peers_connected:
                 kernels["gather"] = gather_ms / nprof * 1e3
             roof = roofline(kernels, args.arch, batch, net.flat_size)
 

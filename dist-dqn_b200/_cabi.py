@@ -64,6 +64,10 @@ SIGNATURES = {
     "dqn_net_backward": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_i32, c_vp]),
     "dqn_net_apply": (C.c_int, [c_vp, c_vp]),
     "dqn_net_target_sync": (C.c_int, [c_vp, c_vp]),
+    "dqn_net_dp_handle": (C.c_int, [c_vp, c_vp]),
+    "dqn_net_dp_connect": (C.c_int, [c_vp, c_i32, c_i32, c_vp]),
+    "dqn_net_dp_step": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
+    "dqn_train_step_dp": (C.c_int, [c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
     "dqn_train_step": (C.c_int, [c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
     "dqn_cnn_forward_noalloc": (C.c_int, [c_vp, c_i32, c_vp, c_i32, c_vp, c_vp, c_vp]),
     "dqn_launch_count": (c_i64, []),

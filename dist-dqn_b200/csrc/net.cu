@@ -177,7 +177,24 @@ struct OptArgs {
   const long long* step;
   float lr, reg, momentum, decay, gscale;
   int opt;
+  // data-parallel one-shot all-reduce over NVLink peer memory (world > 1): the gradient of every rank lives in a
+  // double-buffered exchange block that all ranks have mapped; flags[p] = last step whose gradient rank p published
+  int world;
+  const float* peer_grad[8];             // exchange gradient buffers of all ranks ([2][P] floats each), rank order
+  const unsigned long long* flags;       // this rank's flag array (written by the peers)
+  long long P;
 };
+
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float ld_relaxed_sys(const float* p) {
+  float v;
+  asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
 
 __device__ __forceinline__ float seg_grad(const Seg& s, int i) {
   float gsum = 0.f;
@@ -196,10 +213,31 @@ __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs a) {
     }
     __syncthreads();
   }
+  const long long step = *a.step;
+  if (a.world > 1) {
+    // wait until every rank has published its gradient of this step (bounded: a dead peer traps instead of hanging)
+    if (threadIdx.x == 0) {
+      const long long t0 = clock64();
+      for (int r = 0; r < a.world; ++r) {
+        while (ld_acquire_sys(a.flags + r) < (unsigned long long)step) {
+          if (clock64() - t0 > 8000000000LL) __trap();
+        }
+      }
+    }
+    __syncthreads();
+  }
   if (i >= s.len) return;
   const size_t p = (size_t)s.off + i;
   float w = a.w[p];
-  float g = seg_grad(s, i) * a.gscale;
+  float g;
+  if (a.world > 1) {
+    const size_t gi = (size_t)(step & 1) * (size_t)a.P + p;
+    g = 0.f;
+    for (int r = 0; r < a.world; ++r) g += ld_relaxed_sys(a.peer_grad[r] + gi);     // rank order: identical on every rank
+    g *= a.gscale;
+  } else {
+    g = seg_grad(s, i) * a.gscale;
+  }
   if (i < s.reg_len) g = fmaf(a.reg, w, g);
   switch (a.opt) {
     case DQN_OPT_SGD:
@@ -263,13 +301,41 @@ __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs a) {
 }
 
 // Materialises the flat gradient (data-parallel path and parity checks).
-__global__ void __launch_bounds__(256) reduce_grad_kernel(OptArgs a, float* __restrict__ grad, float reg) {
+struct PublishArgs {
+  unsigned long long* const* peer_flags;   // null: nothing to publish
+  unsigned int* done_counter;              // blocks finished so far (reset by the last one)
+  int rank, world;
+};
+
+__global__ void __launch_bounds__(256) reduce_grad_kernel(OptArgs a, float* __restrict__ grad, float reg, int by_parity,
+                                                          PublishArgs pub) {
   const Seg s = a.seg[blockIdx.y];
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= s.len) return;
-  float g = seg_grad(s, i);
-  if (i < s.reg_len) g = fmaf(reg, a.w[(size_t)s.off + i], g);
-  grad[(size_t)s.off + i] = g;
+  if (by_parity) grad += (size_t)(*a.step & 1) * (size_t)a.P;     // exchange block: buffer of this step's parity
+  if (i < s.len) {
+    float g = seg_grad(s, i);
+    if (i < s.reg_len) g = fmaf(reg, a.w[(size_t)s.off + i], g);
+    grad[(size_t)s.off + i] = g;
+  }
+  if (pub.peer_flags) {
+    // the last block to finish tells every rank (system-scope release) that this rank's gradient is complete
+    __shared__ bool last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const unsigned int total = gridDim.x * gridDim.y;
+      last = atomicAdd(pub.done_counter, 1u) == total - 1;
+    }
+    __syncthreads();
+    if (last) {
+      if (threadIdx.x == 0) *pub.done_counter = 0;
+      if ((int)threadIdx.x < pub.world) {
+        __threadfence_system();
+        const unsigned long long v = (unsigned long long)*a.step;
+        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(pub.peer_flags[threadIdx.x] + pub.rank), "l"(v) : "memory");
+      }
+    }
+  }
 }
 
 // loss = mean_b se_b + reg * sum_{reg tensors} ||w||^2 / 2   (network.py:150-152); one CTA.
@@ -293,6 +359,16 @@ __global__ void __launch_bounds__(256) loss_kernel(OptArgs a, const float* __res
     __syncthreads();
   }
   if (threadIdx.x == 0) *out = red[0];
+}
+
+// Publishes "my gradient of step *step is complete" to every rank's flag array (including my own).
+__global__ void dp_publish_kernel(unsigned long long* const* peer_flags, int rank, int world, const long long* step) {
+  const int r = threadIdx.x;
+  if (r < world) {
+    __threadfence_system();
+    const unsigned long long v = (unsigned long long)*step;
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(peer_flags[r] + rank), "l"(v) : "memory");
+  }
 }
 
 __global__ void fill_kernel(float* p, long long n, float v) {
@@ -489,6 +565,13 @@ struct dqn_net_s {
   dqn_hyper_t hyper;
   MlpOff mo;
   std::vector<void*> allocs;
+  // data-parallel exchange over peer memory (dqn_net_dp_*)
+  void* dp_block = nullptr;                    // [256 B flags][2][P] floats, cudaMalloc'ed, IPC-shared
+  float* dp_grad = nullptr;                    // = dp_block + 256
+  int dp_rank = 0, dp_world = 1;
+  void* dp_peer_block[8] = {};                 // mapped exchange blocks of all ranks (own = dp_block)
+  unsigned long long** dp_peer_flags_dev = nullptr;   // device array of the peers' flag pointers
+  unsigned int* dp_counter = nullptr;                 // finished-block counter of the publishing reduce kernel
   // weight-gradient kernels run on a forked stream, concurrently with the data-gradient chain (captured into the
   // step's CUDA graph as a parallel branch)
   cudaStream_t side = nullptr;
@@ -660,6 +743,9 @@ extern "C" int dqn_net_destroy(dqn_net_t h) {
   DeviceGuard g(h->device);
   cudaDeviceSynchronize();
   for (void* p : h->allocs) cudaFree(p);
+  for (int r = 0; r < 8; ++r)
+    if (h->dp_peer_block[r] && h->dp_peer_block[r] != h->dp_block) cudaIpcCloseMemHandle(h->dp_peer_block[r]);
+  if (h->dp_block) cudaFree(h->dp_block);
   if (h->side) cudaStreamDestroy(h->side);
   for (int i = 0; i < 3; ++i) if (h->ev_fork[i]) cudaEventDestroy(h->ev_fork[i]);
   if (h->ev_join) cudaEventDestroy(h->ev_join);
@@ -746,6 +832,8 @@ extern "C" int dqn_net_set_hyper(dqn_net_t h, const dqn_hyper_t* hyper, int32_t 
     fill_kernel<<<64, 256>>>(h->slot1, h->P, 0.f);
     DQN_CUDA(cudaGetLastError());
     DQN_CUDA(cudaMemset(h->step, 0, 16));
+    // the exchange flags count steps too (only meaningful if every rank resets at the same point, behind a barrier)
+    if (h->dp_block) DQN_CUDA(cudaMemset(h->dp_block, 0, 256));
     DQN_CUDA(cudaDeviceSynchronize());
   }
   return 0;
@@ -985,6 +1073,7 @@ static void fill_segs(dqn_net_s* h, OptArgs* o, const int nsplit[4], bool from_f
     o->seg[4] = s;
   }
   o->w = h->online; o->s0 = h->slot0; o->s1 = h->slot1; o->step = h->step;
+  o->world = 1; o->P = h->P;
   o->lr = h->hyper.lr; o->reg = h->hyper.reg_param; o->momentum = h->hyper.momentum; o->decay = h->hyper.rmsprop_decay;
   o->gscale = h->hyper.grad_scale; o->opt = h->hyper.optimizer;
 }
@@ -1057,7 +1146,13 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       // grad already holds the data term; add reg*w in place through the reduce kernel (partial == grad)
       dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
       StageScope sc(h, DQN_STAGE_REDUCE_GRAD, st);
-      reduce_grad_kernel<<<grid, 256, 0, st>>>(oa, h->grad, h->hyper.reg_param);
+      reduce_grad_kernel<<<grid, 256, 0, st>>>(oa, h->grad, h->hyper.reg_param, 0, PublishArgs{nullptr, nullptr, 0, 1});
+    }
+    if (mode == 2) {
+      dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
+      StageScope sc(h, DQN_STAGE_REDUCE_GRAD, st);
+      reduce_grad_kernel<<<grid, 256, 0, st>>>(oa, h->dp_grad, 0.f, 1,      // copy into this step's exchange buffer + publish
+                                               PublishArgs{h->dp_peer_flags_dev, h->dp_counter, h->dp_rank, h->dp_world});
     }
   } else {
     const bool nat = h->arch == DQN_ARCH_NATURE;
@@ -1131,10 +1226,13 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
     DQN_CUDA(cudaStreamWaitEvent(st, h->ev_join, 0));
     DQN_CUDA(cudaGetLastError());
     fill_segs(h, &oa, nsplit, false);
-    if (mode == 1) {
+    if (mode >= 1) {
       dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
       StageScope sc(h, DQN_STAGE_REDUCE_GRAD, st);
-      reduce_grad_kernel<<<grid, 256, 0, st>>>(oa, h->grad, include_reg ? h->hyper.reg_param : 0.f);
+      reduce_grad_kernel<<<grid, 256, 0, st>>>(
+          oa, mode == 2 ? h->dp_grad : h->grad, include_reg ? h->hyper.reg_param : 0.f, mode == 2 ? 1 : 0,
+          mode == 2 ? PublishArgs{h->dp_peer_flags_dev, h->dp_counter, h->dp_rank, h->dp_world}
+                    : PublishArgs{nullptr, nullptr, 0, 1});
     }
   }
   if (mode == 0) {
@@ -1143,6 +1241,20 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       StageScope sc(h, DQN_STAGE_OPTIMIZER, st);
       optimizer_kernel<<<grid, 256, 0, st>>>(oa);
     }
+  }
+  if (mode == 2) {
+    // the reduce kernel above published this rank's gradient; now sum all ranks' gradients inside the optimizer
+    // (peer loads over NVLink)
+    const int one[4] = {1, 1, 1, 1};
+    fill_segs(h, &oa, one, true);
+    oa.world = h->dp_world;
+    for (int r = 0; r < h->dp_world; ++r)
+      oa.peer_grad[r] = reinterpret_cast<const float*>(static_cast<const char*>(h->dp_peer_block[r]) + 256);
+    oa.flags = static_cast<const unsigned long long*>(h->dp_block);
+    oa.P = h->P;
+    dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
+    StageScope sc(h, DQN_STAGE_OPTIMIZER, st);
+    optimizer_kernel<<<grid, 256, 0, st>>>(oa);
   }
   DQN_CUDA(cudaGetLastError());
   return 0;
@@ -1209,6 +1321,81 @@ extern "C" int dqn_train_step(dqn_net_t net, dqn_replay_t replay, const int32_t*
   }
   if (rc) return rc;
   return run_step(net, net->st_states, net->st_next, net->st_actions, net->st_rewards, net->st_term, k, d_loss, nullptr, 0,
+                  0, static_cast<cudaStream_t>(stream));
+}
+
+// ---------------------------------------------------------------------------------------------- peer-memory data parallelism
+static int dp_alloc(dqn_net_s* h) {
+  if (h->dp_block) return 0;
+  const size_t bytes = 256 + 2 * (size_t)h->P * sizeof(float);
+  DQN_CUDA(cudaMalloc(&h->dp_block, bytes));            // its own allocation: IPC handles cover whole allocations
+  DQN_CUDA(cudaMemset(h->dp_block, 0, bytes));
+  h->dp_grad = reinterpret_cast<float*>(static_cast<char*>(h->dp_block) + 256);
+  DQN_CUDA(cudaMalloc(reinterpret_cast<void**>(&h->dp_peer_flags_dev), 8 * sizeof(void*)));
+  h->allocs.push_back(h->dp_peer_flags_dev);
+  DQN_CUDA(cudaMalloc(reinterpret_cast<void**>(&h->dp_counter), 16));
+  DQN_CUDA(cudaMemset(h->dp_counter, 0, 16));
+  h->allocs.push_back(h->dp_counter);
+  return 0;
+}
+
+extern "C" int dqn_net_dp_handle(dqn_net_t h, void* out_handle64) {
+  DQN_REQUIRE(h && out_handle64, DQN_ERR_INVALID, "dp_handle: NULL argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  DeviceGuard g(h->device);
+  int rc = dp_alloc(h);
+  if (rc) return rc;
+  cudaIpcMemHandle_t hd;
+  DQN_CUDA(cudaIpcGetMemHandle(&hd, h->dp_block));
+  memcpy(out_handle64, &hd, 64);
+  return 0;
+}
+
+extern "C" int dqn_net_dp_connect(dqn_net_t h, int32_t rank, int32_t world, const void* handles) {
+  DQN_REQUIRE(h && handles, DQN_ERR_INVALID, "dp_connect: NULL argument");
+  DQN_REQUIRE(world >= 2 && world <= 8 && rank >= 0 && rank < world, DQN_ERR_INVALID,
+              "dp_connect: world must be 2..8 (one NVLink domain) and 0 <= rank < world");
+  DeviceGuard g(h->device);
+  int rc = dp_alloc(h);
+  if (rc) return rc;
+  unsigned long long* flags[8] = {};
+  for (int r = 0; r < world; ++r) {
+    if (r == rank) {
+      h->dp_peer_block[r] = h->dp_block;
+    } else if (!h->dp_peer_block[r]) {
+      cudaIpcMemHandle_t hd;
+      memcpy(&hd, static_cast<const char*>(handles) + 64 * r, 64);
+      DQN_CUDA(cudaIpcOpenMemHandle(&h->dp_peer_block[r], hd, cudaIpcMemLazyEnablePeerAccess));
+    }
+    flags[r] = static_cast<unsigned long long*>(h->dp_peer_block[r]);
+  }
+  DQN_CUDA(cudaMemcpy(h->dp_peer_flags_dev, flags, sizeof(flags), cudaMemcpyHostToDevice));
+  h->dp_rank = rank;
+  h->dp_world = world;
+  return 0;
+}
+
+extern "C" int dqn_net_dp_step(dqn_net_t h, const void* d_states, const void* d_next_states, const int32_t* d_actions,
+                               const double* d_rewards, const uint8_t* d_terminals, int32_t k, float* d_loss,
+                               dqn_stream_t stream) {
+  DQN_REQUIRE(h, DQN_ERR_INVALID, "dp_step: NULL handle");
+  DQN_REQUIRE(h->dp_world >= 2 && h->dp_peer_flags_dev, DQN_ERR_STATE, "dp_step: call dqn_net_dp_connect first");
+  DeviceGuard g(h->device);
+  return run_step(h, d_states, d_next_states, d_actions, d_rewards, d_terminals, k, d_loss, nullptr, 2, 0,
+                  static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int dqn_train_step_dp(dqn_net_t net, dqn_replay_t replay, const int32_t* d_logical_idx, int32_t k, float* d_loss,
+                                 dqn_stream_t stream) {
+  DQN_REQUIRE(net && replay && d_logical_idx, DQN_ERR_INVALID, "dqn_train_step_dp: NULL argument");
+  DQN_REQUIRE(k >= 1 && k <= net->MB, DQN_ERR_INVALID, "dqn_train_step_dp: minibatch %d outside [1, max_batch=%d]", k, net->MB);
+  DQN_REQUIRE(net->dp_world >= 2 && net->dp_peer_flags_dev, DQN_ERR_STATE, "dqn_train_step_dp: call dqn_net_dp_connect first");
+  DQN_REQUIRE(dqn_replay_device_(replay) == net->device, DQN_ERR_INVALID, "replay and net live on different devices");
+  DeviceGuard g(net->device);
+  int rc = dqn_replay_gather(replay, d_logical_idx, k, net->st_states, net->st_next, net->st_actions, net->st_rewards,
+                             net->st_term, stream);
+  if (rc) return rc;
+  return run_step(net, net->st_states, net->st_next, net->st_actions, net->st_rewards, net->st_term, k, d_loss, nullptr, 2,
                   0, static_cast<cudaStream_t>(stream));
 }
 

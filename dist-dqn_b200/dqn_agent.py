@@ -127,6 +127,8 @@ class DQNAgent(object):
         net, rm = self.network, self.replay_memory
         if self._world == 1:
             return net.train_step(rm, k, d_indices=d_idx, want_loss=want_loss)
+        if getattr(net, 'peers_connected', False):     # gradient exchange fused into the optimizer (NVLink peer loads)
+            return net.dp_train_step(rm, k, d_indices=d_idx, want_loss=want_loss)
         import torch.distributed as dist
         batch = rm.gather(d_idx)
         loss, _ = net.backward_on_batch(batch, want_loss=want_loss)

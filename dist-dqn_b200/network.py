@@ -113,6 +113,7 @@ class Network(object):
             setattr(self, name, _Handle(self, name))
         self._loss = torch.zeros(1, dtype=torch.float32, device=self.device)
         self._io = {}
+        self.peers_connected = False
 
     def __del__(self):
         try:
@@ -257,6 +258,39 @@ class Network(object):
             d_indices = replay_memory.upload_indices(replay_memory.sample_indices(k))
         _c.check(_c.lib.dqn_train_step(self._h, replay_memory.handle, d_indices.data_ptr(), int(k),
                                        self._loss.data_ptr() if want_loss else None, _c.current_stream()), 'train_step')
+        return self._loss if want_loss else None
+
+    # ------------------------------------------------------------------ data parallel over NVLink peer memory
+    def connect_peers(self):
+        """Maps every rank's gradient exchange block (CUDA IPC) so the optimizer kernel can sum the ranks'
+        gradients itself; afterwards ``dp_train_step`` / ``dp_train_on_batch`` replace backward + all-reduce +
+        apply.  Needs an initialised torch.distributed group with one rank per GPU of one box."""
+        import torch
+        import torch.distributed as dist
+        world, rank = dist.get_world_size(), dist.get_rank()
+        mine = (_c.C.c_uint8 * 64)()
+        _c.check(_c.lib.dqn_net_dp_handle(self._h, mine), 'connect_peers')
+        gathered = [None] * world
+        dist.all_gather_object(gathered, bytes(mine))
+        blob = b''.join(gathered)
+        _c.check(_c.lib.dqn_net_dp_connect(self._h, rank, world, blob), 'connect_peers')
+        self.set_hyper(self.config, grad_scale=1.0 / world)
+        self.peers_connected = True
+        dist.barrier()
+
+    def dp_train_on_batch(self, batch, want_loss=False):
+        k = batch.actions.numel()
+        _c.check(_c.lib.dqn_net_dp_step(self._h, batch.states.data_ptr(), batch.next_states.data_ptr(),
+                                        batch.actions.data_ptr(), batch.rewards.data_ptr(), batch.terminals.data_ptr(),
+                                        k, self._loss.data_ptr() if want_loss else None, _c.current_stream()), 'dp_step')
+        return self._loss if want_loss else None
+
+    def dp_train_step(self, replay_memory, k, d_indices=None, want_loss=False):
+        if d_indices is None:
+            d_indices = replay_memory.upload_indices(replay_memory.sample_indices(k))
+        _c.check(_c.lib.dqn_train_step_dp(self._h, replay_memory.handle, d_indices.data_ptr(), int(k),
+                                          self._loss.data_ptr() if want_loss else None, _c.current_stream()),
+                 'dp_train_step')
         return self._loss if want_loss else None
 
     def sync_target(self):

@@ -178,6 +178,24 @@ int dqn_net_backward(dqn_net_t h, const void* d_states, const void* d_next_state
                      const double* d_rewards, const uint8_t* d_terminals, int32_t k, float* d_loss, float* d_q,
                      int32_t include_reg, dqn_stream_t stream);
 int dqn_net_apply(dqn_net_t h, dqn_stream_t stream);
+/* Data-parallel update with the gradient exchange fused into the optimizer kernel (replaces the reference's
+ * parameter-server round trip, main.py:117-120, with the mean semantics of SyncReplicasOptimizer, network.py:187-192):
+ * every rank publishes its local mean gradient in a double-buffered exchange block that all ranks of the NVLink
+ * domain have mapped (CUDA IPC), raises a per-rank flag with a system-scope release store, and the optimizer kernel
+ * of every rank waits for all flags and sums the N gradients with peer loads in rank order (bit-identical weights on
+ * all ranks) -- no separate all-reduce launch.  A dead peer makes the waiting kernel trap after a few seconds
+ * instead of hanging.  Set hyper.grad_scale = 1/world.  2 <= world <= 8, one process per GPU.
+ *   dqn_net_dp_handle : 64-byte IPC handle of this rank's exchange block (all-gather it across ranks)
+ *   dqn_net_dp_connect: maps the peers' blocks; handles = world x 64 bytes in rank order
+ *   dqn_net_dp_step   : dqn_net_train_step across ranks; every rank must call it the same number of times */
+int dqn_net_dp_handle(dqn_net_t h, void* out_handle64);
+int dqn_net_dp_connect(dqn_net_t h, int32_t rank, int32_t world, const void* handles);
+int dqn_net_dp_step(dqn_net_t h, const void* d_states, const void* d_next_states, const int32_t* d_actions,
+                    const double* d_rewards, const uint8_t* d_terminals, int32_t k, float* d_loss, dqn_stream_t stream);
+/* dqn_train_step (gather + update) across ranks. */
+int dqn_train_step_dp(dqn_net_t net, dqn_replay_t replay, const int32_t* d_logical_idx, int32_t k, float* d_loss,
+                      dqn_stream_t stream);
+
 /* DQNAgent._update_target_network's assigns (dqn_agent.py:215-222, network.py:251-252): one D2D copy. */
 int dqn_net_target_sync(dqn_net_t h, dqn_stream_t stream);
 

@@ -47,6 +47,29 @@ def main():
         errs = [rel_err(a, b) for a, b in zip(got, ref.get_params())]
         print("dp identity max rel err", max(errs))
         ok = max(errs) < 2e-5
+    # same step again through the peer-memory path (gradient exchange fused into the optimizer kernel)
+    pnet = network.Network.create_network(cfg, ishape, A, num_replicas=world)
+    if rank == 0:
+        pnet.set_params(params)
+    dp.broadcast_parameters(pnet.flat_buffer("online"))
+    pnet.sync_target()
+    pnet.connect_peers()
+    for _ in range(3):                                   # several steps: exercises the double buffering / flags
+        pnet.dp_train_on_batch(to_device_batch(pnet, *batch))
+    torch.cuda.synchronize()
+    for _ in range(2):
+        net.backward_on_batch(to_device_batch(net, *batch))
+        dp.sync_gradients(net.flat_buffer("grad"))
+        net.apply_gradients()
+    torch.cuda.synchronize()
+    perr = max(rel_err(a, b) for a, b in zip(pnet.get_params(), net.get_params()))
+    if rank == 0:
+        print("peer path vs NCCL path after 3 steps, max rel err", perr)
+    ok = ok and perr < 2e-5
+    pflat = pnet.flat_buffer("online").clone()
+    p0 = pflat.clone()
+    dist.broadcast(p0, 0)
+    ok = ok and bool(torch.equal(pflat, p0))
     # all ranks must hold identical weights afterwards
     flat = net.flat_buffer("online").clone()
     ref0 = flat.clone()
