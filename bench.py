@@ -54,8 +54,8 @@ def parse():
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--dp", default="peer", choices=["peer", "nccl"],
                     help="gradient exchange at N>1: fused into the optimizer over NVLink peer memory, or NCCL all-reduce")
-    ap.add_argument("--precision", default="fp32", choices=["fp32", "bf16"],
-                    help="fp32 = CUDA-core parity mode (1e-4); bf16 = tcgen05 tensor-core mode (2e-2)")
+    ap.add_argument("--precision", default="bf16", choices=["fp32", "bf16"],
+                    help="bf16 = tcgen05 tensor-core mode (parity 2e-2, default; cnn arch); fp32 = CUDA-core parity mode (1e-4)")
     ap.add_argument("--cpu-steps", type=int, default=20)
     ap.add_argument("--e2e-steps", type=int, default=300)
     ap.add_argument("--skip-cpu", action="store_true")
@@ -256,6 +256,8 @@ def run_b200(args):
     batch = args.batch or 32            # same per-GPU minibatch at every N (weak scaling); --batch 512 = large-batch sweep
     steps = args.steps or (2000 if batch <= 64 else 300)
     warmup = max(3, args.warmup if args.warmup is not None else 50)
+    if args.arch != "cnn":
+        args.precision = "fp32"                     # the tensor-core kernels cover the reference conv net
     cfg = atari_config(batch, args.arch, args.precision)
     cfg.device_index = local
 
@@ -386,6 +388,31 @@ def run_b200(args):
                 kernels["gather"] = gather_ms / nprof * 1e3
             roof = roofline(kernels, args.arch, batch, net.flat_size)
 
+        # ---- the other precision mode, same workload, for the record (N=1 only; short)
+        other = None
+        if world == 1 and args.arch == "cnn" and not args.skip_cpu:
+            ocfg = atari_config(batch, args.arch, "fp32" if args.precision == "bf16" else "bf16")
+            ocfg.device_index = local
+            onet = network.Network.create_network(ocfg, (84, 84, 4), A_PONG)
+            d_idx.copy_(idx_table[0])
+            for _ in range(3):
+                onet.train_step(rm, batch, d_indices=d_idx)
+            og = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(og, stream=side):
+                onet.train_step(rm, batch, d_indices=d_idx)
+            nother = min(steps, 500)
+            for i in range(10):
+                d_idx.copy_(idx_table[i], non_blocking=True); og.replay()
+            o0, o1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            o0.record()
+            for i in range(nother):
+                d_idx.copy_(idx_table[warmup + i], non_blocking=True); og.replay()
+            o1.record()
+            torch.cuda.synchronize()
+            other = {"precision": ocfg.precision, "value": nother / (o0.elapsed_time(o1) / 1e3), "unit": "updates/s",
+                     "steps": nother}
+            del og, onet
+
         # ---- gather-only throughput at a large batch (second half of BASELINE.json's metric)
         gather_info = None
         if rank == 0:
@@ -417,6 +444,8 @@ def run_b200(args):
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches_per_step * steps),
         "launches_per_step": int(launches_per_step), "cuda_graph": not args.no_graph,
         "roofline": roof, "cpu_baseline": cpu, "kernels_us": kernels, "gather": gather_info,
+        "precision": args.precision, "other_precision_mode": other,
+        "dp_exchange": (args.dp if world > 1 else None),
     }
     emit(line)
     _finish(world, dist)
@@ -445,6 +474,15 @@ def peaks():
     return 6650.0, 1590.0, 1400.0, "fallback"
 
 
+def _traffic(name, batch):
+    """DRAM bytes per launch of `name` from the committed ncu --set full capture (taken at B=32), else None."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        return t["dram_bytes_per_launch"].get(name) if batch == 32 else None
+    except Exception:
+        return None
+
+
 def roofline(kernels, arch, batch, nparams):
     """Roofline of the dominant kernel of the step (largest average duration)."""
     if not kernels:
@@ -460,7 +498,8 @@ def roofline(kernels, arch, batch, nparams):
         flops = 2.0 * macs[l] * batch * passes
         ach = flops / (us * 1e-6) / 1e12
         return {"kernel": name, "bound": "tensor", "achieved": ach, "peak": sustained, "unit": "TFLOP/s",
-                "frac": ach / sustained, "traffic": None, "us_per_launch": us, "peak_source": src + " bf16 sustained",
+                "frac": ach / sustained, "traffic": _traffic(name, batch), "us_per_launch": us,
+                "peak_source": src + " bf16 sustained",
                 "note": "implicit GEMM measured against the bf16 tensor-pipe peak (fp32 mode runs on CUDA cores)"}
     if name == "gather":
         byts = GATHER_BYTES * batch
