@@ -59,6 +59,7 @@ SIGNATURES = {
     "dqn_net_set_hyper": (C.c_int, [c_vp, C.POINTER(Hyper), c_i32]),
     "dqn_net_global_step": (C.c_int, [c_vp, C.POINTER(c_i64), c_vp]),
     "dqn_net_set_precision": (C.c_int, [c_vp, c_i32]),
+    "dqn_net_set_global_step": (C.c_int, [c_vp, c_i64]),
     "dqn_net_forward": (C.c_int, [c_vp, c_i32, c_vp, c_i32, c_vp, c_vp, c_vp]),
     "dqn_net_train_step": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_vp]),
     "dqn_net_backward": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_i32, c_vp]),

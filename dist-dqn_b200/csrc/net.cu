@@ -839,6 +839,15 @@ extern "C" int dqn_net_set_hyper(dqn_net_t h, const dqn_hyper_t* hyper, int32_t 
   return 0;
 }
 
+extern "C" int dqn_net_set_global_step(dqn_net_t h, int64_t step) {
+  DQN_REQUIRE(h && step >= 0, DQN_ERR_INVALID, "set_global_step: bad argument");
+  DeviceGuard g(h->device);
+  long long v = step;
+  DQN_CUDA(cudaDeviceSynchronize());
+  DQN_CUDA(cudaMemcpy(h->step, &v, sizeof(v), cudaMemcpyHostToDevice));
+  return 0;
+}
+
 extern "C" int dqn_net_global_step(dqn_net_t h, int64_t* step, dqn_stream_t stream) {
   DQN_REQUIRE(h && step, DQN_ERR_INVALID, "global_step: NULL argument");
   DeviceGuard g(h->device);

@@ -260,6 +260,30 @@ class Network(object):
                                        self._loss.data_ptr() if want_loss else None, _c.current_stream()), 'train_step')
         return self._loss if want_loss else None
 
+    # ------------------------------------------------------------------ checkpoint / resume
+    def save(self, path, extra=None):
+        """Everything needed to resume training -- the reference got this from tf.train.Supervisor's Saver
+        (main.py:136-143, 155): online and target parameters, both optimizer slots, global_step -- in one
+        .npz file.  ``extra`` (dict of small python values, e.g. epsilon / training_steps) rides along."""
+        blob = {'arch': np.array(self.ARCH), 'num_actions': np.array(self.num_actions),
+                'input_shape': np.array(self.input_shape), 'global_step': np.array(self.get_global_step())}
+        for which in ('online', 'target', 'slot0', 'slot1'):
+            for i, t in enumerate(self.get_params(which)):
+                blob['%s_%d' % (which, i)] = t
+        for k, v in (extra or {}).items():
+            blob['extra_' + k] = np.array(v)
+        np.savez(path, **blob)
+
+    def load(self, path):
+        """Restores a checkpoint written by ``save`` (same architecture / action count); returns the extras."""
+        z = np.load(path, allow_pickle=False)
+        if str(z['arch']) != self.ARCH or int(z['num_actions']) != self.num_actions:
+            raise RuntimeError('checkpoint is for %s with %d actions' % (z['arch'], int(z['num_actions'])))
+        for which in ('online', 'target', 'slot0', 'slot1'):
+            self.set_params([z['%s_%d' % (which, i)] for i in range(self.num_tensors)], which=which)
+        _c.check(_c.lib.dqn_net_set_global_step(self._h, int(z['global_step'])), 'load')
+        return {k[6:]: z[k].item() for k in z.files if k.startswith('extra_')}
+
     # ------------------------------------------------------------------ data parallel over NVLink peer memory
     def connect_peers(self):
         """Maps every rank's gradient exchange block (CUDA IPC) so the optimizer kernel can sum the ranks'

@@ -150,6 +150,8 @@ int dqn_net_download(dqn_net_t h, int32_t which, float* host, int64_t floats);
  * and resets the update counter (global_step, network.py:83). */
 int dqn_net_set_hyper(dqn_net_t h, const dqn_hyper_t* hyper, int32_t reset_slots);
 int dqn_net_global_step(dqn_net_t h, int64_t* step, dqn_stream_t stream); /* synchronises the stream */
+/* Restores the update counter when resuming from a checkpoint (the Supervisor restored global_step, main.py:136-143). */
+int dqn_net_set_global_step(dqn_net_t h, int64_t step);
 /* Arithmetic of the conv / fully-connected GEMMs (north_star's two modes; no reference counterpart, TF ran fp32):
  * 0 = fp32 on CUDA cores, the parity mode (<= 1e-4 vs the oracle);
  * 1 = bf16 operands on the tcgen05 tensor cores with fp32 accumulation, fp32 master weights, fp32 optimizer
