@@ -70,6 +70,9 @@ SIGNATURES = {
     "dqn_net_dp_step": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
     "dqn_train_step_dp": (C.c_int, [c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
     "dqn_train_step": (C.c_int, [c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
+    "dqn_preproc_create": (C.c_int, [C.POINTER(c_vp), c_i32, c_i32, c_i32, c_i32, c_i32]),
+    "dqn_preproc_destroy": (C.c_int, [c_vp]),
+    "dqn_preproc_run": (C.c_int, [c_vp, c_vp, c_i32, c_vp, c_vp]),
     "dqn_cnn_forward_noalloc": (C.c_int, [c_vp, c_i32, c_vp, c_i32, c_vp, c_vp, c_vp]),
     "dqn_launch_count": (c_i64, []),
     "dqn_net_set_timing": (C.c_int, [c_vp, c_i32]),

@@ -28,6 +28,7 @@ extern "C" {
 
 typedef struct dqn_replay_s* dqn_replay_t;
 typedef struct dqn_net_s* dqn_net_t;
+typedef struct dqn_preproc_s* dqn_preproc_t;
 typedef void* dqn_stream_t; /* cudaStream_t */
 
 enum dqn_status {
@@ -205,6 +206,15 @@ int dqn_net_target_sync(dqn_net_t h, dqn_stream_t stream);
  * net's own staging buffers, then dqn_net_train_step.  This is the unit bench.py times. */
 int dqn_train_step(dqn_net_t net, dqn_replay_t replay, const int32_t* d_logical_idx, int32_t k, float* d_loss,
                    dqn_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Frame preprocessing on the device -- utils.resize_image (utils.py:39-45: cv2.cvtColor(RGB2GRAY) then
+ * cv2.resize, bilinear), bit-exact with OpenCV's fixed-point uint8 paths.  d_rgb: n frames uint8
+ * [n][src_h][src_w][3]; d_out: uint8 [n][dst_h][dst_w], ready for dqn_replay_append_frames_device.
+ * ------------------------------------------------------------------------------------------------ */
+int dqn_preproc_create(dqn_preproc_t* out, int32_t src_h, int32_t src_w, int32_t dst_h, int32_t dst_w, int32_t device);
+int dqn_preproc_destroy(dqn_preproc_t h);
+int dqn_preproc_run(dqn_preproc_t h, const uint8_t* d_rgb, int32_t n, uint8_t* d_out, dqn_stream_t stream);
 
 /* Forward pass for callers that may not allocate device memory.  No counterpart in the reference.
  *
