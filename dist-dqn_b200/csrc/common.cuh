@@ -45,6 +45,41 @@ static inline int64_t round_up(int64_t v, int64_t m) { return (v + m - 1) / m * 
 void count_launch();
 int64_t launch_count();
 
+// Programmatic dependent launch (PDL): a kernel launched with launch_pdl may start while its predecessor in the
+// stream is still running; it must call pdl_wait() before touching any global memory (the wait returns once the
+// predecessor has completed and flushed), and calls pdl_trigger() early so that its own successor can be launched
+// and run its prologue (barrier init, TMEM allocation, index arithmetic) in the shadow of this kernel.  Both are
+// no-ops for kernels launched the ordinary way.
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                     unsigned cluster_z, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[2];
+  int na = 0;
+  at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[na].val.programmaticStreamSerializationAllowed = 1;
+  ++na;
+  if (cluster_z > 1) {
+    at[na].id = cudaLaunchAttributeClusterDimension;
+    at[na].val.clusterDim.x = 1;
+    at[na].val.clusterDim.y = 1;
+    at[na].val.clusterDim.z = cluster_z;
+    ++na;
+  }
+  cfg.attrs = at;
+  cfg.numAttrs = na;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+#endif
+
 // Ring view passed to kernels that read the replay ring (replay.cu, and the fused step).
 struct RingView {
   const uint8_t* frames;   // frame_capacity x pitch bytes

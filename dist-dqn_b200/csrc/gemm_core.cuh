@@ -19,6 +19,8 @@
 #include <cooperative_groups.h>
 #include <cuda_runtime.h>
 
+#include "common.cuh"
+
 namespace dqn {
 
 namespace cg = cooperative_groups;
@@ -198,6 +200,7 @@ __global__ void __launch_bounds__(NT) conv_fwd_kernel(FwdArgs a) {
   const Row row = decode_row<G>(m0 + am, a.B);
   const int bkk = tid >> 3, bnq = tid & 7;           // weight rows bkk and bkk+16
   const int ti = tid >> 3, tj = tid & 7;
+  pdl_wait();
   constexpr int T = G::K / BK;
   const int it0 = (int)(T * rank / S), it1 = (int)(T * (rank + 1) / S);
   float acc[4][4] = {};
@@ -223,6 +226,7 @@ __global__ void __launch_bounds__(NT) conv_fwd_kernel(FwdArgs a) {
     tile_fma(As, Bs, ti, tj, acc);
     __syncthreads();
   }
+  pdl_trigger();                                     // main loop done: the next kernel may start its prologue
   if (!cluster_reduce(&As[0][0], acc, tid)) return;
   const int n = n0 + tj * 4;
   const float4 bias = __ldg(reinterpret_cast<const float4*>(P.bias + n));
@@ -287,6 +291,7 @@ __global__ void __launch_bounds__(NT) conv_wgrad_kernel(WgradArgs a) {
   const int R = a.B * G::ROWS;
   const int r_begin = blockIdx.z * a.rows_per_split;
   const int r_end = min(R, r_begin + a.rows_per_split);
+  pdl_wait();
   const int aiq = tid & 15, ar = tid >> 4;          // gathers k-quad aiq of rows ar, ar+8, ar+16, ar+24
   const int kquad = (i0 >> 2) + aiq;
   const int br = tid >> 3, bnq = tid & 7;           // dz quad bnq of rows br and br+16
@@ -322,6 +327,7 @@ __global__ void __launch_bounds__(NT) conv_wgrad_kernel(WgradArgs a) {
     }
     __syncthreads();
   }
+  pdl_trigger();
   float* out = a.partial + (size_t)blockIdx.z * ((size_t)(G::K + 1) * G::COUT);
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
@@ -360,6 +366,7 @@ __global__ void __launch_bounds__(NT) conv_dgrad_kernel(DgradArgs a) {
   const int rem = m - b * (G::IH * G::IW);
   const int iy = rem / G::IW, ix = rem - iy * G::IW;
   const bool mvalid = m < M;
+  pdl_wait();
   const int brq = tid & 7, bc = tid >> 3;           // w quad (4 consecutive n) brq for input channels c0+bc, c0+bc+16
   const int ti = tid >> 3, tj = tid & 7;
   const unsigned S = cg::this_cluster().num_blocks();
@@ -412,6 +419,7 @@ __global__ void __launch_bounds__(NT) conv_dgrad_kernel(DgradArgs a) {
     tile_fma(As, Bs, ti, tj, acc);
     __syncthreads();
   }
+  pdl_trigger();                                     // main loop done: the next kernel may start its prologue
   if (!cluster_reduce(&As[0][0], acc, tid)) return;
 #pragma unroll
   for (int i = 0; i < 4; ++i) {

@@ -72,6 +72,8 @@ td_head_kernel(const float* __restrict__ h_on, const float* __restrict__ h_tg, c
   constexpr int F = FPL * 32;
   const int lane = threadIdx.x & 31;
   const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  pdl_trigger();
+  pdl_wait();
   if (blockIdx.x == 0 && threadIdx.x == 0) *step += 1;      // global_step (network.py:83, 198-202)
   if (b >= B) return;
   float x[FPL], xt[FPL];
@@ -113,6 +115,8 @@ td_head_kernel(const float* __restrict__ h_on, const float* __restrict__ h_tg, c
 __global__ void __launch_bounds__(256)
 head_wgrad_kernel(const float* __restrict__ h_on, const float* __restrict__ g, const int32_t* __restrict__ actions,
                   int B, int F, int A, float* __restrict__ out) {
+  pdl_trigger();
+  pdl_wait();
   const int o = blockIdx.x * blockDim.x + threadIdx.x;
   if (o >= (F + 1) * A) return;
   const int j = o / A, a = o - j * A;
@@ -203,6 +207,7 @@ __device__ __forceinline__ float seg_grad(const Seg& s, int i) {
 }
 
 __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs a) {
+  pdl_wait();
   const Seg s = a.seg[blockIdx.y];
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   __shared__ float lr_t_s;
@@ -309,6 +314,7 @@ struct PublishArgs {
 
 __global__ void __launch_bounds__(256) reduce_grad_kernel(OptArgs a, float* __restrict__ grad, float reg, int by_parity,
                                                           PublishArgs pub) {
+  pdl_wait();
   const Seg s = a.seg[blockIdx.y];
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (by_parity) grad += (size_t)(*a.step & 1) * (size_t)a.P;     // exchange block: buffer of this step's parity
@@ -341,6 +347,8 @@ __global__ void __launch_bounds__(256) reduce_grad_kernel(OptArgs a, float* __re
 // loss = mean_b se_b + reg * sum_{reg tensors} ||w||^2 / 2   (network.py:150-152); one CTA.
 __global__ void __launch_bounds__(256) loss_kernel(OptArgs a, const float* __restrict__ se, int B, float* __restrict__ out) {
   __shared__ float red[256];
+  pdl_trigger();
+  pdl_wait();
   float s = 0.f;
   for (int b = threadIdx.x; b < B; b += 256) s += se[b];
   s /= (float)B;
@@ -870,19 +878,7 @@ static int pick_split(int tiles, int chunks, int num_sms) {
 
 template <typename Kern, typename Args>
 static void launch_clustered(Kern kern, dim3 grid, int split, const Args& args, cudaStream_t st) {
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = grid;
-  cfg.blockDim = dim3(NT, 1, 1);
-  cfg.dynamicSmemBytes = 0;
-  cfg.stream = st;
-  cudaLaunchAttribute at[1];
-  at[0].id = cudaLaunchAttributeClusterDimension;
-  at[0].val.clusterDim.x = 1;
-  at[0].val.clusterDim.y = 1;
-  at[0].val.clusterDim.z = (unsigned)split;
-  cfg.attrs = at;
-  cfg.numAttrs = 1;
-  cudaLaunchKernelEx(&cfg, kern, args);
+  launch_pdl(kern, grid, dim3(NT, 1, 1), 0, st, (unsigned)split, args);
 }
 
 template <class G, typename TIn>
@@ -905,7 +901,7 @@ static void launch_wgrad(dqn_net_s* h, int l, const void* x, int B, cudaStream_t
   dim3 grid(G::K / BM, G::COUT / BN, ns);
   {
     StageScope sc(h, DQN_STAGE_WGRAD_FC + 2 * (3 - l), st);
-    conv_wgrad_kernel<G, TIn><<<grid, NT, 0, st>>>(a);
+    launch_pdl(conv_wgrad_kernel<G, TIn>, grid, dim3(NT), 0, st, 1, a);
   }
   *nsplit_out = ns;
 }
@@ -968,7 +964,7 @@ static void launch_fwd_tc(const umma::FwdArgsT& a, int npass, cudaStream_t st) {
   static bool once = (set_smem(umma::umma_fwd_kernel<G, TIn, NTILE>, smem), true);
   (void)once;
   dim3 grid((unsigned)((a.B * G::ROWS + umma::TM - 1) / umma::TM), G::COUT / NTILE, npass);
-  umma::umma_fwd_kernel<G, TIn, NTILE><<<grid, umma::TT, smem, st>>>(a);
+  launch_pdl(umma::umma_fwd_kernel<G, TIn, NTILE>, grid, dim3(umma::TT), smem, st, 1, a);
 }
 
 template <class G, typename TIn, int NTILE>
@@ -986,7 +982,7 @@ static void launch_wgrad_tc(dqn_net_s* h, int l, const void* x, int B, cudaStrea
   dim3 grid((G::K + umma::TM - 1) / umma::TM, G::COUT / NTILE, ns);
   {
     StageScope sc(h, DQN_STAGE_WGRAD_FC + 2 * (3 - l), st);
-    umma::umma_wgrad_kernel<G, TIn, NTILE><<<grid, umma::TT, smem, st>>>(a);
+    launch_pdl(umma::umma_wgrad_kernel<G, TIn, NTILE>, grid, dim3(umma::TT), smem, st, 1, a);
   }
   *nsplit_out = ns;
 }
@@ -1000,7 +996,7 @@ static void launch_dgrad_tc(dqn_net_s* h, int l, int B, cudaStream_t st) {
                      h->dact_bf[l - 1], B};
   dim3 grid((unsigned)((B * G::IH * G::IW + umma::TM - 1) / umma::TM), G::CIN / NTILE, 1);
   StageScope sc(h, DQN_STAGE_DGRAD_FC + 2 * (3 - l), st);
-  umma::umma_dgrad_kernel<G, NTILE><<<grid, umma::TT, smem, st>>>(a);
+  launch_pdl(umma::umma_dgrad_kernel<G, NTILE>, grid, dim3(umma::TT), smem, st, 1, a);
 }
 
 // fp32 master weights of one parameter set -> bf16 operand copies
@@ -1175,13 +1171,13 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
     {
     StageScope sc(h, DQN_STAGE_TD_HEAD, st);
     if (h->F == 256)
-      td_head_kernel<8><<<(k + 7) / 8, 256, 0, st>>>(h->act[0][3], h->act[1][3], w5, h->online + h->tensors[9].off,
+      launch_pdl(td_head_kernel<8>, dim3((k + 7) / 8), dim3(256), 0, st, 1, h->act[0][3], h->act[1][3], w5, h->online + h->tensors[9].off,
                                                      h->target + h->tensors[8].off, h->target + h->tensors[9].off,
                                                      d_actions, d_rewards, d_term, k, h->A, h->hyper.gamma, h->hyper.loss,
                                                      d_q, h->se, h->g, h->dact[3],
                                                      h->precision == 1 ? h->dact_bf[3] : nullptr, h->step);
     else
-      td_head_kernel<16><<<(k + 7) / 8, 256, 0, st>>>(h->act[0][3], h->act[1][3], w5, h->online + h->tensors[9].off,
+      launch_pdl(td_head_kernel<16>, dim3((k + 7) / 8), dim3(256), 0, st, 1, h->act[0][3], h->act[1][3], w5, h->online + h->tensors[9].off,
                                                       h->target + h->tensors[8].off, h->target + h->tensors[9].off,
                                                       d_actions, d_rewards, d_term, k, h->A, h->hyper.gamma, h->hyper.loss,
                                                       d_q, h->se, h->g, h->dact[3],
@@ -1193,13 +1189,13 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
     DQN_CUDA(cudaStreamWaitEvent(sd, h->ev_fork[0], 0));
     {
     StageScope sc(h, DQN_STAGE_HEAD_WGRAD, sd);
-    head_wgrad_kernel<<<((h->F + 1) * h->A + 255) / 256, 256, 0, sd>>>(h->act[0][3], h->g, d_actions, k, h->F, h->A,
-                                                                       h->head_partial);
+    launch_pdl(head_wgrad_kernel, dim3(((h->F + 1) * h->A + 255) / 256), dim3(256), 0, sd, 1, h->act[0][3], h->g, d_actions,
+               k, h->F, h->A, h->head_partial);
     }
     if (d_loss) {
       fill_segs(h, &oa, nsplit, false);
       StageScope sc(h, DQN_STAGE_LOSS, sd);
-      loss_kernel<<<1, 256, 0, sd>>>(oa, h->se, k, d_loss);
+      launch_pdl(loss_kernel, dim3(1), dim3(256), 0, sd, 1, oa, h->se, k, d_loss);
     }
     auto fork_after_dgrad = [&](int i) -> int {      // dact of the next layer down is ready on `st`
       DQN_CUDA(cudaEventRecord(h->ev_fork[i], st));
@@ -1238,17 +1234,17 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
     if (mode >= 1) {
       dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
       StageScope sc(h, DQN_STAGE_REDUCE_GRAD, st);
-      reduce_grad_kernel<<<grid, 256, 0, st>>>(
-          oa, mode == 2 ? h->dp_grad : h->grad, include_reg ? h->hyper.reg_param : 0.f, mode == 2 ? 1 : 0,
-          mode == 2 ? PublishArgs{h->dp_peer_flags_dev, h->dp_counter, h->dp_rank, h->dp_world}
-                    : PublishArgs{nullptr, nullptr, 0, 1});
+      launch_pdl(reduce_grad_kernel, grid, dim3(256), 0, st, 1, oa, mode == 2 ? h->dp_grad : h->grad,
+                 include_reg ? h->hyper.reg_param : 0.f, mode == 2 ? 1 : 0,
+                 mode == 2 ? PublishArgs{h->dp_peer_flags_dev, h->dp_counter, h->dp_rank, h->dp_world}
+                           : PublishArgs{nullptr, nullptr, 0, 1});
     }
   }
   if (mode == 0) {
     dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
     {
       StageScope sc(h, DQN_STAGE_OPTIMIZER, st);
-      optimizer_kernel<<<grid, 256, 0, st>>>(oa);
+      launch_pdl(optimizer_kernel, grid, dim3(256), 0, st, 1, oa);
     }
   }
   if (mode == 2) {
@@ -1263,7 +1259,7 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
     oa.P = h->P;
     dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
     StageScope sc(h, DQN_STAGE_OPTIMIZER, st);
-    optimizer_kernel<<<grid, 256, 0, st>>>(oa);
+    launch_pdl(optimizer_kernel, grid, dim3(256), 0, st, 1, oa);
   }
   DQN_CUDA(cudaGetLastError());
   return 0;

@@ -83,6 +83,7 @@ gather_stack4_u8_kernel(RingView rv, const int32_t* __restrict__ idx, int32_t k,
                         uint8_t* __restrict__ states, uint8_t* __restrict__ next_states,
                         int32_t* __restrict__ actions, double* __restrict__ rewards,
                         uint8_t* __restrict__ terminals) {
+  pdl_wait();
   const int64_t total = (int64_t)k * chunks;
   const int64_t head = rv.state[0];
   const TransitionRec* meta = static_cast<const TransitionRec*>(rv.meta);
@@ -461,9 +462,8 @@ extern "C" int dqn_replay_gather(dqn_replay_t h, const int32_t* d_logical_idx, i
     int64_t blocks = (total + threads - 1) / threads;
     int64_t maxb = (int64_t)h->num_sms * 32;
     if (blocks > maxb) blocks = maxb;
-    gather_stack4_u8_kernel<<<(unsigned)blocks, threads, 0, st>>>(
-        rv, d_logical_idx, k, chunks, static_cast<uint8_t*>(d_states), static_cast<uint8_t*>(d_next_states),
-        d_actions, d_rewards, d_terminals);
+    launch_pdl(gather_stack4_u8_kernel, dim3((unsigned)blocks), dim3(threads), 0, st, 1, rv, d_logical_idx, k, chunks,
+               static_cast<uint8_t*>(d_states), static_cast<uint8_t*>(d_next_states), d_actions, d_rewards, d_terminals);
   } else {
     const int elems = h->frame_bytes / h->elem_bytes;
     int64_t total = (int64_t)k * elems;

@@ -271,12 +271,13 @@ __global__ void __launch_bounds__(TT) umma_fwd_kernel(FwdArgsT a) {
   const TIn* __restrict__ x = static_cast<const TIn*>(P.x);
   const int tid = threadIdx.x;
   const int m0 = blockIdx.x * TM, n0 = blockIdx.y * NTILE;
-  for (int j = tid; j < NTILE; j += TT) bias_sm[j] = __ldg(P.bias + n0 + j);
   const uint32_t tmem = setup(bars, &tmem_slot, tmem_cols(NTILE));
   const uint32_t sbase = smem_u32(smem);
   // gather mapping (lanes along the contiguous k direction): chunk id = tid + 512*q -> row id>>3, chunk id&7
   const Row grow0 = decode_row<G>(m0 + (tid >> 3), a.B), grow1 = decode_row<G>(m0 + 64 + (tid >> 3), a.B);
   const int gc = tid & 7;
+  pdl_wait();                                           // everything above overlapped the previous kernel
+  for (int j = tid; j < NTILE; j += TT) bias_sm[j] = __ldg(P.bias + n0 + j);
   // convert / epilogue mapping: tile row tid&127
   const int arow = tid & (TM - 1), ac0 = (tid >> 7) * 2;
   constexpr int T = (G::K + TK - 1) / TK;
@@ -325,6 +326,7 @@ __global__ void __launch_bounds__(TT) umma_fwd_kernel(FwdArgsT a) {
     __syncthreads();
     if (tid == 0) issue_stage<!U8, true>(tmem, a_addr, sbase + OFF_B + slot * B_STAGE, idesc, it == 0, &bars[par]);
   }
+  pdl_trigger();                                                // all loads issued: let the next kernel start its prologue
   // the last commit covers every MMA issued before it
   mbar_wait(&bars[(T - 1) & 1], ((T - 1) >> 1) & 1);
   tc_fence_after();
@@ -438,6 +440,7 @@ __global__ void __launch_bounds__(TT) umma_wgrad_kernel(WgradArgsT a) {
   for (int j = tid; j < NTILE; j += TT) bias_sm[j] = 0.f;
   const uint32_t tmem = setup(bars, &tmem_slot, tmem_cols(NTILE));
   const uint32_t sbase = smem_u32(smem);
+  pdl_wait();
   const int R = a.B * G::ROWS;
   const int r_begin = blockIdx.z * a.rows_per_split;
   const int r_end = min(R, r_begin + a.rows_per_split);
@@ -522,6 +525,7 @@ __global__ void __launch_bounds__(TT) umma_wgrad_kernel(WgradArgsT a) {
       issue_stage<false, false>(tmem, sbase + OFF_OPA + par * A_STAGE_BYTES, sbase + OFF_OPB + par * B_STAGE, idesc, it == 0,
                                 &bars[par]);
   }
+  pdl_trigger();
   float* out = a.partial + (size_t)blockIdx.z * ((size_t)(G::K + 1) * G::COUT);
   const int warp = tid >> 5, lane = tid & 31;
   const int k = i0 + (warp & 3) * 32 + lane;
@@ -618,6 +622,7 @@ __global__ void __launch_bounds__(TT) umma_dgrad_kernel(DgradArgsT a) {
   static_assert(KD % TK == 0, "dgrad reduction must be a multiple of the stage depth");
   constexpr int BCH = (NTILE * 8 + TT - 1) / TT;
   constexpr uint32_t idesc = make_idesc(TM, NTILE, false, false);
+  pdl_wait();
   auto issue = [&](int it) {
     if (it < T) {
       const int slot = it & (RS - 1);
@@ -685,6 +690,7 @@ __global__ void __launch_bounds__(TT) umma_dgrad_kernel(DgradArgsT a) {
     __syncthreads();
     if (tid == 0) issue_stage<!G::POOL, true>(tmem, a_addr, sbase + OFF_B + slot * B_STAGE, idesc, it == 0, &bars[par]);
   }
+  pdl_trigger();
   mbar_wait(&bars[(T - 1) & 1], ((T - 1) >> 1) & 1);
   tc_fence_after();
   const int warp = tid >> 5;
