@@ -993,8 +993,18 @@ static void launch_dgrad_tc(dqn_net_s* h, int l, int B, cudaStream_t st) {
   static bool once = (set_smem(umma::umma_dgrad_kernel<G, NTILE>, smem), true);
   (void)once;
   umma::DgradArgsT a{h->wd_bf + h->wd_off[l], h->dact_bf[l], l < 3 ? h->arg[0][l] : nullptr, h->act_bf[0][l - 1],
-                     h->dact_bf[l - 1], B};
-  dim3 grid((unsigned)((B * G::IH * G::IW + umma::TM - 1) / umma::TM), G::CIN / NTILE, 1);
+                     h->dact_bf[l - 1], B, {0, 0, 0, 0, 0}};
+  unsigned mtiles = (unsigned)((B * G::IH * G::IW + umma::TM - 1) / umma::TM);
+  if constexpr (G::ST == 2) {          // tiles are grouped by input-pixel parity class
+    int acc = 0;
+    for (int c = 0; c < 4; ++c) {
+      a.cls_tile[c] = acc;
+      acc += (B * umma::DgradClasses<G>::count(c) + umma::TM - 1) / umma::TM;
+    }
+    a.cls_tile[4] = acc;
+    mtiles = (unsigned)acc;
+  }
+  dim3 grid(mtiles, G::CIN / NTILE, 1);
   StageScope sc(h, DQN_STAGE_DGRAD_FC + 2 * (3 - l), st);
   launch_pdl(umma::umma_dgrad_kernel<G, NTILE>, grid, dim3(umma::TT), smem, st, 1, a);
 }

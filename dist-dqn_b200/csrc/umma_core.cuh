@@ -574,6 +574,19 @@ struct DgradArgsT {
   const __nv_bfloat16* act_prev;  // previous layer's pooled output: its ReLU gate is applied to dx here
   __nv_bfloat16* dx;              // [B, IH, IW, CIN] gated gradient of the previous layer's pooled output
   int B;
+  int cls_tile[5];                // stride-2 layers: first tile of each input-pixel parity class (see below)
+};
+
+// Stride-2 convolutions: an input pixel only receives gradient through the filter taps whose parity matches its own
+// ((iy + pad - ky) even), i.e. through (KS/2)^2 of the KS^2 taps.  Input pixels are therefore processed in 4 parity
+// classes (iy&1, ix&1); every tile belongs to one class and reduces over that class's taps only -- 4x fewer stages
+// than the dense formulation, whose other taps are all zero.
+template <class G>
+struct DgradClasses {
+  static constexpr int NY0 = (G::IH + 1) / 2, NY1 = G::IH / 2, NX0 = (G::IW + 1) / 2, NX1 = G::IW / 2;
+  __host__ __device__ static constexpr int ny(int c) { return (c >> 1) ? NY1 : NY0; }
+  __host__ __device__ static constexpr int nx(int c) { return (c & 1) ? NX1 : NX0; }
+  __host__ __device__ static constexpr int count(int c) { return ny(c) * nx(c); }
 };
 
 constexpr uint32_t DG_PD = 144, DG_PA = 72;                          // raw gradient / arg-max row pitches (8 chunks + pad)
@@ -600,25 +613,44 @@ __global__ void __launch_bounds__(TT) umma_dgrad_kernel(DgradArgsT a) {
   const int m0 = blockIdx.x * TM, c0t = blockIdx.y * NTILE;
   const uint32_t tmem = setup(bars, &tmem_slot, tmem_cols(NTILE));
   const uint32_t sbase = smem_u32(smem);
-  const int M = a.B * G::IH * G::IW;
+  constexpr bool S2 = G::ST == 2;                     // parity-class formulation
+  static_assert(!S2 || (G::KS % 2 == 0 && G::COUT == TK), "stride-2 path: even filter, one tap per stage");
+  // which rows does this tile cover?  dense: m0 + r over all input pixels; S2: r-th pixel of parity class `cls`
+  int cls = 0, row0 = m0;
+  if constexpr (S2) {
+    while (cls < 3 && (int)blockIdx.x >= a.cls_tile[cls + 1]) ++cls;
+    row0 = ((int)blockIdx.x - a.cls_tile[cls]) * TM;
+  }
+  const int cy = cls >> 1, cx = cls & 1;
+  auto decode = [&](int r, int& b, int& iy, int& ix) -> bool {
+    if constexpr (S2) {
+      const int nxc = DgradClasses<G>::nx(cls), cnt = DgradClasses<G>::count(cls);
+      b = r / cnt;
+      const int rem = r - b * cnt;
+      const int yy = rem / nxc;
+      iy = 2 * yy + cy;
+      ix = 2 * (rem - yy * nxc) + cx;
+      return r < a.B * cnt;
+    } else {
+      b = r / (G::IH * G::IW);
+      const int rem = r - b * (G::IH * G::IW);
+      iy = rem / G::IW;
+      ix = rem - iy * G::IW;
+      return r < a.B * G::IH * G::IW;
+    }
+  };
   // gather mapping: chunk id = tid + 512*q -> tile row id>>3, reduction chunk id&7 (8 lanes = 128 contiguous bytes)
   const int gc = tid & 7;
   int gb[2], giy[2], gix[2];
   bool gvalid[2];
 #pragma unroll
-  for (int q = 0; q < 2; ++q) {
-    const int mm = m0 + (tid >> 3) + 64 * q;
-    gb[q] = mm / (G::IH * G::IW);
-    const int rem = mm - gb[q] * (G::IH * G::IW);
-    giy[q] = rem / G::IW;
-    gix[q] = rem - giy[q] * G::IW;
-    gvalid[q] = mm < M;
-  }
+  for (int q = 0; q < 2; ++q) gvalid[q] = decode(row0 + (tid >> 3) + 64 * q, gb[q], giy[q], gix[q]);
   // route / epilogue mapping: tile row tid&127
   const int arow = tid & (TM - 1), ac0 = (tid >> 7) * 2;
-  const int m = m0 + arow;
-  const bool mvalid = m < M;
-  constexpr int T = KD / TK;
+  int eb, eiy, eix;
+  const bool mvalid = decode(row0 + arow, eb, eiy, eix);
+  const int m = (eb * G::IH + eiy) * G::IW + eix;
+  constexpr int T = S2 ? (G::KS / 2) * (G::KS / 2) : KD / TK;
   static_assert(KD % TK == 0, "dgrad reduction must be a multiple of the stage depth");
   constexpr int BCH = (NTILE * 8 + TT - 1) / TT;
   constexpr uint32_t idesc = make_idesc(TM, NTILE, false, false);
@@ -626,8 +658,17 @@ __global__ void __launch_bounds__(TT) umma_dgrad_kernel(DgradArgsT a) {
   auto issue = [&](int it) {
     if (it < T) {
       const int slot = it & (RS - 1);
-      const int kc8 = it * 8 + gc;
-      const int nq = kc8 % CC, t = kc8 / CC;
+      int nq, t;
+      if constexpr (S2) {        // stage = one of the class's taps: ky = (1-cy) + 2a, kx = (1-cx) + 2b  (pad is 1)
+        static_assert(!S2 || (G::PADH == 1 && G::PADW == 1), "parity classes assume pad 1");
+        const int ta = it / (G::KS / 2), tb = it % (G::KS / 2);
+        t = ((1 - cy) + 2 * ta) * G::KS + (1 - cx) + 2 * tb;
+        nq = gc;
+      } else {
+        const int kc8 = it * 8 + gc;
+        nq = kc8 % CC;
+        t = kc8 / CC;
+      }
       const int kx = t % G::KS, ky = t / G::KS;
 #pragma unroll
       for (int q = 0; q < 2; ++q) {
@@ -658,7 +699,8 @@ __global__ void __launch_bounds__(TT) umma_dgrad_kernel(DgradArgsT a) {
       for (int q = 0; q < BCH; ++q) {
         const int ch = tid + TT * q, n = ch >> 3, kc = ch & 7;
         if (ch < NTILE * 8)
-          cp_async16(sbase + OFF_B + slot * B_STAGE + sw128_off(n, kc), a.wd + (size_t)(c0t + n) * KD + it * TK + kc * 8, true);
+          cp_async16(sbase + OFF_B + slot * B_STAGE + sw128_off(n, kc),
+                     a.wd + (size_t)(c0t + n) * KD + (S2 ? t * G::COUT : it * TK) + kc * 8, true);
       }
     }
     cp_async_commit();
