@@ -185,8 +185,10 @@ struct OptArgs {
   // double-buffered exchange block that all ranks have mapped; flags[p] = last step whose gradient rank p published
   int world;
   const float* peer_grad[8];             // exchange gradient buffers of all ranks ([2][P] floats each), rank order
-  const unsigned long long* flags;       // this rank's flag array (written by the peers)
+  const unsigned long long* flags;       // this rank's flag arrays (written by the peers): slot 0 = [0..7], slot 1 = [8..15]
   long long P;
+  int peer_mask;                         // bit s set: segment s is summed over the ranks here; clear: already summed locally
+  int flag_slot;                         // which flag array guards the peer-summed segments
 };
 
 __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
@@ -224,7 +226,7 @@ __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs a) {
     if (threadIdx.x == 0) {
       const long long t0 = clock64();
       for (int r = 0; r < a.world; ++r) {
-        while (ld_acquire_sys(a.flags + r) < (unsigned long long)step) {
+        while (ld_acquire_sys(a.flags + 8 * a.flag_slot + r) < (unsigned long long)step) {
           if (clock64() - t0 > 8000000000LL) __trap();
         }
       }
@@ -235,7 +237,7 @@ __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs a) {
   const size_t p = (size_t)s.off + i;
   float w = a.w[p];
   float g;
-  if (a.world > 1) {
+  if (a.world > 1 && ((a.peer_mask >> blockIdx.y) & 1)) {
     const size_t gi = (size_t)(step & 1) * (size_t)a.P + p;
     g = 0.f;
     for (int r = 0; r < a.world; ++r) g += ld_relaxed_sys(a.peer_grad[r] + gi);     // rank order: identical on every rank
@@ -310,12 +312,14 @@ struct PublishArgs {
   unsigned long long* const* peer_flags;   // null: nothing to publish
   unsigned int* done_counter;              // blocks finished so far (reset by the last one)
   int rank, world;
+  int flag_slot;                           // flag array to raise: 0 = early segments, 1 = final segment(s)
+  int seg_base;                            // first segment this launch covers (gridDim.y segments)
 };
 
 __global__ void __launch_bounds__(256) reduce_grad_kernel(OptArgs a, float* __restrict__ grad, float reg, int by_parity,
                                                           PublishArgs pub) {
   pdl_wait();
-  const Seg s = a.seg[blockIdx.y];
+  const Seg s = a.seg[blockIdx.y + pub.seg_base];
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (by_parity) grad += (size_t)(*a.step & 1) * (size_t)a.P;     // exchange block: buffer of this step's parity
   if (i < s.len) {
@@ -338,10 +342,37 @@ __global__ void __launch_bounds__(256) reduce_grad_kernel(OptArgs a, float* __re
       if ((int)threadIdx.x < pub.world) {
         __threadfence_system();
         const unsigned long long v = (unsigned long long)*a.step;
-        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(pub.peer_flags[threadIdx.x] + pub.rank), "l"(v) : "memory");
+        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(pub.peer_flags[threadIdx.x] + 8 * pub.flag_slot + pub.rank),
+                     "l"(v)
+                     : "memory");
       }
     }
   }
+}
+
+// Early half of the data-parallel exchange: sums the already published segments of all ranks into the local flat
+// gradient buffer while the data-gradient chain is still running; the optimizer then only has to exchange what the
+// last kernel of the step produces.
+__global__ void __launch_bounds__(256) peer_sum_kernel(OptArgs a, int seg_base, float* __restrict__ gsum) {
+  pdl_wait();
+  const Seg s = a.seg[blockIdx.y + seg_base];
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const long long step = *a.step;
+  if (threadIdx.x == 0) {
+    const long long t0 = clock64();
+    for (int r = 0; r < a.world; ++r) {
+      while (ld_acquire_sys(a.flags + 8 * a.flag_slot + r) < (unsigned long long)step) {
+        if (clock64() - t0 > 8000000000LL) __trap();
+      }
+    }
+  }
+  __syncthreads();
+  if (i >= s.len) return;
+  const size_t p = (size_t)s.off + i;
+  const size_t gi = (size_t)(step & 1) * (size_t)a.P + p;
+  float g = 0.f;
+  for (int r = 0; r < a.world; ++r) g += ld_relaxed_sys(a.peer_grad[r] + gi);      // rank order: identical on every rank
+  gsum[p] = g;
 }
 
 // loss = mean_b se_b + reg * sum_{reg tensors} ||w||^2 / 2   (network.py:150-152); one CTA.
@@ -582,8 +613,8 @@ struct dqn_net_s {
   unsigned int* dp_counter = nullptr;                 // finished-block counter of the publishing reduce kernel
   // weight-gradient kernels run on a forked stream, concurrently with the data-gradient chain (captured into the
   // step's CUDA graph as a parallel branch)
-  cudaStream_t side = nullptr;
-  cudaEvent_t ev_fork[3] = {}, ev_join = nullptr;
+  cudaStream_t side = nullptr, side2 = nullptr;     // side2: early half of the data-parallel exchange
+  cudaEvent_t ev_fork[3] = {}, ev_join = nullptr, ev_x = nullptr, ev_join2 = nullptr;
   // bf16 tensor-core mode (precision == 1; DQN_ARCH_CNN only)
   int precision = 0;
   __nv_bfloat16* act_bf[2][4] = {};
@@ -734,6 +765,9 @@ extern "C" int dqn_net_create(dqn_net_t* out, int32_t arch, const int32_t* in_sh
     }
     NET_ALLOC(h->head_partial, (size_t)(h->F + 1) * A * 4);
     cudaError_t e = cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->side2, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_x, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_join2, cudaEventDisableTiming);
     for (int i = 0; i < 3 && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&h->ev_fork[i], cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming);
     if (e != cudaSuccess) {
@@ -755,6 +789,9 @@ extern "C" int dqn_net_destroy(dqn_net_t h) {
     if (h->dp_peer_block[r] && h->dp_peer_block[r] != h->dp_block) cudaIpcCloseMemHandle(h->dp_peer_block[r]);
   if (h->dp_block) cudaFree(h->dp_block);
   if (h->side) cudaStreamDestroy(h->side);
+  if (h->side2) cudaStreamDestroy(h->side2);
+  if (h->ev_x) cudaEventDestroy(h->ev_x);
+  if (h->ev_join2) cudaEventDestroy(h->ev_join2);
   for (int i = 0; i < 3; ++i) if (h->ev_fork[i]) cudaEventDestroy(h->ev_fork[i]);
   if (h->ev_join) cudaEventDestroy(h->ev_join);
   for (int i = 0; i < DQN_NUM_STAGES; ++i) {
@@ -1161,13 +1198,13 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       // grad already holds the data term; add reg*w in place through the reduce kernel (partial == grad)
       dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
       StageScope sc(h, DQN_STAGE_REDUCE_GRAD, st);
-      reduce_grad_kernel<<<grid, 256, 0, st>>>(oa, h->grad, h->hyper.reg_param, 0, PublishArgs{nullptr, nullptr, 0, 1});
+      reduce_grad_kernel<<<grid, 256, 0, st>>>(oa, h->grad, h->hyper.reg_param, 0, PublishArgs{nullptr, nullptr, 0, 1, 0, 0});
     }
     if (mode == 2) {
       dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
       StageScope sc(h, DQN_STAGE_REDUCE_GRAD, st);
       reduce_grad_kernel<<<grid, 256, 0, st>>>(oa, h->dp_grad, 0.f, 1,      // copy into this step's exchange buffer + publish
-                                               PublishArgs{h->dp_peer_flags_dev, h->dp_counter, h->dp_rank, h->dp_world});
+                                               PublishArgs{h->dp_peer_flags_dev, h->dp_counter + 1, h->dp_rank, h->dp_world, 1, 0});
     }
   } else {
     const bool nat = h->arch == DQN_ARCH_NATURE;
@@ -1207,6 +1244,30 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       StageScope sc(h, DQN_STAGE_LOSS, sd);
       launch_pdl(loss_kernel, dim3(1), dim3(256), 0, sd, 1, oa, h->se, k, d_loss);
     }
+    // data-parallel: as soon as the gradients of conv3, fc and the head (segments 2..4, 72% of the parameters) exist,
+    // a third stream publishes them and sums them over the ranks into the local flat gradient buffer, in the shadow
+    // of the rest of the backward pass
+    auto early_exchange = [&]() -> int {
+      if (mode != 2) return 0;
+      cudaStream_t s2 = h->side2;
+      DQN_CUDA(cudaEventRecord(h->ev_x, sd));
+      DQN_CUDA(cudaStreamWaitEvent(s2, h->ev_x, 0));
+      OptArgs ea;
+      fill_segs(h, &ea, nsplit, false);
+      ea.world = h->dp_world;
+      for (int r = 0; r < h->dp_world; ++r)
+        ea.peer_grad[r] = reinterpret_cast<const float*>(static_cast<const char*>(h->dp_peer_block[r]) + 256);
+      ea.flags = static_cast<const unsigned long long*>(h->dp_block);
+      ea.flag_slot = 0;
+      dim3 g3((max_seg_len(ea) + 255) / 256, 3);
+      dqn::count_launch();
+      launch_pdl(reduce_grad_kernel, g3, dim3(256), 0, s2, 1, ea, h->dp_grad, 0.f, 1,
+                 PublishArgs{h->dp_peer_flags_dev, h->dp_counter, h->dp_rank, h->dp_world, 0, 2});
+      dqn::count_launch();
+      launch_pdl(peer_sum_kernel, g3, dim3(256), 0, s2, 1, ea, 2, h->grad);
+      DQN_CUDA(cudaEventRecord(h->ev_join2, s2));
+      return 0;
+    };
     auto fork_after_dgrad = [&](int i) -> int {      // dact of the next layer down is ready on `st`
       DQN_CUDA(cudaEventRecord(h->ev_fork[i], st));
       DQN_CUDA(cudaStreamWaitEvent(sd, h->ev_fork[i], 0));
@@ -1216,6 +1277,7 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       launch_wgrad_tc<F4, __nv_bfloat16, 128>(h, 3, h->act_bf[0][2], k, sd, &nsplit[3]); launch_dgrad_tc<F4, 256>(h, 3, k, st);
       if (fork_after_dgrad(1)) return DQN_ERR_CUDA;
       launch_wgrad_tc<C3, __nv_bfloat16, 64>(h, 2, h->act_bf[0][1], k, sd, &nsplit[2]); launch_dgrad_tc<C3, 64>(h, 2, k, st);
+      if (early_exchange()) return DQN_ERR_CUDA;
       if (fork_after_dgrad(2)) return DQN_ERR_CUDA;
       launch_wgrad_tc<C2, __nv_bfloat16, 64>(h, 1, h->act_bf[0][0], k, sd, &nsplit[1]); launch_dgrad_tc<C2, 32>(h, 1, k, st);
       launch_wgrad_tc<C1, uint8_t, 32>(h, 0, d_states, k, st, &nsplit[0]);
@@ -1223,6 +1285,7 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       launch_wgrad<NF, float>(h, 3, h->act[0][2], k, sd, &nsplit[3]); launch_dgrad<NF>(h, 3, k, st);
       if (fork_after_dgrad(1)) return DQN_ERR_CUDA;
       launch_wgrad<N3, float>(h, 2, h->act[0][1], k, sd, &nsplit[2]); launch_dgrad<N3>(h, 2, k, st);
+      if (early_exchange()) return DQN_ERR_CUDA;
       if (fork_after_dgrad(2)) return DQN_ERR_CUDA;
       launch_wgrad<N2, float>(h, 1, h->act[0][0], k, sd, &nsplit[1]); launch_dgrad<N2>(h, 1, k, st);
       if (u8) launch_wgrad<N1, uint8_t>(h, 0, d_states, k, st, &nsplit[0]);
@@ -1231,23 +1294,36 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       launch_wgrad<F4, float>(h, 3, h->act[0][2], k, sd, &nsplit[3]); launch_dgrad<F4>(h, 3, k, st);
       if (fork_after_dgrad(1)) return DQN_ERR_CUDA;
       launch_wgrad<C3, float>(h, 2, h->act[0][1], k, sd, &nsplit[2]); launch_dgrad<C3>(h, 2, k, st);
+      if (early_exchange()) return DQN_ERR_CUDA;
       if (fork_after_dgrad(2)) return DQN_ERR_CUDA;
       launch_wgrad<C2, float>(h, 1, h->act[0][0], k, sd, &nsplit[1]); launch_dgrad<C2>(h, 1, k, st);
       if (u8) launch_wgrad<C1, uint8_t>(h, 0, d_states, k, st, &nsplit[0]);
       else launch_wgrad<C1, float>(h, 0, d_states, k, st, &nsplit[0]);
     }
+    fill_segs(h, &oa, nsplit, false);
     // join
     DQN_CUDA(cudaEventRecord(h->ev_join, sd));
     DQN_CUDA(cudaStreamWaitEvent(st, h->ev_join, 0));
     DQN_CUDA(cudaGetLastError());
-    fill_segs(h, &oa, nsplit, false);
-    if (mode >= 1) {
+    if (mode == 2) {
+      // late half of the exchange: conv1 and conv2 (segments 0, 1) are published here and summed by the optimizer
+      oa.world = h->dp_world;
+      for (int r = 0; r < h->dp_world; ++r)
+        oa.peer_grad[r] = reinterpret_cast<const float*>(static_cast<const char*>(h->dp_peer_block[r]) + 256);
+      oa.flags = static_cast<const unsigned long long*>(h->dp_block);
+      dim3 g01((max_seg_len(oa) + 255) / 256, 2);
+      {
+        StageScope sc(h, DQN_STAGE_REDUCE_GRAD, st);
+        launch_pdl(reduce_grad_kernel, g01, dim3(256), 0, st, 1, oa, h->dp_grad, 0.f, 1,
+                   PublishArgs{h->dp_peer_flags_dev, h->dp_counter + 1, h->dp_rank, h->dp_world, 1, 0});
+      }
+      DQN_CUDA(cudaStreamWaitEvent(st, h->ev_join2, 0));
+    }
+    if (mode == 1) {
       dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
       StageScope sc(h, DQN_STAGE_REDUCE_GRAD, st);
-      launch_pdl(reduce_grad_kernel, grid, dim3(256), 0, st, 1, oa, mode == 2 ? h->dp_grad : h->grad,
-                 include_reg ? h->hyper.reg_param : 0.f, mode == 2 ? 1 : 0,
-                 mode == 2 ? PublishArgs{h->dp_peer_flags_dev, h->dp_counter, h->dp_rank, h->dp_world}
-                           : PublishArgs{nullptr, nullptr, 0, 1});
+      launch_pdl(reduce_grad_kernel, grid, dim3(256), 0, st, 1, oa, h->grad, include_reg ? h->hyper.reg_param : 0.f, 0,
+                 PublishArgs{nullptr, nullptr, 0, 1, 0, 0});
     }
   }
   if (mode == 0) {
@@ -1267,6 +1343,9 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       oa.peer_grad[r] = reinterpret_cast<const float*>(static_cast<const char*>(h->dp_peer_block[r]) + 256);
     oa.flags = static_cast<const unsigned long long*>(h->dp_block);
     oa.P = h->P;
+    oa.flag_slot = 1;
+    // conv nets: only segments 0, 1 (conv1, conv2) are still to be summed over the ranks; the MLP exchanges everything here
+    oa.peer_mask = h->arch == DQN_ARCH_SIMPLE ? 0x7 : 0x3;
     dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
     StageScope sc(h, DQN_STAGE_OPTIMIZER, st);
     launch_pdl(optimizer_kernel, grid, dim3(256), 0, st, 1, oa);
