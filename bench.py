@@ -276,6 +276,7 @@ def run_b200(args):
     with torch.cuda.stream(side):
         fill_ring(rm.handle, args.capacity, 100 + rank, dev, c.current_stream())
         torch.cuda.synchronize()
+        rm._resync()
         size = rm.size()
         assert size == args.capacity, size
 
@@ -580,8 +581,8 @@ def run_e2e(args, cfg, net, rm, world, dev, DQNAgent, FrameBuffer, dist):
             nxt = fb.get_state()
             rm.add(state, fi % A_PONG, float(fi % 3 - 1), nxt, False)
             state = nxt
-        agent._train_minibatch(batch)          # summary_freq=1 -> reads the loss back every step
-        return agent.last_loss
+        agent._train_minibatch(batch)          # summary_freq=1 -> the loss of every update is read back to the host
+        return agent.last_loss                 # (asynchronously: it is picked up while the next update is prepared)
 
     for _ in range(warm):
         one()
@@ -597,13 +598,16 @@ def run_e2e(args, cfg, net, rm, world, dev, DQNAgent, FrameBuffer, dist):
         t = torch.tensor([dt], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dt = float(t.item())
+    agent.flush_summaries()
+    loss = agent.last_loss
     assert loss is not None and np.isfinite(loss)
     agent._graphs.clear()
     h2d = cfg.update_freq * (FRAME + 32) + 16 + batch * 4
     return {"value": n / dt, "unit": "updates/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
             "steps": n, "ms_per_step": dt / n * 1e3,
             "path": "FrameBuffer.append/get_state + ReplayMemory.add x%d (host uint8 frames) + DQNAgent._train_minibatch "
-                    "(random.sample on host, loss read back each step)" % cfg.update_freq}
+                    "(random.sample on host; every update's loss is copied to pinned host memory and collected one "
+                    "update later)" % cfg.update_freq}
 
 
 _REAL_STDOUT = None

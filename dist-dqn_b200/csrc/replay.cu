@@ -414,6 +414,15 @@ extern "C" int dqn_replay_add(dqn_replay_t h, int64_t state_pos, int64_t next_po
   return 0;
 }
 
+extern "C" int dqn_replay_push(dqn_replay_t h, const void* host_frame, int32_t action, double reward, uint8_t terminal) {
+  DQN_REQUIRE(h && host_frame, DQN_ERR_INVALID, "push: NULL argument");
+  DQN_REQUIRE(h->total_frames >= h->S, DQN_ERR_STATE, "push: the ring does not hold a complete state stack yet");
+  int64_t pos = 0;
+  int rc = dqn_replay_append_frames(h, host_frame, 1, &pos);
+  if (rc) return rc;
+  return dqn_replay_add(h, pos - 1, pos, action, reward, terminal);
+}
+
 extern "C" int dqn_replay_flush(dqn_replay_t h, dqn_stream_t stream) {
   DQN_REQUIRE(h, DQN_ERR_INVALID, "flush: NULL handle");
   DeviceGuard g(h->device);

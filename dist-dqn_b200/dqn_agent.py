@@ -67,6 +67,10 @@ class DQNAgent(object):
         self._graphs = {}
         self.use_cuda_graph = bool(getattr(config, 'cuda_graph', True))
         self.last_loss = None
+        # summaries are written one update late: the loss of update s is copied to pinned host memory asynchronously
+        # and picked up when update s+1 is launched, so the host never idles on the GPU (flush_summaries() drains it)
+        self.async_summary = bool(getattr(config, 'async_summary', True))
+        self._pending = None
 
         self._prefill_replay_memory(config.replay_start_size)     # dqn_agent.py:47
         self._update_target_network()                             # dqn_agent.py:50 (step 0 always syncs)
@@ -81,6 +85,7 @@ class DQNAgent(object):
             if supervisor and supervisor.should_stop():
                 logging.warning('Received signal to stop. Exiting train loop.')
                 break
+        self.flush_summaries()
 
     def train_episode(self, max_steps):
         state = self._reset_episode()
@@ -111,17 +116,50 @@ class DQNAgent(object):
 
     # ------------------------------------------------------------------ the hot path (dqn_agent.py:108-143)
     def _train_minibatch(self, minibatch_size):
-        rm, net = self.replay_memory, self.network
+        rm = self.replay_memory
         if rm.size() < minibatch_size:
             return
-        d_idx = rm.upload_indices(rm.sample_indices(minibatch_size))     # random.sample on the global generator
+        indices = rm.sample_indices(minibatch_size)               # random.sample on the global generator
         want_loss = self._should_log_summary()
-        loss = self._device_step(minibatch_size, d_idx, want_loss)
+        loss = self._device_step(minibatch_size, indices, want_loss)
         if want_loss:
-            self.last_loss = float(loss.item())
-            self.summary_writer.add_summary(self.last_loss, self.training_steps)
+            if self.async_summary:
+                self._read_loss_later(loss, self.training_steps)
+            else:
+                self.last_loss = float(loss.item())
+                self.summary_writer.add_summary(self.last_loss, self.training_steps)
+        elif self._pending is not None:
+            self.flush_summaries()
         self.training_steps += 1
         self._update_target_network()
+
+    def _read_loss_later(self, loss, step):
+        import torch
+        if not hasattr(self, '_loss_pin'):
+            self._loss_pin = [torch.empty(1, dtype=torch.float32, pin_memory=True) for _ in range(2)]
+            self._loss_evt = [torch.cuda.Event(), torch.cuda.Event()]
+            self._loss_turn = 0
+        t = self._loss_turn
+        self._loss_pin[t].copy_(loss, non_blocking=True)          # device -> pinned host, async
+        self._loss_evt[t].record()
+        previous = self._pending
+        self._pending = (t, step)
+        self._loss_turn = t ^ 1
+        if previous is not None:
+            self._collect(previous)
+
+    def _collect(self, pending):
+        t, step = pending
+        self._loss_evt[t].synchronize()
+        self.last_loss = float(self._loss_pin[t].item())
+        if self.summary_writer is not None:
+            self.summary_writer.add_summary(self.last_loss, step)
+
+    def flush_summaries(self):
+        """Writes the summary of the most recent update (pending because summaries trail by one update)."""
+        if self._pending is not None:
+            pending, self._pending = self._pending, None
+            self._collect(pending)
 
     def _eager_step(self, k, d_idx, want_loss):
         net, rm = self.network, self.replay_memory
@@ -136,29 +174,41 @@ class DQNAgent(object):
         net.apply_gradients()
         return loss
 
-    def _device_step(self, k, d_idx, want_loss):
+    def _device_step(self, k, indices, want_loss):
+        """One update for the given logical sample indices (host list).  After two eager calls per (k, want_loss) the
+        step is replayed as a CUDA graph whose first node copies the indices from pinned host memory, so a replay
+        costs the host one small memcpy into that pinned buffer and one graph launch.  Two graphs alternate so that
+        the pinned buffer of the update in flight is never overwritten."""
         import torch
+        rm = self.replay_memory
         if not self.use_cuda_graph:
-            return self._eager_step(k, d_idx, want_loss)
+            return self._eager_step(k, rm.upload_indices(indices), want_loss)
         key = (k, bool(want_loss))
         g = self._graphs.get(key)
         if g is None:
-            # first call per shape runs eagerly (loads kernels, sizes buffers), the second is captured
-            self._graphs[key] = 'warm'
-            return self._eager_step(k, d_idx, want_loss)
-        if g == 'warm':
-            self.replay_memory.flush()
+            # first call per shape runs eagerly (loads kernels, sizes buffers); the next ones are captured
+            self._graphs[key] = []
+            return self._eager_step(k, rm.upload_indices(indices), want_loss)
+        if len(g) < 2:
+            rm.flush()
             torch.cuda.synchronize()
+            pin = torch.empty(k, dtype=torch.int32, pin_memory=True)
+            pin.numpy()[:] = indices
+            d_idx = torch.empty(k, dtype=torch.int32, device=self.network.device)
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph):
+                d_idx.copy_(pin, non_blocking=True)
                 out = self._eager_step(k, d_idx, want_loss)
-            self._graphs[key] = g = (graph, out, d_idx)
-        graph, out, captured_idx = g
-        if captured_idx.data_ptr() != d_idx.data_ptr():
-            captured_idx.copy_(d_idx)
-        self.replay_memory.flush()                                # staged frames go in before the graph reads the ring
-        graph.replay()
-        return out
+            g.append(dict(graph=graph, out=out, pin=pin, pin_np=pin.numpy(), d_idx=d_idx, evt=torch.cuda.Event(), used=False))
+        slot = g[self.training_steps & 1] if len(g) == 2 else g[-1]
+        if slot['used']:
+            slot['evt'].synchronize()                             # the previous replay of this graph has consumed its indices
+        slot['pin_np'][:] = indices
+        rm.flush()                                                # staged frames go in before the graph reads the ring
+        slot['graph'].replay()
+        slot['evt'].record()
+        slot['used'] = True
+        return slot['out']
 
     # ------------------------------------------------------------------ acting (dqn_agent.py:145-189)
     def _pick_action(self, state):

@@ -7,9 +7,23 @@ frame in the device ring (see replay_memory.py), so this class stays a small hos
 """
 import numpy as np
 
+try:                      # OpenCV is already a dependency of the reference (utils.resize_image); its channel merge is
+    import cv2            # a much faster interleave than np.stack for uint8 frames
+except ImportError:       # pragma: no cover
+    cv2 = None
+
 
 def _identity(frame):
     return frame
+
+
+def _stack_last(frames):
+    """np.stack(frames, axis=-1), through cv2.merge when that yields the identical array."""
+    f0 = frames[0]
+    if (cv2 is not None and isinstance(f0, np.ndarray) and f0.ndim == 2 and f0.dtype == np.uint8
+            and 2 <= len(frames) <= 4):
+        return cv2.merge(frames)
+    return np.stack(frames, axis=-1)
 
 
 class FrameBuffer(object):
@@ -42,7 +56,7 @@ class FrameBuffer(object):
             return None
         if self.frames_per_state == 1:
             return self._window[0]
-        return np.stack(self._window, axis=-1)
+        return _stack_last(self._window)
 
     def clear(self):
         self._window = []

@@ -58,5 +58,5 @@ def ingest(replay_memory, frames, actions, rewards, terminals, first_is_episode_
     for j in range(n):
         _c.check(_c.lib.dqn_replay_add(replay_memory.handle, p + j - 1, p + j, int(actions[j]), float(rewards[j]),
                                        1 if terminals[j] else 0), 'ingest')
-    replay_memory._last_next, replay_memory._last_next_pos = None, -1       # the host-side chain is broken
+    replay_memory._resync()                                                # counters moved; the host-side chain is broken
     return p

@@ -38,6 +38,9 @@ class ReplayMemory(object):
         self._last_next_pos = -1
         self._stack = None           # (frames_per_state, frame_shape, dtype) once known
         self._bufs = {}
+        self._size = 0               # host mirror of the ring's counters (saves ctypes round trips on the hot path)
+        self._frames_total = 0
+        self._scratch = None
 
     # ------------------------------------------------------------------ construction of the ring
     @staticmethod
@@ -94,10 +97,28 @@ class ReplayMemory(object):
         pos = _c.c_i64()
         _c.check(_c.lib.dqn_replay_append_frames(self._h, frames.ctypes.data, frames.shape[0], _c.C.byref(pos)),
                  "ReplayMemory.add")
+        self._frames_total = pos.value + frames.shape[0]
         return pos.value
 
     def add(self, state, action, reward, observation, terminal):
         """replay_memory.py:22-23.  ``observation`` is the next state."""
+        if (self._trusted and state is self._last_next and self._h is not None
+                and self._last_next_pos == self._frames_total - 1):
+            # fast lane (the agent loop, dqn_agent.py:96-100): one new frame, one C call
+            S = self._stack[0]
+            if S > 1:
+                np.copyto(self._scratch, observation[..., -1])
+                src = self._scratch
+            else:
+                src = np.ascontiguousarray(observation)
+            _c.check(_c.lib.dqn_replay_push(self._h, src.ctypes.data, int(action), float(reward), 1 if terminal else 0),
+                     "ReplayMemory.add")
+            self._last_next = observation
+            self._last_next_pos += 1
+            self._frames_total += 1
+            if self._size < self._capacity:
+                self._size += 1
+            return
         self._ensure(state)
         S = self._stack[0]
         if self._trusted:
@@ -123,13 +144,29 @@ class ReplayMemory(object):
                  "ReplayMemory.add")
         self._last_next = observation if self._trusted else np.array(observation, copy=True)
         self._last_next_pos = npos
+        if self._size < self._capacity:
+            self._size += 1
+        if self._scratch is None and S > 1:
+            self._scratch = np.empty(self._stack[1], self._stack[2])
 
     def size(self):
+        return self._size
+
+    def device_size(self):
+        """The ring's own counter (equals size(); used by tests and after device-side ingest)."""
         if self._h is None:
             return 0
         n = _c.c_i64()
         _c.lib.dqn_replay_size(self._h, _c.C.byref(n), None)
         return n.value
+
+    def _resync(self):
+        """Re-reads the counters from the library after frames / transitions were added behind the shell's back."""
+        n, p = _c.c_i64(), _c.c_i64()
+        _c.lib.dqn_replay_size(self._h, _c.C.byref(n), None)
+        _c.lib.dqn_replay_next_frame_pos(self._h, _c.C.byref(p))
+        self._size, self._frames_total = n.value, p.value
+        self._last_next, self._last_next_pos = None, -1
 
     def capacity(self):
         return self._capacity

@@ -107,6 +107,10 @@ int dqn_replay_append_frames_device(dqn_replay_t h, const void* d_frames, int32_
 /* Records one transition whose state / next_state stacks end at the given frame positions. */
 int dqn_replay_add(dqn_replay_t h, int64_t state_pos, int64_t next_pos, int32_t action, double reward,
                    uint8_t terminal);
+/* The common case of ReplayMemory.add in one call (dqn_agent.py:96-100: the transition's state is the previous
+ * transition's next_state): appends ONE host frame and records the transition from the stack that ended at the
+ * previous newest frame to the stack ending at the new one. */
+int dqn_replay_push(dqn_replay_t h, const void* host_frame, int32_t action, double reward, uint8_t terminal);
 /* Sends staged frames + records to the device (async H2D on stream). Called by gather itself. */
 int dqn_replay_flush(dqn_replay_t h, dqn_stream_t stream);
 /* ReplayMemory.size / capacity (replay_memory.py:25-29); host-side counters, no sync. */

@@ -84,7 +84,7 @@ def test_random_scripts_vs_oracle_including_unchained_stacks(seed):
         mine.add(state, a, r, nxt, t)
         ref.add(state, a, r, nxt, t)
         prev = nxt
-        assert mine.size() == ref.size()
+        assert mine.size() == ref.size() == mine.device_size()
         if step % 3 == 0:
             k = int(rng.integers(1, 8))
             st = random.getstate()
