@@ -111,10 +111,11 @@ td_head_kernel(const float* __restrict__ h_on, const float* __restrict__ h_tg, c
   }
 }
 
-// out[(F+1)*A]: rows 0..F-1 = dL/dw5 (data term), row F = dL/db5.
+// out[split][(F+1)*A]: rows 0..F-1 = dL/dw5 (data term), row F = dL/db5; blockIdx.y = batch split (partial sums are
+// added up in split order by the optimizer, like the conv wgrad partials).
 __global__ void __launch_bounds__(256)
 head_wgrad_kernel(const float* __restrict__ h_on, const float* __restrict__ g, const int32_t* __restrict__ actions,
-                  int B, int F, int A, float* __restrict__ out) {
+                  int Btot, int per_split, int F, int A, float* __restrict__ out) {
   pdl_trigger();
   pdl_wait();
   const int o = blockIdx.x * blockDim.x + threadIdx.x;
@@ -122,7 +123,9 @@ head_wgrad_kernel(const float* __restrict__ h_on, const float* __restrict__ g, c
   const int j = o / A, a = o - j * A;
   float acc[4] = {0.f, 0.f, 0.f, 0.f};      // 4 independent chains; summed in a fixed order
   const int jj = j < F ? j : 0;
-  int b = 0;
+  int b = blockIdx.y * per_split;
+  const int B = min(Btot, b + per_split);
+  out += (size_t)blockIdx.y * (size_t)((F + 1) * A);
   for (; b + 4 <= B; b += 4) {
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
@@ -593,7 +596,8 @@ struct dqn_net_s {
   float* act[2][4] = {};         // [pass][layer] pooled activations; layer 3 = fc output
   uint8_t* arg[2][3] = {};
   float* dact[4] = {};
-  float* head_partial = nullptr; // (F+1)*A
+  float* head_partial = nullptr; // [16][(F+1)*A]
+  int head_nsplit = 1;
   float *se = nullptr, *g = nullptr, *loss_tmp = nullptr, *q_tmp = nullptr;
   long long* step = nullptr;
   void *st_states = nullptr, *st_next = nullptr;
@@ -763,7 +767,7 @@ extern "C" int dqn_net_create(dqn_net_t* out, int32_t arch, const int32_t* in_sh
       NET_ALLOC(h->dact[l], (size_t)MB * h->L[l].out_elems * 4);
       NET_ALLOC(h->L[l].partial, (size_t)h->L[l].maxsplit * (h->L[l].K + 1) * h->L[l].N * 4);
     }
-    NET_ALLOC(h->head_partial, (size_t)(h->F + 1) * A * 4);
+    NET_ALLOC(h->head_partial, (size_t)16 * (h->F + 1) * A * 4);
     cudaError_t e = cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->side2, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_x, cudaEventDisableTiming);
@@ -1120,8 +1124,9 @@ static void fill_segs(dqn_net_s* h, OptArgs* o, const int nsplit[4], bool from_f
       o->seg[l] = s;
     }
     const Tensor& w5 = h->tensors[8];
-    Seg s{(long long)w5.off, (h->F + 1) * h->A, h->F * h->A, h->head_partial, 1, 0, nullptr, nullptr, 0, 0, 0};
-    if (from_flat_grad) s.partial = h->grad + w5.off;
+    Seg s{(long long)w5.off, (h->F + 1) * h->A, h->F * h->A, h->head_partial, h->head_nsplit,
+          (long long)(h->F + 1) * h->A, nullptr, nullptr, 0, 0, 0};
+    if (from_flat_grad) { s.partial = h->grad + w5.off; s.nsplit = 1; s.stride = 0; }
     o->seg[4] = s;
   }
   o->w = h->online; o->s0 = h->slot0; o->s1 = h->slot1; o->step = h->step;
@@ -1236,8 +1241,11 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
     DQN_CUDA(cudaStreamWaitEvent(sd, h->ev_fork[0], 0));
     {
     StageScope sc(h, DQN_STAGE_HEAD_WGRAD, sd);
-    launch_pdl(head_wgrad_kernel, dim3(((h->F + 1) * h->A + 255) / 256), dim3(256), 0, sd, 1, h->act[0][3], h->g, d_actions,
-               k, h->F, h->A, h->head_partial);
+    h->head_nsplit = (k + 31) / 32 > 16 ? 16 : (k + 31) / 32;
+    const int head_per = (k + h->head_nsplit - 1) / h->head_nsplit;
+    h->head_nsplit = (k + head_per - 1) / head_per;
+    launch_pdl(head_wgrad_kernel, dim3(((h->F + 1) * h->A + 255) / 256, h->head_nsplit), dim3(256), 0, sd, 1, h->act[0][3],
+               h->g, d_actions, k, head_per, h->F, h->A, h->head_partial);
     }
     if (d_loss) {
       fill_segs(h, &oa, nsplit, false);
