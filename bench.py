@@ -603,7 +603,7 @@ def run_e2e(args, cfg, net, rm, world, dev, DQNAgent, FrameBuffer, dist):
     assert loss is not None and np.isfinite(loss)
     agent._graphs.clear()
     h2d = cfg.update_freq * (FRAME + 32) + 16 + batch * 4
-    return {"value": n / dt, "unit": "updates/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
+    return {"value": world * n / dt, "unit": "updates/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
             "steps": n, "ms_per_step": dt / n * 1e3,
             "path": "FrameBuffer.append/get_state + ReplayMemory.add x%d (host uint8 frames) + DQNAgent._train_minibatch "
                     "(random.sample on host; every update's loss is copied to pinned host memory and collected one "
