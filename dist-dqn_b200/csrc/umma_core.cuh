@@ -55,6 +55,9 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       "}" ::"r"(smem_u32(bar)), "r"(parity)
       : "memory");
 }
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(smem_u32(bar)) : "memory");
+}
 __device__ __forceinline__ void fence_async_proxy() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -264,13 +267,18 @@ __global__ void __launch_bounds__(TT) umma_fwd_kernel(FwdArgsT a) {
   constexpr uint32_t B_STAGE = NTILE * 128;
   constexpr uint32_t OFF_OPA = U8 ? RS * FWD_RAW_A : 0;              // converted A tiles (uint8 input only), 2 slots
   constexpr uint32_t OFF_B = U8 ? RS * FWD_RAW_A + 2 * A_STAGE_BYTES : RS * A_STAGE_BYTES;
-  __shared__ uint64_t bars[2];
+  __shared__ uint64_t bars[2];        // MMAs of a stage parity have completed (tcgen05.commit)
+  __shared__ uint64_t full[RS];       // a ring slot is filled: one arrival per warp
   __shared__ uint32_t tmem_slot;
   __shared__ float bias_sm[NTILE];
   const FwdPassT P = a.p[blockIdx.z];
   const TIn* __restrict__ x = static_cast<const TIn*>(P.x);
   const int tid = threadIdx.x;
   const int m0 = blockIdx.x * TM, n0 = blockIdx.y * NTILE;
+  if (tid == 0) {
+#pragma unroll
+    for (int i = 0; i < RS; ++i) mbar_init(&full[i], TT / 32);
+  }
   const uint32_t tmem = setup(bars, &tmem_slot, tmem_cols(NTILE));
   const uint32_t sbase = smem_u32(smem);
   // gather mapping (lanes along the contiguous k direction): chunk id = tid + 512*q -> row id>>3, chunk id&7
@@ -278,29 +286,55 @@ __global__ void __launch_bounds__(TT) umma_fwd_kernel(FwdArgsT a) {
   const int gc = tid & 7;
   pdl_wait();                                           // everything above overlapped the previous kernel
   for (int j = tid; j < NTILE; j += TT) bias_sm[j] = __ldg(P.bias + n0 + j);
-  // convert / epilogue mapping: tile row tid&127
-  const int arow = tid & (TM - 1), ac0 = (tid >> 7) * 2;
-  constexpr int T = (G::K + TK - 1) / TK;
+  // epilogue mapping: tile row tid&127
+  const int arow = tid & (TM - 1);
+  constexpr int T = G::K / TK;
+  static_assert(G::K % TK == 0, "the reduction must be a whole number of stages");
   constexpr int BCH = (NTILE * 8 + TT - 1) / TT;      // weight chunks per thread per stage
   constexpr uint32_t idesc = make_idesc(TM, NTILE, false, false);
+  // Address generation is hoisted out of the stage loop (the gather is instruction-issue bound otherwise): per thread
+  // and row a base pointer at the window origin, per stage one (ky, kx, channel) offset shared by both rows.
+  constexpr int EPC = 8;                               // elements per chunk (8 bf16, or 2 pixels x 4 uint8)
+  const TIn* abase[2];
+  int aiy0[2], aix0[2];
+  bool avalid[2];
+  uint32_t adst[2];
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    const Row& r = q ? grow1 : grow0;
+    aiy0[q] = r.oy * G::ST - G::PADH;
+    aix0[q] = r.ox * G::ST - G::PADW;
+    avalid[q] = r.valid;
+    abase[q] = x + ((ptrdiff_t)(r.b * G::IH + aiy0[q]) * G::IW + aix0[q]) * G::CIN;     // may point outside: only used when in bounds
+    const int rr = (tid >> 3) + 64 * q;
+    adst[q] = U8 ? (uint32_t)(rr * FWD_RAW_PITCH + gc * 8) : sw128_off(rr, gc);
+  }
+  const __nv_bfloat16* bsrc[BCH];
+  uint32_t bdst[BCH];
+#pragma unroll
+  for (int q = 0; q < BCH; ++q) {
+    const int ch = tid + TT * q, n = ch >> 3, kc = ch & 7;
+    bsrc[q] = P.wt + (size_t)(n0 + (ch < NTILE * 8 ? n : 0)) * G::K + kc * 8;
+    bdst[q] = OFF_B + sw128_off(n, kc);
+  }
   auto issue = [&](int it) {
     if (it < T) {
       const int slot = it & (RS - 1);
+      // chunk (it*8 + gc) of the (ky, kx, c) reduction axis: which filter tap, which channel group
+      const int e = (it * 8 + gc) * EPC;               // first reduction element of this chunk
+      const int tap = e / G::CIN, c0 = e - tap * G::CIN;
+      const int ky = tap / G::KS, kx = tap - ky * G::KS;
+      const int delta = (ky * G::IW + kx) * G::CIN + c0;
 #pragma unroll
       for (int q = 0; q < 2; ++q) {
-        const int r = (tid >> 3) + 64 * q;
-        const TIn* src = x_chunk_ptr<G, TIn>(x, q ? grow1 : grow0, it * 8 + gc);
-        if constexpr (U8) cp_async8(sbase + slot * FWD_RAW_A + r * FWD_RAW_PITCH + gc * 8, src ? src : x, src != nullptr);
-        else cp_async16(sbase + slot * A_STAGE_BYTES + sw128_off(r, gc), src ? src : x, src != nullptr);
+        const bool ok = avalid[q] && (unsigned)(aiy0[q] + ky) < (unsigned)G::IH && (unsigned)(aix0[q] + kx) < (unsigned)G::IW;
+        const TIn* src = ok ? abase[q] + delta : x;
+        if constexpr (U8) cp_async8(sbase + slot * FWD_RAW_A + adst[q], src, ok);
+        else cp_async16(sbase + slot * A_STAGE_BYTES + adst[q], src, ok);
       }
 #pragma unroll
-      for (int q = 0; q < BCH; ++q) {
-        const int ch = tid + TT * q, n = ch >> 3, kc = ch & 7;
-        const int k = it * TK + kc * 8;
-        if (ch < NTILE * 8)
-          cp_async16(sbase + OFF_B + slot * B_STAGE + sw128_off(n, kc), P.wt + (size_t)(n0 + n) * G::K + (k < G::K ? k : 0),
-                     k < G::K);
-      }
+      for (int q = 0; q < BCH; ++q)
+        if (tid + TT * q < NTILE * 8) cp_async16(sbase + slot * B_STAGE + bdst[q], bsrc[q] + it * TK, true);
     }
     cp_async_commit();
   };
@@ -313,18 +347,29 @@ __global__ void __launch_bounds__(TT) umma_fwd_kernel(FwdArgsT a) {
     cp_async_wait<2>();                                         // this thread's copies for stage `it` have landed
     uint32_t a_addr;
     if constexpr (U8) {
-      __syncthreads();                                          // ... and everybody else's
+      // widen the two 8-byte chunks this thread fetched itself and store them swizzled (lanes run along the chunks
+      // of a row, which the 128-byte swizzle keeps bank-conflict free)
       uint8_t* opa = smem + OFF_OPA + par * A_STAGE_BYTES;
-      const uint4 u = *reinterpret_cast<const uint4*>(smem + slot * FWD_RAW_A + arow * FWD_RAW_PITCH + ac0 * 8);
-      *reinterpret_cast<uint4*>(opa + kmajor_off(arow, ac0)) = cvt_u8x8(make_uint2(u.x, u.y));
-      *reinterpret_cast<uint4*>(opa + kmajor_off(arow, ac0 + 1)) = cvt_u8x8(make_uint2(u.z, u.w));
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const int r = (tid >> 3) + 64 * q;
+        const uint2 u = *reinterpret_cast<const uint2*>(smem + slot * FWD_RAW_A + r * FWD_RAW_PITCH + gc * 8);
+        *reinterpret_cast<uint4*>(opa + sw128_off(r, gc)) = cvt_u8x8(u);
+      }
       a_addr = sbase + OFF_OPA + par * A_STAGE_BYTES;
     } else {
       a_addr = sbase + slot * A_STAGE_BYTES;
     }
+    // No CTA-wide barrier: every warp publishes "my part of this slot is written and visible to the tensor core"
+    // on the slot's mbarrier and moves on to the next stage; only the MMA-issuing thread waits for all 16 warps.
     fence_async_proxy();
-    __syncthreads();
-    if (tid == 0) issue_stage<!U8, true>(tmem, a_addr, sbase + OFF_B + slot * B_STAGE, idesc, it == 0, &bars[par]);
+    __syncwarp();
+    if ((tid & 31) == 0) mbar_arrive(&full[slot]);
+    if (tid == 0) {
+      mbar_wait(&full[slot], (it >> 2) & 1);
+      issue_stage<true, true>(tmem, a_addr, sbase + OFF_B + slot * B_STAGE, idesc, it == 0, &bars[par]);
+    }
+    __syncwarp();
   }
   pdl_trigger();                                                // all loads issued: let the next kernel start its prologue
   // the last commit covers every MMA issued before it
