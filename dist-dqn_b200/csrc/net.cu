@@ -14,6 +14,7 @@
 #include "common.cuh"
 #include "gemm_core.cuh"
 #include "umma_core.cuh"
+#include "fc_fused.cuh"
 
 #include <cmath>
 #include <cstdlib>
@@ -42,21 +43,6 @@ __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
-}
-
-__device__ __forceinline__ void td_terms(float q_sel, float maxq, double reward, bool terminal, double gamma, int B,
-                                         int loss_kind, float* se, float* g) {
-  // dqn_agent.py:242-246: python float64 arithmetic, rounded to float32 by the q_placeholder
-  const float y = (float)(reward + gamma * (terminal ? 0.0 : (double)maxq));
-  const float diff = q_sel - y;
-  if (loss_kind == DQN_LOSS_HUBER) {
-    const float ad = fabsf(diff);
-    *se = ad <= 1.f ? 0.5f * diff * diff : ad - 0.5f;
-    *g = fminf(fmaxf(diff, -1.f), 1.f) / (float)B;
-  } else {                                   // network.py:150  reduce_mean(squared_difference)
-    *se = diff * diff;
-    *g = 2.f * diff / (float)B;
-  }
 }
 
 // One warp per sample; lane l owns hidden units l, l+32, ... (FPL per lane, kept in registers so every load of the
@@ -302,10 +288,10 @@ __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs a) {
   if (s.wt && i < s.K * s.N) {
     const int k = i / s.N, n = i - k * s.N;
     const __nv_bfloat16 v = __float2bfloat16_rn(w);
-    s.wt[(size_t)n * s.K + k] = v;
+    s.wt[umma::img_index(n, k, s.N)] = v;
     if (s.wd) {
       const int t = k / s.CIN, c = k - t * s.CIN;
-      s.wd[((size_t)c * (s.K / s.CIN) + t) * s.N + n] = v;
+      s.wd[umma::img_index(c, t * s.N + n, s.CIN)] = v;
     }
   }
 }
@@ -418,7 +404,8 @@ __global__ void fill_kernel(float* p, long long n, float v) {
 }
 
 // bf16 copies of one layer's weights for the tensor-core path: wt[n][k] (forward: B operand, K-major) and
-// wd[c][(ky,kx,n)] (dgrad).  w is the fp32 master in TF layout [k=(ky,kx,c)][n].
+// wd[c][(ky,kx,n)] (dgrad), both stored as swizzled stage images (umma::img_index) so that a stage's tile is one
+// contiguous bulk copy.  w is the fp32 master in TF layout [k=(ky,kx,c)][n].
 struct CvtLayer { const float* w; __nv_bfloat16* wt; __nv_bfloat16* wd; int K, N, CIN; };
 struct CvtArgs { CvtLayer l[4]; };
 __global__ void __launch_bounds__(256) weights_to_bf16_kernel(CvtArgs a) {
@@ -427,11 +414,10 @@ __global__ void __launch_bounds__(256) weights_to_bf16_kernel(CvtArgs a) {
   if (i >= L.K * L.N) return;
   const int k = i / L.N, n = i - k * L.N;
   const __nv_bfloat16 v = __float2bfloat16_rn(L.w[i]);
-  L.wt[(size_t)n * L.K + k] = v;
+  L.wt[umma::img_index(n, k, L.N)] = v;
   if (L.wd) {
     const int t = k / L.CIN, c = k - t * L.CIN;
-    const int taps = L.K / L.CIN;
-    L.wd[((size_t)c * taps + t) * L.N + n] = v;
+    L.wd[umma::img_index(c, t * L.N + n, L.CIN)] = v;
   }
 }
 
@@ -618,7 +604,9 @@ struct dqn_net_s {
   // weight-gradient kernels run on a forked stream, concurrently with the data-gradient chain (captured into the
   // step's CUDA graph as a parallel branch)
   cudaStream_t side = nullptr, side2 = nullptr;     // side2: early half of the data-parallel exchange
-  cudaEvent_t ev_fork[3] = {}, ev_join = nullptr, ev_x = nullptr, ev_join2 = nullptr;
+  cudaStream_t side3 = nullptr;                     // head weight gradient + loss (fused fc/TD path)
+  bool no_fused_fc = true;                          // DQN_FUSED_FC=1: fc forward / TD head / fc dgrad as one launch (experimental)
+  cudaEvent_t ev_fork[3] = {}, ev_join = nullptr, ev_x = nullptr, ev_join2 = nullptr, ev_head = nullptr;
   // bf16 tensor-core mode (precision == 1; DQN_ARCH_CNN only)
   int precision = 0;
   __nv_bfloat16* act_bf[2][4] = {};
@@ -651,7 +639,7 @@ struct StageScope {
 static const char* kStageNames[DQN_NUM_STAGES] = {
     "gather", "fwd_conv1", "fwd_conv2", "fwd_conv3", "fwd_fc", "td_head", "head_wgrad", "loss",
     "wgrad_fc", "dgrad_fc", "wgrad_conv3", "dgrad_conv3", "wgrad_conv2", "dgrad_conv2", "wgrad_conv1",
-    "reduce_grad", "optimizer", "mlp_backward", "mlp_forward", "head_forward"};
+    "reduce_grad", "optimizer", "mlp_backward", "mlp_forward", "head_forward", "fc_td_fused"};
 
 static int refresh_bf16_weights(dqn_net_s* h, int set, cudaStream_t st);
 
@@ -770,6 +758,9 @@ extern "C" int dqn_net_create(dqn_net_t* out, int32_t arch, const int32_t* in_sh
     NET_ALLOC(h->head_partial, (size_t)16 * (h->F + 1) * A * 4);
     cudaError_t e = cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->side2, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->side3, cudaStreamNonBlocking);
+    { const char* nf = getenv("DQN_FUSED_FC"); h->no_fused_fc = !(nf && nf[0] == '1'); }
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_head, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_x, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_join2, cudaEventDisableTiming);
     for (int i = 0; i < 3 && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&h->ev_fork[i], cudaEventDisableTiming);
@@ -794,6 +785,8 @@ extern "C" int dqn_net_destroy(dqn_net_t h) {
   if (h->dp_block) cudaFree(h->dp_block);
   if (h->side) cudaStreamDestroy(h->side);
   if (h->side2) cudaStreamDestroy(h->side2);
+  if (h->side3) cudaStreamDestroy(h->side3);
+  if (h->ev_head) cudaEventDestroy(h->ev_head);
   if (h->ev_x) cudaEventDestroy(h->ev_x);
   if (h->ev_join2) cudaEventDestroy(h->ev_join2);
   for (int i = 0; i < 3; ++i) if (h->ev_fork[i]) cudaEventDestroy(h->ev_fork[i]);
@@ -999,13 +992,24 @@ static void set_smem(Kern kern, size_t bytes) {
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
 }
 
-template <class G, typename TIn, int NTILE>
-static void launch_fwd_tc(const umma::FwdArgsT& a, int npass, cudaStream_t st) {
-  constexpr size_t smem = umma::fwd_smem_bytes<TIn, NTILE>();
-  static bool once = (set_smem(umma::umma_fwd_kernel<G, TIn, NTILE>, smem), true);
+template <class G, typename TIn, int NTILE, int RSN, int PD>
+static void launch_fwd_tc_cfg(const umma::FwdArgsT& a, int npass, cudaStream_t st) {
+  constexpr size_t smem = umma::fwd_smem_bytes<TIn, NTILE, RSN>();
+  static_assert(smem <= 227 * 1024, "ring does not fit in shared memory");
+  static bool once = (set_smem(umma::umma_fwd_kernel<G, TIn, NTILE, RSN, PD>, smem), true);
   (void)once;
   dim3 grid((unsigned)((a.B * G::ROWS + umma::TM - 1) / umma::TM), G::COUT / NTILE, npass);
-  launch_pdl(umma::umma_fwd_kernel<G, TIn, NTILE>, grid, dim3(umma::TT), smem, st, 1, a);
+  launch_pdl(umma::umma_fwd_kernel<G, TIn, NTILE, RSN, PD>, grid, dim3(umma::TT), smem, st, 1, a);
+}
+// Ring depth: a grid of at most one CTA per SM is latency-bound (deep ring, loads far ahead of the MMAs); a grid of
+// several waves wants two CTAs resident per SM (small ring).  (Splitting the reduction of a tile over a cluster with a
+// DSMEM reduction was measured slower at B=32: the cluster launch and its two cluster barriers cost more than the
+// shorter main loop saves.)
+template <class G, typename TIn, int NTILE, int RS_DEEP, int PD_DEEP>
+static void launch_fwd_tc(const umma::FwdArgsT& a, int npass, int num_sms, cudaStream_t st) {
+  const long ctas = (long)((a.B * G::ROWS + umma::TM - 1) / umma::TM) * (G::COUT / NTILE) * npass;
+  if (ctas <= 2L * num_sms) launch_fwd_tc_cfg<G, TIn, NTILE, RS_DEEP, PD_DEEP>(a, npass, st);
+  else launch_fwd_tc_cfg<G, TIn, NTILE, 4, 2>(a, npass, st);
 }
 
 template <class G, typename TIn, int NTILE>
@@ -1071,8 +1075,9 @@ static int refresh_bf16_weights(dqn_net_s* h, int set, cudaStream_t st) {
   return 0;
 }
 
-static int run_trunk_tc(dqn_net_s* h, int npass, const void* const x[2], const int pass_id[2], int B, cudaStream_t st) {
-  for (int l = 0; l < 4; ++l) {
+static int run_trunk_tc(dqn_net_s* h, int npass, const void* const x[2], const int pass_id[2], int B, cudaStream_t st,
+                        int nlayers = 4) {
+  for (int l = 0; l < nlayers; ++l) {
     umma::FwdArgsT a;
     a.B = B;
     for (int p = 0; p < npass; ++p) {
@@ -1088,10 +1093,13 @@ static int run_trunk_tc(dqn_net_s* h, int npass, const void* const x[2], const i
     if (npass == 1) a.p[1] = a.p[0];
     StageScope sc(h, DQN_STAGE_FWD_CONV1 + l, st);
     switch (l) {
-      case 0: launch_fwd_tc<C1, uint8_t, 32>(a, npass, st); break;
-      case 1: launch_fwd_tc<C2, __nv_bfloat16, 64>(a, npass, st); break;
-      case 2: launch_fwd_tc<C3, __nv_bfloat16, 64>(a, npass, st); break;
-      case 3: launch_fwd_tc<F4, __nv_bfloat16, 256>(a, npass, st); break;
+      case 0: launch_fwd_tc<C1, uint8_t, 32, 4, 4>(a, npass, h->num_sms, st); break;
+      case 1: launch_fwd_tc<C2, __nv_bfloat16, 64, 8, 4>(a, npass, h->num_sms, st); break;
+      case 2: launch_fwd_tc<C3, __nv_bfloat16, 64, 8, 4>(a, npass, h->num_sms, st); break;
+      case 3:          // few rows: narrow tiles spread the weight traffic over more SMs (a lone CTA is bound by its SM's L2 port)
+        if (B <= 256) launch_fwd_tc<F4, __nv_bfloat16, 64, 4, 4>(a, npass, h->num_sms, st);
+        else launch_fwd_tc<F4, __nv_bfloat16, 256, 4, 4>(a, npass, h->num_sms, st);
+        break;
     }
   }
   DQN_CUDA(cudaGetLastError());
@@ -1217,10 +1225,30 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
     const void* xs[2] = {d_states, d_next};
     const float* ps[2] = {h->online, h->target};
     const int ids[2] = {0, 1};
-    int rc = h->precision == 1 ? run_trunk_tc(h, 2, xs, ids, k, st) : run_trunk(h, 2, xs, ps, ids, k, st);
+    // reference architecture in tensor-core mode: fc forward (both nets) + head + TD + fc data gradient are one kernel
+    const bool fused = h->precision == 1 && !nat && h->F == umma::FCF && h->A <= umma::FC_AP && !h->no_fused_fc;
+    int rc = h->precision == 1 ? run_trunk_tc(h, 2, xs, ids, k, st, fused ? 3 : 4) : run_trunk(h, 2, xs, ps, ids, k, st);
     if (rc) return rc;
     const float* w5 = h->online + h->tensors[8].off;
-    {
+    cudaStream_t sd = h->side;
+    cudaStream_t sh = fused ? h->side3 : h->side;      // head weight gradient + loss
+    if (fused) {
+      static bool once = (set_smem(umma::fc_td_fused_kernel, umma::FC_SMEM), true);
+      (void)once;
+      umma::FcFusedArgs fa;
+      fa.x[0] = h->act_bf[0][2]; fa.x[1] = h->act_bf[1][2];
+      fa.wt[0] = h->wt_bf[0] + h->wt_off[3]; fa.wt[1] = h->wt_bf[1] + h->wt_off[3];
+      fa.b4[0] = h->online + h->tensors[7].off; fa.b4[1] = h->target + h->tensors[7].off;
+      fa.w5[0] = w5; fa.w5[1] = h->target + h->tensors[8].off;
+      fa.b5[0] = h->online + h->tensors[9].off; fa.b5[1] = h->target + h->tensors[9].off;
+      fa.wd = h->wd_bf + h->wd_off[3];
+      fa.actions = d_actions; fa.rewards = d_rewards; fa.terminals = d_term;
+      fa.a4 = h->act[0][3]; fa.qout = d_q; fa.se = h->se; fa.g = h->g;
+      fa.dh_bf = h->dact_bf[3]; fa.dx = h->dact_bf[2];
+      fa.step = h->step; fa.gamma = h->hyper.gamma; fa.B = k; fa.A = h->A; fa.loss_kind = h->hyper.loss;
+      StageScope sc(h, DQN_STAGE_FC_TD_FUSED, st);
+      launch_pdl(umma::fc_td_fused_kernel, dim3((k + umma::TM - 1) / umma::TM), dim3(umma::TT), umma::FC_SMEM, st, 1, fa);
+    } else {
     StageScope sc(h, DQN_STAGE_TD_HEAD, st);
     if (h->F == 256)
       launch_pdl(td_head_kernel<8>, dim3((k + 7) / 8), dim3(256), 0, st, 1, h->act[0][3], h->act[1][3], w5, h->online + h->tensors[9].off,
@@ -1235,23 +1263,24 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
                                                       d_q, h->se, h->g, h->dact[3],
                                                       h->precision == 1 ? h->dact_bf[3] : nullptr, h->step);
     }
-    // fork: head/fc/conv3/conv2 weight gradients on the side stream, data-gradient chain + conv1 wgrad on `st`
-    cudaStream_t sd = h->side;
+    // fork: head/fc/conv3/conv2 weight gradients on the side stream(s), data-gradient chain + conv1 wgrad on `st`
     DQN_CUDA(cudaEventRecord(h->ev_fork[0], st));
     DQN_CUDA(cudaStreamWaitEvent(sd, h->ev_fork[0], 0));
+    if (fused) DQN_CUDA(cudaStreamWaitEvent(sh, h->ev_fork[0], 0));
     {
-    StageScope sc(h, DQN_STAGE_HEAD_WGRAD, sd);
+    StageScope sc(h, DQN_STAGE_HEAD_WGRAD, sh);
     h->head_nsplit = (k + 31) / 32 > 16 ? 16 : (k + 31) / 32;
     const int head_per = (k + h->head_nsplit - 1) / h->head_nsplit;
     h->head_nsplit = (k + head_per - 1) / head_per;
-    launch_pdl(head_wgrad_kernel, dim3(((h->F + 1) * h->A + 255) / 256, h->head_nsplit), dim3(256), 0, sd, 1, h->act[0][3],
+    launch_pdl(head_wgrad_kernel, dim3(((h->F + 1) * h->A + 255) / 256, h->head_nsplit), dim3(256), 0, sh, 1, h->act[0][3],
                h->g, d_actions, k, head_per, h->F, h->A, h->head_partial);
     }
     if (d_loss) {
       fill_segs(h, &oa, nsplit, false);
-      StageScope sc(h, DQN_STAGE_LOSS, sd);
-      launch_pdl(loss_kernel, dim3(1), dim3(256), 0, sd, 1, oa, h->se, k, d_loss);
+      StageScope sc(h, DQN_STAGE_LOSS, sh);
+      launch_pdl(loss_kernel, dim3(1), dim3(256), 0, sh, 1, oa, h->se, k, d_loss);
     }
+    if (fused) DQN_CUDA(cudaEventRecord(h->ev_head, sh));
     // data-parallel: as soon as the gradients of conv3, fc and the head (segments 2..4, 72% of the parameters) exist,
     // a third stream publishes them and sums them over the ranks into the local flat gradient buffer, in the shadow
     // of the rest of the backward pass
@@ -1260,6 +1289,7 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       cudaStream_t s2 = h->side2;
       DQN_CUDA(cudaEventRecord(h->ev_x, sd));
       DQN_CUDA(cudaStreamWaitEvent(s2, h->ev_x, 0));
+      if (fused) DQN_CUDA(cudaStreamWaitEvent(s2, h->ev_head, 0));
       OptArgs ea;
       fill_segs(h, &ea, nsplit, false);
       ea.world = h->dp_world;
@@ -1282,8 +1312,12 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       return 0;
     };
     if (h->precision == 1) {
-      launch_wgrad_tc<F4, __nv_bfloat16, 128>(h, 3, h->act_bf[0][2], k, sd, &nsplit[3]); launch_dgrad_tc<F4, 256>(h, 3, k, st);
-      if (fork_after_dgrad(1)) return DQN_ERR_CUDA;
+      launch_wgrad_tc<F4, __nv_bfloat16, 128>(h, 3, h->act_bf[0][2], k, sd, &nsplit[3]);
+      if (!fused) {                  // the fused kernel already produced the fc data gradient
+        if (k <= 256) launch_dgrad_tc<F4, 64>(h, 3, k, st);
+        else launch_dgrad_tc<F4, 256>(h, 3, k, st);
+        if (fork_after_dgrad(1)) return DQN_ERR_CUDA;
+      }
       launch_wgrad_tc<C3, __nv_bfloat16, 64>(h, 2, h->act_bf[0][1], k, sd, &nsplit[2]); launch_dgrad_tc<C3, 64>(h, 2, k, st);
       if (early_exchange()) return DQN_ERR_CUDA;
       if (fork_after_dgrad(2)) return DQN_ERR_CUDA;
@@ -1312,6 +1346,7 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
     // join
     DQN_CUDA(cudaEventRecord(h->ev_join, sd));
     DQN_CUDA(cudaStreamWaitEvent(st, h->ev_join, 0));
+    if (fused) DQN_CUDA(cudaStreamWaitEvent(st, h->ev_head, 0));
     DQN_CUDA(cudaGetLastError());
     if (mode == 2) {
       // late half of the exchange: conv1 and conv2 (segments 0, 1) are published here and summed by the optimizer

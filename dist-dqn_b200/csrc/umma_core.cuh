@@ -148,6 +148,24 @@ __device__ __forceinline__ void issue_stage(uint32_t tmem_d, uint32_t a_addr, ui
   mma_commit(bar);
 }
 
+// Weight operands live in global memory as "stage images": for a K-major operand matrix [rows][Kdim], stage s (64
+// reduction elements) is one contiguous block of rows*128 bytes already in SWIZZLE_128B order, so the B tile of a
+// stage (rows n0..n0+NTILE, n0 % 8 == 0) is ONE contiguous run of NTILE*128 bytes that a single thread fetches with a
+// bulk async copy (TMA engine) straight into its ring slot; completion is counted on the slot's mbarrier.
+__host__ __device__ inline size_t img_index(int row, int kk, int rows) {      // element (bf16) index of (row, kk)
+  const int s = kk >> 6, c = (kk >> 3) & 7, e = kk & 7;
+  return (size_t)s * rows * 64 + (size_t)((row >> 3) * 512 + (row & 7) * 64 + ((c ^ (row & 7)) << 3) + e);
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
+               "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
 constexpr int RS = 4;          // ring slots
 // prefetch distance is 2 stages: slot (it+2)%4 was last read by the MMAs of stage it-2
 
@@ -254,21 +272,24 @@ struct FwdArgsT {
 
 constexpr uint32_t FWD_RAW_PITCH = 80;                       // 64 uint8 of one tile row + pad (keeps 16-byte alignment)
 constexpr uint32_t FWD_RAW_A = 128 * FWD_RAW_PITCH;          // 10 KB
-template <typename TIn, int NTILE>
+// RSN ring slots, loads run PD stages ahead of the MMAs (PD <= RSN)
+template <typename TIn, int NTILE, int RSN>
 __host__ __device__ constexpr uint32_t fwd_smem_bytes() {
-  return SMEM_SLACK + (sizeof(TIn) == 1 ? RS * FWD_RAW_A + 2u * A_STAGE_BYTES : RS * A_STAGE_BYTES) + RS * (uint32_t)NTILE * 128u;
+  return SMEM_SLACK + (sizeof(TIn) == 1 ? RSN * FWD_RAW_A + 2u * A_STAGE_BYTES : RSN * A_STAGE_BYTES) + RSN * (uint32_t)NTILE * 128u;
 }
 
-template <class G, typename TIn, int NTILE>
+template <class G, typename TIn, int NTILE, int RSN, int PD>
 __global__ void __launch_bounds__(TT) umma_fwd_kernel(FwdArgsT a) {
+  static_assert(PD >= 1 && PD <= RSN, "prefetch distance");
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align_smem(smem_raw);
   constexpr bool U8 = sizeof(TIn) == 1;
   constexpr uint32_t B_STAGE = NTILE * 128;
-  constexpr uint32_t OFF_OPA = U8 ? RS * FWD_RAW_A : 0;              // converted A tiles (uint8 input only), 2 slots
-  constexpr uint32_t OFF_B = U8 ? RS * FWD_RAW_A + 2 * A_STAGE_BYTES : RS * A_STAGE_BYTES;
-  __shared__ uint64_t bars[2];        // MMAs of a stage parity have completed (tcgen05.commit)
-  __shared__ uint64_t full[RS];       // a ring slot is filled: one arrival per warp
+  constexpr uint32_t OFF_OPA = U8 ? RSN * FWD_RAW_A : 0;             // converted A tiles (uint8 input only), 2 slots
+  constexpr uint32_t OFF_B = U8 ? RSN * FWD_RAW_A + 2 * A_STAGE_BYTES : RSN * A_STAGE_BYTES;
+  __shared__ uint64_t bars[2];        // set-up only (TMEM allocation helper)
+  __shared__ uint64_t done[RSN];      // the MMAs reading a ring slot have completed (tcgen05.commit)
+  __shared__ uint64_t full[RSN];      // a ring slot is filled: one arrival per warp
   __shared__ uint32_t tmem_slot;
   __shared__ float bias_sm[NTILE];
   const FwdPassT P = a.p[blockIdx.z];
@@ -277,7 +298,7 @@ __global__ void __launch_bounds__(TT) umma_fwd_kernel(FwdArgsT a) {
   const int m0 = blockIdx.x * TM, n0 = blockIdx.y * NTILE;
   if (tid == 0) {
 #pragma unroll
-    for (int i = 0; i < RS; ++i) mbar_init(&full[i], TT / 32);
+    for (int i = 0; i < RSN; ++i) { mbar_init(&full[i], TT / 32 + 1); mbar_init(&done[i], 1); }   // 16 warps + the weight copy
   }
   const uint32_t tmem = setup(bars, &tmem_slot, tmem_cols(NTILE));
   const uint32_t sbase = smem_u32(smem);
@@ -290,7 +311,6 @@ __global__ void __launch_bounds__(TT) umma_fwd_kernel(FwdArgsT a) {
   const int arow = tid & (TM - 1);
   constexpr int T = G::K / TK;
   static_assert(G::K % TK == 0, "the reduction must be a whole number of stages");
-  constexpr int BCH = (NTILE * 8 + TT - 1) / TT;      // weight chunks per thread per stage
   constexpr uint32_t idesc = make_idesc(TM, NTILE, false, false);
   // Address generation is hoisted out of the stage loop (the gather is instruction-issue bound otherwise): per thread
   // and row a base pointer at the window origin, per stage one (ky, kx, channel) offset shared by both rows.
@@ -309,17 +329,10 @@ __global__ void __launch_bounds__(TT) umma_fwd_kernel(FwdArgsT a) {
     const int rr = (tid >> 3) + 64 * q;
     adst[q] = U8 ? (uint32_t)(rr * FWD_RAW_PITCH + gc * 8) : sw128_off(rr, gc);
   }
-  const __nv_bfloat16* bsrc[BCH];
-  uint32_t bdst[BCH];
-#pragma unroll
-  for (int q = 0; q < BCH; ++q) {
-    const int ch = tid + TT * q, n = ch >> 3, kc = ch & 7;
-    bsrc[q] = P.wt + (size_t)(n0 + (ch < NTILE * 8 ? n : 0)) * G::K + kc * 8;
-    bdst[q] = OFF_B + sw128_off(n, kc);
-  }
+  const __nv_bfloat16* wimg = P.wt + (size_t)n0 * 64;       // stage image: COUT*64 elements per stage, rows n0.. contiguous
   auto issue = [&](int it) {
     if (it < T) {
-      const int slot = it & (RS - 1);
+      const int slot = it % RSN;
       // chunk (it*8 + gc) of the (ky, kx, c) reduction axis: which filter tap, which channel group
       const int e = (it * 8 + gc) * EPC;               // first reduction element of this chunk
       const int tap = e / G::CIN, c0 = e - tap * G::CIN;
@@ -332,23 +345,28 @@ __global__ void __launch_bounds__(TT) umma_fwd_kernel(FwdArgsT a) {
         if constexpr (U8) cp_async8(sbase + slot * FWD_RAW_A + adst[q], src, ok);
         else cp_async16(sbase + slot * A_STAGE_BYTES + adst[q], src, ok);
       }
-#pragma unroll
-      for (int q = 0; q < BCH; ++q)
-        if (tid + TT * q < NTILE * 8) cp_async16(sbase + slot * B_STAGE + bdst[q], bsrc[q] + it * TK, true);
+      if (tid == 0) {                                    // the whole weight tile of the stage: one bulk copy
+        mbar_expect_tx(&full[slot], B_STAGE);
+        bulk_g2s(sbase + OFF_B + slot * B_STAGE, wimg + (size_t)it * (G::COUT * 64), B_STAGE, &full[slot]);
+      }
     }
     cp_async_commit();
   };
-  issue(0);
-  issue(1);
+#pragma unroll
+  for (int s = 0; s < PD; ++s) issue(s);
+#pragma unroll 1
   for (int it = 0; it < T; ++it) {
-    const int slot = it & (RS - 1), par = it & 1;
-    if (it >= 2) mbar_wait(&bars[par], ((it >> 1) - 1) & 1);   // MMAs of stage it-2 are done: their slots are free
-    issue(it + 2);
-    cp_async_wait<2>();                                         // this thread's copies for stage `it` have landed
+    const int slot = it % RSN, par = it & 1;
+    // stage it+PD goes into the slot stage it+PD-RSN used: the MMAs that read it must be done
+    if (it + PD < T && it + PD >= RSN) mbar_wait(&done[(it + PD) % RSN], ((it + PD - RSN) / RSN) & 1);
+    issue(it + PD);
+    cp_async_wait<PD>();                                        // this thread's copies for stage `it` have landed
     uint32_t a_addr;
     if constexpr (U8) {
       // widen the two 8-byte chunks this thread fetched itself and store them swizzled (lanes run along the chunks
-      // of a row, which the 128-byte swizzle keeps bank-conflict free)
+      // of a row, which the 128-byte swizzle keeps bank-conflict free); the tile being overwritten was read by the
+      // MMAs of stage it-2
+      if (it >= 2) mbar_wait(&done[(it - 2) % RSN], ((it - 2) / RSN) & 1);
       uint8_t* opa = smem + OFF_OPA + par * A_STAGE_BYTES;
 #pragma unroll
       for (int q = 0; q < 2; ++q) {
@@ -366,18 +384,18 @@ __global__ void __launch_bounds__(TT) umma_fwd_kernel(FwdArgsT a) {
     __syncwarp();
     if ((tid & 31) == 0) mbar_arrive(&full[slot]);
     if (tid == 0) {
-      mbar_wait(&full[slot], (it >> 2) & 1);
-      issue_stage<true, true>(tmem, a_addr, sbase + OFF_B + slot * B_STAGE, idesc, it == 0, &bars[par]);
+      mbar_wait(&full[slot], (it / RSN) & 1);
+      issue_stage<true, true>(tmem, a_addr, sbase + OFF_B + slot * B_STAGE, idesc, it == 0, &done[slot]);
     }
     __syncwarp();
   }
   pdl_trigger();                                                // all loads issued: let the next kernel start its prologue
   // the last commit covers every MMA issued before it
-  mbar_wait(&bars[(T - 1) & 1], ((T - 1) >> 1) & 1);
+  mbar_wait(&done[(T - 1) % RSN], ((T - 1) / RSN) & 1);
   tc_fence_after();
-  const Row row = decode_row<G>(m0 + arow, a.B);
   const int warp = tid >> 5, lane = tid & 31;
   const uint32_t trow = tmem + ((uint32_t)((warp & 3) * 32) << 16);    // tile row = arow (same for warps w and w+4k)
+  const Row row = decode_row<G>(m0 + arow, a.B);
   const bool row_in = row.valid;
 #pragma unroll 1
   for (int c0 = (warp >> 2) * 32; c0 < NTILE; c0 += 128) {             // the 4 warps of a lane group split the columns
@@ -653,9 +671,14 @@ __global__ void __launch_bounds__(TT) umma_dgrad_kernel(DgradArgsT a) {
   constexpr uint32_t OFF_RG = RS * DG_RAW_D, OFF_RW = OFF_RG + RS * DG_RAW_A, OFF_OPA = OFF_RW + RS * DG_RAW_W;
   constexpr uint32_t OFF_B = G::POOL ? OFF_OPA + 2 * A_STAGE_BYTES : RS * A_STAGE_BYTES;
   __shared__ uint64_t bars[2];
+  __shared__ uint64_t wfull[RS];      // the weight tile of a ring slot has landed (bulk copy)
   __shared__ uint32_t tmem_slot;
   const int tid = threadIdx.x;
   const int m0 = blockIdx.x * TM, c0t = blockIdx.y * NTILE;
+  if (tid == 0) {
+#pragma unroll
+    for (int i = 0; i < RS; ++i) mbar_init(&wfull[i], 1);
+  }
   const uint32_t tmem = setup(bars, &tmem_slot, tmem_cols(NTILE));
   const uint32_t sbase = smem_u32(smem);
   constexpr bool S2 = G::ST == 2;                     // parity-class formulation
@@ -697,8 +720,8 @@ __global__ void __launch_bounds__(TT) umma_dgrad_kernel(DgradArgsT a) {
   const int m = (eb * G::IH + eiy) * G::IW + eix;
   constexpr int T = S2 ? (G::KS / 2) * (G::KS / 2) : KD / TK;
   static_assert(KD % TK == 0, "dgrad reduction must be a multiple of the stage depth");
-  constexpr int BCH = (NTILE * 8 + TT - 1) / TT;
   constexpr uint32_t idesc = make_idesc(TM, NTILE, false, false);
+  const __nv_bfloat16* wimg = a.wd + (size_t)c0t * 64;      // stage image: CIN*64 elements per stage, rows c0t.. contiguous
   pdl_wait();
   auto issue = [&](int it) {
     if (it < T) {
@@ -740,12 +763,9 @@ __global__ void __launch_bounds__(TT) umma_dgrad_kernel(DgradArgsT a) {
           cp_async16(sbase + slot * A_STAGE_BYTES + sw128_off(r, gc), a.dactg + off, ok);
         }
       }
-#pragma unroll
-      for (int q = 0; q < BCH; ++q) {
-        const int ch = tid + TT * q, n = ch >> 3, kc = ch & 7;
-        if (ch < NTILE * 8)
-          cp_async16(sbase + OFF_B + slot * B_STAGE + sw128_off(n, kc),
-                     a.wd + (size_t)(c0t + n) * KD + (S2 ? t * G::COUT : it * TK) + kc * 8, true);
+      if (tid == 0) {                                    // weight tile of the stage (S2: the stage is filter tap t)
+        mbar_expect_tx(&wfull[slot], B_STAGE);
+        bulk_g2s(sbase + OFF_B + slot * B_STAGE, wimg + (size_t)(S2 ? t : it) * (G::CIN * 64), B_STAGE, &wfull[slot]);
       }
     }
     cp_async_commit();
@@ -775,7 +795,10 @@ __global__ void __launch_bounds__(TT) umma_dgrad_kernel(DgradArgsT a) {
     }
     fence_async_proxy();
     __syncthreads();
-    if (tid == 0) issue_stage<!G::POOL, true>(tmem, a_addr, sbase + OFF_B + slot * B_STAGE, idesc, it == 0, &bars[par]);
+    if (tid == 0) {
+      mbar_wait(&wfull[slot], (it >> 2) & 1);
+      issue_stage<!G::POOL, true>(tmem, a_addr, sbase + OFF_B + slot * B_STAGE, idesc, it == 0, &bars[par]);
+    }
   }
   pdl_trigger();
   mbar_wait(&bars[(T - 1) & 1], ((T - 1) >> 1) & 1);
