@@ -605,6 +605,7 @@ struct dqn_net_s {
   // step's CUDA graph as a parallel branch)
   cudaStream_t side = nullptr, side2 = nullptr;     // side2: early half of the data-parallel exchange
   cudaStream_t side3 = nullptr;                     // head weight gradient + loss (fused fc/TD path)
+  bool no_resident = false;                         // DQN_NO_RESIDENT=1: im2col gathers from L2 instead of a shared-memory resident input block
   bool no_fused_fc = true;                          // DQN_FUSED_FC=1: fc forward / TD head / fc dgrad as one launch (experimental)
   cudaEvent_t ev_fork[3] = {}, ev_join = nullptr, ev_x = nullptr, ev_join2 = nullptr, ev_head = nullptr;
   // bf16 tensor-core mode (precision == 1; DQN_ARCH_CNN only)
@@ -759,6 +760,7 @@ extern "C" int dqn_net_create(dqn_net_t* out, int32_t arch, const int32_t* in_sh
     cudaError_t e = cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->side2, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->side3, cudaStreamNonBlocking);
+    { const char* nr = getenv("DQN_NO_RESIDENT"); h->no_resident = nr && nr[0] == '1'; }
     { const char* nf = getenv("DQN_FUSED_FC"); h->no_fused_fc = !(nf && nf[0] == '1'); }
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_head, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_x, cudaEventDisableTiming);
@@ -1001,6 +1003,15 @@ static void launch_fwd_tc_cfg(const umma::FwdArgsT& a, int npass, cudaStream_t s
   dim3 grid((unsigned)((a.B * G::ROWS + umma::TM - 1) / umma::TM), G::COUT / NTILE, npass);
   launch_pdl(umma::umma_fwd_kernel<G, TIn, NTILE, RSN, PD>, grid, dim3(umma::TT), smem, st, 1, a);
 }
+template <class G, int NTILE, int NK, int NA>
+static void launch_fwd_res(const umma::FwdArgsT& a, int npass, cudaStream_t st) {
+  constexpr size_t smem = umma::fwd_res_smem_bytes<G, NTILE, NK, NA>();
+  static_assert(smem <= 227 * 1024, "patch + operand slots + weights do not fit in shared memory");
+  static bool once = (set_smem(umma::umma_fwd_res_kernel<G, NTILE, NK, NA>, smem), true);
+  (void)once;
+  dim3 grid((unsigned)((a.B * G::ROWS + umma::TM - 1) / umma::TM), G::COUT / NTILE, npass);
+  launch_pdl(umma::umma_fwd_res_kernel<G, NTILE, NK, NA>, grid, dim3(umma::TT), smem, st, 1, a);
+}
 // Ring depth: a grid of at most one CTA per SM is latency-bound (deep ring, loads far ahead of the MMAs); a grid of
 // several waves wants two CTAs resident per SM (small ring).  (Splitting the reduction of a tile over a cluster with a
 // DSMEM reduction was measured slower at B=32: the cluster launch and its two cluster barriers cost more than the
@@ -1094,8 +1105,14 @@ static int run_trunk_tc(dqn_net_s* h, int npass, const void* const x[2], const i
     StageScope sc(h, DQN_STAGE_FWD_CONV1 + l, st);
     switch (l) {
       case 0: launch_fwd_tc<C1, uint8_t, 32, 4, 4>(a, npass, h->num_sms, st); break;
-      case 1: launch_fwd_tc<C2, __nv_bfloat16, 64, 8, 4>(a, npass, h->num_sms, st); break;
-      case 2: launch_fwd_tc<C3, __nv_bfloat16, 64, 8, 4>(a, npass, h->num_sms, st); break;
+      case 1:
+        if (h->no_resident) launch_fwd_tc<C2, __nv_bfloat16, 64, 8, 4>(a, npass, h->num_sms, st);
+        else launch_fwd_res<C2, 64, 2, 3>(a, npass, st);
+        break;
+      case 2:
+        if (h->no_resident) launch_fwd_tc<C3, __nv_bfloat16, 64, 8, 4>(a, npass, h->num_sms, st);
+        else launch_fwd_res<C3, 64, 3, 2>(a, npass, st);
+        break;
       case 3:          // few rows: narrow tiles spread the weight traffic over more SMs (a lone CTA is bound by its SM's L2 port)
         if (B <= 256) launch_fwd_tc<F4, __nv_bfloat16, 64, 4, 4>(a, npass, h->num_sms, st);
         else launch_fwd_tc<F4, __nv_bfloat16, 256, 4, 4>(a, npass, h->num_sms, st);

@@ -251,6 +251,7 @@ __device__ __forceinline__ void teardown(uint32_t tmem_base, uint32_t ncols) {
 __host__ __device__ constexpr uint32_t tmem_cols(int n) { return n <= 32 ? 32u : (n <= 64 ? 64u : (n <= 128 ? 128u : 256u)); }
 // dynamic shared memory is re-based to a 1024-byte boundary inside the kernels (swizzled tiles need it)
 constexpr uint32_t SMEM_SLACK = 1024;
+__host__ __device__ constexpr uint32_t round1k_c(uint32_t v) { return (v + 1023u) & ~1023u; }
 __device__ __forceinline__ uint8_t* align_smem(uint8_t* p) {
   const uint32_t a = smem_u32(p);
   return p + (((a + 1023u) & ~1023u) - a);
@@ -269,6 +270,73 @@ struct FwdArgsT {
   FwdPassT p[2];
   int B;
 };
+
+// Forward epilogue: TMEM -> bias + ReLU (+ 2x2 max-pool and arg-max) -> bf16 NHWC (+ optional fp32 copy).
+template <class G, int NTILE>
+__device__ __forceinline__ void fwd_epilogue(uint32_t tmem, const FwdPassT& P, int m0, int n0, int B, const float* bias_sm) {
+  const int tid = threadIdx.x;
+  const int arow = tid & (TM - 1);
+  const int warp = tid >> 5, lane = tid & 31;
+  const uint32_t trow = tmem + ((uint32_t)((warp & 3) * 32) << 16);    // tile row = arow (same for warps w and w+4k)
+  const Row row = decode_row<G>(m0 + arow, B);
+  const bool row_in = row.valid;
+#pragma unroll 1
+  for (int c0 = (warp >> 2) * 32; c0 < NTILE; c0 += 128) {             // the 4 warps of a lane group split the columns
+    float v[32];
+    tmem_ld32(trow + c0, v);
+    const int n = n0 + c0;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j] + bias_sm[c0 + j], 0.f);
+    if constexpr (G::POOL) {
+      // Lanes 4q..4q+3 hold the 4 conv outputs of one pool window.  Values are >= 0 after ReLU, so their float bits
+      // order like unsigned integers: pack (value with the 2 lowest mantissa bits replaced by 3-win) into one key and
+      // take the maximum over the window -- largest value wins, ties go to the first window element, rows outside
+      // the image (key 0) never beat a positive value.  The 2 dropped bits are far below bf16 resolution.
+      uint32_t key[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        uint32_t kj = row_in ? ((__float_as_uint(v[j]) & ~3u) | (3u - (uint32_t)(lane & 3))) : 0u;
+        kj = max(kj, __shfl_xor_sync(0xffffffffu, kj, 1));
+        kj = max(kj, __shfl_xor_sync(0xffffffffu, kj, 2));
+        key[j] = kj;
+      }
+      if ((lane & 3) == 0 && row.b < B) {
+        const size_t off = (size_t)row.pidx * G::COUT + n;
+        uint32_t pk[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+          pk[j] = pack_bf16(__uint_as_float(key[2 * j] & ~3u), __uint_as_float(key[2 * j + 1] & ~3u));
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          *reinterpret_cast<uint4*>(P.out + off + 8 * j) = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+        if (P.arg) {
+          uint32_t ak[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            ak[j] = (3u - (key[4 * j] & 3u)) | ((3u - (key[4 * j + 1] & 3u)) << 8) | ((3u - (key[4 * j + 2] & 3u)) << 16) |
+                    ((3u - (key[4 * j + 3] & 3u)) << 24);
+          *reinterpret_cast<uint4*>(P.arg + off) = make_uint4(ak[0], ak[1], ak[2], ak[3]);
+          *reinterpret_cast<uint4*>(P.arg + off + 16) = make_uint4(ak[4], ak[5], ak[6], ak[7]);
+        }
+      }
+    } else {
+      if (row_in) {
+        const size_t off = (size_t)row.pidx * G::COUT + n;
+        uint32_t pk[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) pk[j] = pack_bf16(v[2 * j], v[2 * j + 1]);
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          *reinterpret_cast<uint4*>(P.out + off + 8 * j) = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+        if (P.out_f32) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<float4*>(P.out_f32 + off + 4 * j) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        }
+      }
+    }
+  }
+}
 
 constexpr uint32_t FWD_RAW_PITCH = 80;                       // 64 uint8 of one tile row + pad (keeps 16-byte alignment)
 constexpr uint32_t FWD_RAW_A = 128 * FWD_RAW_PITCH;          // 10 KB
@@ -393,66 +461,144 @@ __global__ void __launch_bounds__(TT) umma_fwd_kernel(FwdArgsT a) {
   // the last commit covers every MMA issued before it
   mbar_wait(&done[(T - 1) % RSN], ((T - 1) / RSN) & 1);
   tc_fence_after();
-  const int warp = tid >> 5, lane = tid & 31;
-  const uint32_t trow = tmem + ((uint32_t)((warp & 3) * 32) << 16);    // tile row = arow (same for warps w and w+4k)
-  const Row row = decode_row<G>(m0 + arow, a.B);
-  const bool row_in = row.valid;
-#pragma unroll 1
-  for (int c0 = (warp >> 2) * 32; c0 < NTILE; c0 += 128) {             // the 4 warps of a lane group split the columns
-    float v[32];
-    tmem_ld32(trow + c0, v);
-    const int n = n0 + c0;
+  fwd_epilogue<G, NTILE>(tmem, P, m0, n0, a.B, bias_sm);
+  teardown(tmem, tmem_cols(NTILE));
+}
+
+// ------------------------------------------------------------------------------------------------ forward, resident input
+// bf16 conv layers whose tiles span only a few samples.  Two observations from cycle traces of the ring kernels:
+// (1) the im2col gather from L2 re-reads every input pixel once per filter tap that touches it (conv2: 4x, conv3: 9x);
+// (2) with N = 64 a 64-deep stage is only 128 cycles of tensor-core work, but every stage costs ~1000 cycles of fixed
+//     latencies on the issuing warp (mbarrier try_waits, proxy fence, MMA issue + commit).
+// Here the input feature maps of the tile's samples -- one contiguous NHWC block -- are fetched ONCE with a bulk async
+// copy, ALL weight stages are fetched up front with bulk copies (before the PDL wait: they do not depend on the
+// previous kernel), and the A operand is built shared->shared (one 16-byte load + store per chunk) in BIG stages of
+// NK k-blocks (NK*64 reduction elements): one barrier round and one commit per 4*NK MMAs.
+template <class G, int NK, int NA>
+struct FwdRes {
+  static constexpr int NS = (TM + G::ROWS - 2) / G::ROWS + 1;                       // samples a 128-row tile can touch
+  static constexpr uint32_t SAMPLE_BYTES = G::IH * G::IW * G::CIN * 2;
+  static constexpr uint32_t PATCH_BYTES = round1k_c(NS * SAMPLE_BYTES);
+  static constexpr int T = G::K / TK;                                               // k-blocks
+  static constexpr int NBS = T / NK;                                                // big stages
+  static constexpr uint32_t A_SLOT = NK * A_STAGE_BYTES;
+  static_assert(G::K % (TK * NK) == 0, "the reduction must be a whole number of big stages");
+  static_assert(SAMPLE_BYTES % 16 == 0, "bulk copies move multiples of 16 bytes");
+};
+template <class G, int NTILE, int NK, int NA>
+__host__ __device__ constexpr uint32_t fwd_res_smem_bytes() {
+  using R = FwdRes<G, NK, NA>;
+  return SMEM_SLACK + R::PATCH_BYTES + NA * R::A_SLOT + R::T * (uint32_t)NTILE * 128u;
+}
+
+template <class G, int NTILE, int NK, int NA>
+__global__ void __launch_bounds__(TT) umma_fwd_res_kernel(FwdArgsT a) {
+  using R = FwdRes<G, NK, NA>;
+  constexpr int T = R::T, NBS = R::NBS;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align_smem(smem_raw);
+  constexpr uint32_t B_STAGE = NTILE * 128;
+  constexpr uint32_t OFF_A = R::PATCH_BYTES, OFF_B = OFF_A + NA * R::A_SLOT;
+  __shared__ uint64_t bars[2];
+  __shared__ uint64_t afull[NA];      // an operand slot is built: one arrival per warp
+  __shared__ uint64_t wfull[NBS];     // the weights of a big stage have landed (used once each)
+  __shared__ uint64_t done[NBS];      // the MMAs of a big stage have completed (used once each)
+  __shared__ uint64_t patchbar;       // the input feature maps have landed
+  __shared__ uint32_t tmem_slot;
+  __shared__ float bias_sm[NTILE];
+  const FwdPassT P = a.p[blockIdx.z];
+  const __nv_bfloat16* __restrict__ x = static_cast<const __nv_bfloat16*>(P.x);
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int m0 = blockIdx.x * TM, n0 = blockIdx.y * NTILE;
+  if (tid == 0) {
 #pragma unroll
-    for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j] + bias_sm[c0 + j], 0.f);
-    if constexpr (G::POOL) {
-      // Lanes 4q..4q+3 hold the 4 conv outputs of one pool window.  Values are >= 0 after ReLU, so their float bits
-      // order like unsigned integers: pack (value with the 2 lowest mantissa bits replaced by 3-win) into one key and
-      // take the maximum over the window -- largest value wins, ties go to the first window element, rows outside
-      // the image (key 0) never beat a positive value.  The 2 dropped bits are far below bf16 resolution.
-      uint32_t key[32];
+    for (int i = 0; i < NA; ++i) mbar_init(&afull[i], TT / 32);
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        uint32_t kj = row_in ? ((__float_as_uint(v[j]) & ~3u) | (3u - (uint32_t)(lane & 3))) : 0u;
-        kj = max(kj, __shfl_xor_sync(0xffffffffu, kj, 1));
-        kj = max(kj, __shfl_xor_sync(0xffffffffu, kj, 2));
-        key[j] = kj;
-      }
-      if ((lane & 3) == 0 && row.b < a.B) {
-        const size_t off = (size_t)row.pidx * G::COUT + n;
-        uint32_t pk[16];
+    for (int i = 0; i < NBS; ++i) { mbar_init(&wfull[i], 1); mbar_init(&done[i], 1); }
+    mbar_init(&patchbar, 1);
+  }
+  const uint32_t tmem = setup(bars, &tmem_slot, tmem_cols(NTILE));
+  const uint32_t sbase = smem_u32(smem);
+  // weights were written by the previous step's optimizer, several launches back: fetch them before the PDL wait.
+  // The NK k-block images of a big stage are contiguous in the stage-image layout when the tile spans all COUT rows.
+  if (tid == 0) {
+    const __nv_bfloat16* wimg = P.wt + (size_t)n0 * 64;
 #pragma unroll
-        for (int j = 0; j < 16; ++j)
-          pk[j] = pack_bf16(__uint_as_float(key[2 * j] & ~3u), __uint_as_float(key[2 * j + 1] & ~3u));
+    for (int bs = 0; bs < NBS; ++bs) {
+      mbar_expect_tx(&wfull[bs], NK * B_STAGE);
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-          *reinterpret_cast<uint4*>(P.out + off + 8 * j) = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
-        if (P.arg) {
-          uint32_t ak[8];
-#pragma unroll
-          for (int j = 0; j < 8; ++j)
-            ak[j] = (3u - (key[4 * j] & 3u)) | ((3u - (key[4 * j + 1] & 3u)) << 8) | ((3u - (key[4 * j + 2] & 3u)) << 16) |
-                    ((3u - (key[4 * j + 3] & 3u)) << 24);
-          *reinterpret_cast<uint4*>(P.arg + off) = make_uint4(ak[0], ak[1], ak[2], ak[3]);
-          *reinterpret_cast<uint4*>(P.arg + off + 16) = make_uint4(ak[4], ak[5], ak[6], ak[7]);
-        }
-      }
-    } else {
-      if (row_in) {
-        const size_t off = (size_t)row.pidx * G::COUT + n;
-        uint32_t pk[16];
-#pragma unroll
-        for (int j = 0; j < 16; ++j) pk[j] = pack_bf16(v[2 * j], v[2 * j + 1]);
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-          *reinterpret_cast<uint4*>(P.out + off + 8 * j) = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
-        if (P.out_f32) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j)
-            *reinterpret_cast<float4*>(P.out_f32 + off + 4 * j) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-        }
-      }
+      for (int kb = 0; kb < NK; ++kb)
+        bulk_g2s(sbase + OFF_B + (bs * NK + kb) * B_STAGE, wimg + (size_t)(bs * NK + kb) * (G::COUT * 64), B_STAGE, &wfull[bs]);
     }
   }
+  for (int j = tid; j < NTILE; j += TT) bias_sm[j] = __ldg(P.bias + n0 + j);
+  // rows of this thread in the build mapping: tile rows (tid>>3) and (tid>>3)+64, chunk gc of each k-block
+  const int gc = tid & 7;
+  const int b0 = m0 / G::ROWS;
+  int b1 = (m0 + TM - 1) / G::ROWS;
+  if (b1 > a.B - 1) b1 = a.B - 1;
+  int poff[2], aiy0[2], aix0[2];
+  bool avalid[2];
+  uint32_t adst[2];
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    const int rr = (tid >> 3) + 64 * q;
+    const Row r = decode_row<G>(m0 + rr, a.B);
+    aiy0[q] = r.oy * G::ST - G::PADH;
+    aix0[q] = r.ox * G::ST - G::PADW;
+    avalid[q] = r.valid;
+    poff[q] = (((r.b - b0) * G::IH + aiy0[q]) * G::IW + aix0[q]) * G::CIN * 2;   // byte offset in the patch (may be < 0 at the border)
+    adst[q] = OFF_A + sw128_off(rr, gc);
+  }
+  pdl_wait();
+  if (tid == 0) {
+    const uint32_t pbytes = (uint32_t)(b1 - b0 + 1) * R::SAMPLE_BYTES;
+    mbar_expect_tx(&patchbar, pbytes);
+    bulk_g2s(sbase, x + (size_t)b0 * (R::SAMPLE_BYTES / 2), pbytes, &patchbar);
+  }
+  constexpr uint32_t idesc = make_idesc(TM, NTILE, false, false);
+  mbar_wait(&patchbar, 0);
+#pragma unroll 1
+  for (int bs = 0; bs < NBS; ++bs) {
+    const int as = bs % NA;
+    if (bs >= NA) mbar_wait(&done[bs - NA], 0);        // the MMAs that read this operand slot are done
+#pragma unroll
+    for (int kb = 0; kb < NK; ++kb) {
+      const int e = ((bs * NK + kb) * 8 + gc) * 8;     // first reduction element of this thread's chunk
+      const int tap = e / G::CIN, c0 = e - tap * G::CIN;
+      const int ky = tap / G::KS, kx = tap - ky * G::KS;
+      const int delta = ((ky * G::IW + kx) * G::CIN + c0) * 2;
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const bool ok = avalid[q] && (unsigned)(aiy0[q] + ky) < (unsigned)G::IH && (unsigned)(aix0[q] + kx) < (unsigned)G::IW;
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (ok) v = *reinterpret_cast<const uint4*>(smem + poff[q] + delta);
+        *reinterpret_cast<uint4*>(smem + as * R::A_SLOT + kb * A_STAGE_BYTES + adst[q]) = v;
+      }
+    }
+    fence_async_proxy();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&afull[as]);
+    if (tid == 0) {
+      mbar_wait(&afull[as], (bs / NA) & 1);
+      mbar_wait(&wfull[bs], 0);
+      tc_fence_after();
+#pragma unroll
+      for (int kb = 0; kb < NK; ++kb) {
+        const uint32_t a_addr = sbase + OFF_A + as * R::A_SLOT + kb * A_STAGE_BYTES;
+        const uint32_t b_addr = sbase + OFF_B + (bs * NK + kb) * B_STAGE;
+#pragma unroll
+        for (int j = 0; j < TK / 16; ++j)
+          mma_bf16(tmem, make_desc_sw128(a_addr + j * 32), make_desc_sw128(b_addr + j * 32), idesc, (bs | kb | j) ? 1u : 0u);
+      }
+      mma_commit(&done[bs]);
+    }
+    __syncwarp();
+  }
+  pdl_trigger();
+  mbar_wait(&done[NBS - 1], 0);
+  tc_fence_after();
+  fwd_epilogue<G, NTILE>(tmem, P, m0, n0, a.B, bias_sm);
   teardown(tmem, tmem_cols(NTILE));
 }
 
