@@ -1065,6 +1065,28 @@ static void launch_dgrad_tc(dqn_net_s* h, int l, int B, cudaStream_t st) {
   launch_pdl(umma::umma_dgrad_kernel<G, NTILE>, grid, dim3(umma::TT), smem, st, 1, a);
 }
 
+template <class G, int NTILE, int NK, int NA>
+static void launch_dgrad_res(dqn_net_s* h, int l, int B, cudaStream_t st) {
+  constexpr size_t smem = umma::dgrad_res_smem_bytes<G, NTILE, NK, NA>();
+  static_assert(smem <= 227 * 1024, "patch + operand slots + weights do not fit in shared memory");
+  static bool once = (set_smem(umma::umma_dgrad_res_kernel<G, NTILE, NK, NA>, smem), true);
+  (void)once;
+  umma::DgradArgsT a{h->wd_bf + h->wd_off[l], h->dact_bf[l], h->arg[0][l], h->act_bf[0][l - 1], h->dact_bf[l - 1], B, {0, 0, 0, 0, 0}};
+  unsigned mtiles = (unsigned)((B * G::IH * G::IW + umma::TM - 1) / umma::TM);
+  if constexpr (G::ST == 2) {          // tiles are grouped by input-pixel parity class
+    int acc = 0;
+    for (int c = 0; c < 4; ++c) {
+      a.cls_tile[c] = acc;
+      acc += (B * umma::DgradClasses<G>::count(c) + umma::TM - 1) / umma::TM;
+    }
+    a.cls_tile[4] = acc;
+    mtiles = (unsigned)acc;
+  }
+  dim3 grid(mtiles, G::CIN / NTILE, 1);
+  StageScope sc(h, DQN_STAGE_DGRAD_FC + 2 * (3 - l), st);
+  launch_pdl(umma::umma_dgrad_res_kernel<G, NTILE, NK, NA>, grid, dim3(umma::TT), smem, st, 1, a);
+}
+
 // fp32 master weights of one parameter set -> bf16 operand copies
 static int refresh_bf16_weights(dqn_net_s* h, int set, cudaStream_t st) {
   CvtArgs c;
@@ -1335,10 +1357,10 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
         else launch_dgrad_tc<F4, 256>(h, 3, k, st);
         if (fork_after_dgrad(1)) return DQN_ERR_CUDA;
       }
-      launch_wgrad_tc<C3, __nv_bfloat16, 64>(h, 2, h->act_bf[0][1], k, sd, &nsplit[2]); launch_dgrad_tc<C3, 64>(h, 2, k, st);
+      launch_wgrad_tc<C3, __nv_bfloat16, 64>(h, 2, h->act_bf[0][1], k, sd, &nsplit[2]); if (h->no_resident) launch_dgrad_tc<C3, 64>(h, 2, k, st); else launch_dgrad_res<C3, 64, 3, 2>(h, 2, k, st);
       if (early_exchange()) return DQN_ERR_CUDA;
       if (fork_after_dgrad(2)) return DQN_ERR_CUDA;
-      launch_wgrad_tc<C2, __nv_bfloat16, 64>(h, 1, h->act_bf[0][0], k, sd, &nsplit[1]); launch_dgrad_tc<C2, 32>(h, 1, k, st);
+      launch_wgrad_tc<C2, __nv_bfloat16, 64>(h, 1, h->act_bf[0][0], k, sd, &nsplit[1]); if (h->no_resident) launch_dgrad_tc<C2, 32>(h, 1, k, st); else launch_dgrad_res<C2, 32, 4, 1>(h, 1, k, st);
       launch_wgrad_tc<C1, uint8_t, 32>(h, 0, d_states, k, st, &nsplit[0]);
     } else if (nat) {
       launch_wgrad<NF, float>(h, 3, h->act[0][2], k, sd, &nsplit[3]); launch_dgrad<NF>(h, 3, k, st);

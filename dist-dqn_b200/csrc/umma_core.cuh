@@ -798,6 +798,38 @@ struct DgradClasses {
   __host__ __device__ static constexpr int count(int c) { return ny(c) * nx(c); }
 };
 
+// Data-gradient epilogue: TMEM -> ReLU gate of the layer below -> bf16 gradient of its pooled output.
+template <class G, int NTILE>
+__device__ __forceinline__ void dgrad_epilogue(uint32_t tmem, const DgradArgsT& a, int m, bool mvalid, int c0t) {
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5;
+  const uint32_t trow = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+#pragma unroll 1
+  for (int c0 = (warp >> 2) * 32; c0 < NTILE; c0 += 128) {
+    float v[32];
+    tmem_ld32(trow + c0, v);
+    if (mvalid) {
+      const size_t off = (size_t)m * G::CIN + c0t + c0;
+      uint32_t pk[16];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        // ReLU gate of the layer below: zero the gradient where its (pooled) output is not positive
+        const uint4 p = *reinterpret_cast<const uint4*>(a.act_prev + off + 8 * j);
+        const uint32_t pw[4] = {p.x, p.y, p.z, p.w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const bool lo = ((pw[q] & 0x7FFFu) != 0u) && !(pw[q] & 0x8000u);
+          const bool hi = ((pw[q] & 0x7FFF0000u) != 0u) && !(pw[q] & 0x80000000u);
+          pk[4 * j + q] = pack_bf16(lo ? v[8 * j + 2 * q] : 0.f, hi ? v[8 * j + 2 * q + 1] : 0.f);
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        *reinterpret_cast<uint4*>(a.dx + off + 8 * j) = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+    }
+  }
+}
+
 constexpr uint32_t DG_PD = 144, DG_PA = 72;                          // raw gradient / arg-max row pitches (8 chunks + pad)
 constexpr uint32_t DG_RAW_D = 128 * DG_PD, DG_RAW_A = 128 * DG_PA, DG_RAW_W = 1024;   // 18 KB, 9 KB, 1 KB
 template <class G, int NTILE>
@@ -949,32 +981,177 @@ __global__ void __launch_bounds__(TT) umma_dgrad_kernel(DgradArgsT a) {
   pdl_trigger();
   mbar_wait(&bars[(T - 1) & 1], ((T - 1) >> 1) & 1);
   tc_fence_after();
-  const int warp = tid >> 5;
-  const uint32_t trow = tmem + ((uint32_t)((warp & 3) * 32) << 16);
-#pragma unroll 1
-  for (int c0 = (warp >> 2) * 32; c0 < NTILE; c0 += 128) {
-    float v[32];
-    tmem_ld32(trow + c0, v);
-    if (mvalid) {
-      const size_t off = (size_t)m * G::CIN + c0t + c0;
-      uint32_t pk[16];
+  dgrad_epilogue<G, NTILE>(tmem, a, m, mvalid, c0t);
+  teardown(tmem, tmem_cols(NTILE));
+}
+
+// ------------------------------------------------------------------------------------------------ data gradient, resident
+// Pooled conv layers (conv2: stride-2 parity classes, conv3: dense 3x3).  Same idea as umma_fwd_res_kernel: the
+// (ReLU-gated) gradient of the pooled output and the pool arg-max of the tile's samples are two small contiguous
+// blocks, fetched once with bulk copies; all weight stages are fetched before the PDL wait; every filter tap is one
+// k-block (COUT == 64) whose A tile is built shared->shared with the pool routing applied on the way, NK taps per
+// barrier round.
+template <class G, bool S2>
+struct DgradRes {
+  static constexpr int RPS_MIN = S2 ? DgradClasses<G>::count(3) : G::IH * G::IW;    // fewest tile rows one sample contributes
+  static constexpr int NS = (TM + RPS_MIN - 2) / RPS_MIN + 1;
+  static constexpr uint32_t D_BYTES = G::PH * G::PW * G::COUT * 2;                   // gradient bytes per sample
+  static constexpr uint32_t A_BYTES = G::PH * G::PW * G::COUT;                       // arg-max bytes per sample
+  static constexpr uint32_t OFF_ARG = round1k_c(NS * D_BYTES);
+  static constexpr uint32_t PATCH_BYTES = OFF_ARG + round1k_c(NS * A_BYTES);
+  static constexpr int T = S2 ? (G::KS / 2) * (G::KS / 2) : G::KS * G::KS;           // taps = k-blocks
+  static_assert(G::COUT == TK && G::POOL, "one filter tap per 64-deep k-block, pooled layers only");
+  static_assert(D_BYTES % 16 == 0 && A_BYTES % 16 == 0, "bulk copies move multiples of 16 bytes");
+};
+template <class G, int NTILE, int NK, int NA>
+__host__ __device__ constexpr uint32_t dgrad_res_smem_bytes() {
+  using R = DgradRes<G, G::ST == 2>;
+  return SMEM_SLACK + R::PATCH_BYTES + NA * NK * A_STAGE_BYTES + R::T * (uint32_t)NTILE * 128u;
+}
+
+template <class G, int NTILE, int NK, int NA>
+__global__ void __launch_bounds__(TT) umma_dgrad_res_kernel(DgradArgsT a) {
+  constexpr bool S2 = G::ST == 2;
+  using R = DgradRes<G, S2>;
+  constexpr int T = R::T, NBS = T / NK;
+  static_assert(T % NK == 0, "taps must split into whole big stages");
+  static_assert(!S2 || (G::KS % 2 == 0 && G::PADH == 1 && G::PADW == 1), "parity classes assume an even filter and pad 1");
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align_smem(smem_raw);
+  constexpr uint32_t B_STAGE = NTILE * 128, A_SLOT = NK * A_STAGE_BYTES;
+  constexpr uint32_t OFF_A = R::PATCH_BYTES, OFF_B = OFF_A + NA * A_SLOT;
+  __shared__ uint64_t bars[2];
+  __shared__ uint64_t afull[NA];
+  __shared__ uint64_t wfull[NBS];
+  __shared__ uint64_t done[NBS];
+  __shared__ uint64_t patchbar;
+  __shared__ uint32_t tmem_slot;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int c0t = blockIdx.y * NTILE;
+  if (tid == 0) {
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        // ReLU gate of the layer below: zero the gradient where its (pooled) output is not positive
-        const uint4 p = *reinterpret_cast<const uint4*>(a.act_prev + off + 8 * j);
-        const uint32_t pw[4] = {p.x, p.y, p.z, p.w};
+    for (int i = 0; i < NA; ++i) mbar_init(&afull[i], TT / 32);
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const bool lo = ((pw[q] & 0x7FFFu) != 0u) && !(pw[q] & 0x8000u);
-          const bool hi = ((pw[q] & 0x7FFF0000u) != 0u) && !(pw[q] & 0x80000000u);
-          pk[4 * j + q] = pack_bf16(lo ? v[8 * j + 2 * q] : 0.f, hi ? v[8 * j + 2 * q + 1] : 0.f);
-        }
-      }
+    for (int i = 0; i < NBS; ++i) { mbar_init(&wfull[i], 1); mbar_init(&done[i], 1); }
+    mbar_init(&patchbar, 1);
+  }
+  const uint32_t tmem = setup(bars, &tmem_slot, tmem_cols(NTILE));
+  const uint32_t sbase = smem_u32(smem);
+  // which rows does this tile cover?  dense: m0 + r over all input pixels; S2: r-th pixel of parity class `cls`
+  int cls = 0, row0 = blockIdx.x * TM;
+  if constexpr (S2) {
+    while (cls < 3 && (int)blockIdx.x >= a.cls_tile[cls + 1]) ++cls;
+    row0 = ((int)blockIdx.x - a.cls_tile[cls]) * TM;
+  }
+  const int cy = cls >> 1, cx = cls & 1;
+  // weights first (they do not depend on the previous kernel); S2: k-block i is the class's i-th tap
+  auto tap_of = [&](int i) -> int {
+    if constexpr (S2) return ((1 - cy) + 2 * (i / (G::KS / 2))) * G::KS + (1 - cx) + 2 * (i % (G::KS / 2));
+    else return i;
+  };
+  if (tid == 0) {
+    const __nv_bfloat16* wimg = a.wd + (size_t)c0t * 64;
 #pragma unroll
-      for (int j = 0; j < 4; ++j)
-        *reinterpret_cast<uint4*>(a.dx + off + 8 * j) = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+    for (int bs = 0; bs < NBS; ++bs) {
+      mbar_expect_tx(&wfull[bs], NK * B_STAGE);
+#pragma unroll
+      for (int kb = 0; kb < NK; ++kb)
+        bulk_g2s(sbase + OFF_B + (bs * NK + kb) * B_STAGE, wimg + (size_t)tap_of(bs * NK + kb) * (G::CIN * 64), B_STAGE, &wfull[bs]);
     }
   }
+  auto decode = [&](int r, int& b, int& iy, int& ix) -> bool {
+    if constexpr (S2) {
+      const int nxc = DgradClasses<G>::nx(cls), cnt = DgradClasses<G>::count(cls);
+      b = r / cnt;
+      const int rem = r - b * cnt;
+      const int yy = rem / nxc;
+      iy = 2 * yy + cy;
+      ix = 2 * (rem - yy * nxc) + cx;
+      return r < a.B * cnt;
+    } else {
+      b = r / (G::IH * G::IW);
+      const int rem = r - b * (G::IH * G::IW);
+      iy = rem / G::IW;
+      ix = rem - iy * G::IW;
+      return r < a.B * G::IH * G::IW;
+    }
+  };
+  const int rps = S2 ? DgradClasses<G>::count(cls) : G::IH * G::IW;
+  const int b0 = row0 / rps;
+  int b1 = (row0 + TM - 1) / rps;
+  if (b1 > a.B - 1) b1 = a.B - 1;
+  // build mapping: tile rows (tid>>3) and (tid>>3)+64, channel chunk gc of the tap
+  const int gc = tid & 7;
+  int gb[2], giy[2], gix[2];
+  bool gvalid[2];
+  uint32_t adst[2];
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    const int rr = (tid >> 3) + 64 * q;
+    gvalid[q] = decode(row0 + rr, gb[q], giy[q], gix[q]);
+    gb[q] -= b0;
+    adst[q] = OFF_A + sw128_off(rr, gc);
+  }
+  // epilogue mapping: tile row tid&127
+  int eb, eiy, eix;
+  const bool mvalid = decode(row0 + (tid & (TM - 1)), eb, eiy, eix);
+  const int m = (eb * G::IH + eiy) * G::IW + eix;
+  pdl_wait();
+  if (tid == 0) {
+    const uint32_t nb = (uint32_t)(b1 - b0 + 1);
+    mbar_expect_tx(&patchbar, nb * (R::D_BYTES + R::A_BYTES));
+    bulk_g2s(sbase, a.dactg + (size_t)b0 * (R::D_BYTES / 2), nb * R::D_BYTES, &patchbar);
+    bulk_g2s(sbase + R::OFF_ARG, a.arg + (size_t)b0 * R::A_BYTES, nb * R::A_BYTES, &patchbar);
+  }
+  constexpr uint32_t idesc = make_idesc(TM, NTILE, false, false);
+  mbar_wait(&patchbar, 0);
+#pragma unroll 1
+  for (int bs = 0; bs < NBS; ++bs) {
+    const int as = bs % NA;
+    if (bs >= NA) mbar_wait(&done[bs - NA], 0);
+#pragma unroll
+    for (int kb = 0; kb < NK; ++kb) {
+      const int t = tap_of(bs * NK + kb);
+      const int ky = t / G::KS, kx = t - ky * G::KS;
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const int ty = giy[q] + G::PADH - ky, tx = gix[q] + G::PADW - kx;
+        bool ok = gvalid[q] && ty >= 0 && tx >= 0 && (ty % G::ST) == 0 && (tx % G::ST) == 0;
+        const int oy = ty / G::ST, ox = tx / G::ST;
+        ok = ok && oy < G::OH && ox < G::OW;
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (ok) {
+          const int pl = ((gb[q] * G::PH + (oy >> 1)) * G::PW + (ox >> 1)) * G::COUT + gc * 8;
+          const uint4 d = *reinterpret_cast<const uint4*>(smem + pl * 2);
+          const uint2 ag = *reinterpret_cast<const uint2*>(smem + R::OFF_ARG + pl);
+          v = route_chunk(d, ag, (oy & 1) * 2 + (ox & 1));
+        }
+        *reinterpret_cast<uint4*>(smem + as * A_SLOT + kb * A_STAGE_BYTES + adst[q]) = v;
+      }
+    }
+    fence_async_proxy();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&afull[as]);
+    if (tid == 0) {
+      mbar_wait(&afull[as], (bs / NA) & 1);
+      mbar_wait(&wfull[bs], 0);
+      tc_fence_after();
+#pragma unroll
+      for (int kb = 0; kb < NK; ++kb) {
+        const uint32_t a_addr = sbase + OFF_A + as * A_SLOT + kb * A_STAGE_BYTES;
+        const uint32_t b_addr = sbase + OFF_B + (bs * NK + kb) * B_STAGE;
+#pragma unroll
+        for (int j = 0; j < TK / 16; ++j)
+          mma_bf16(tmem, make_desc_sw128(a_addr + j * 32), make_desc_sw128(b_addr + j * 32), idesc, (bs | kb | j) ? 1u : 0u);
+      }
+      mma_commit(&done[bs]);
+    }
+    __syncwarp();
+  }
+  pdl_trigger();
+  mbar_wait(&done[NBS - 1], 0);
+  tc_fence_after();
+  dgrad_epilogue<G, NTILE>(tmem, a, m, mvalid, c0t);
   teardown(tmem, tmem_cols(NTILE));
 }
 
