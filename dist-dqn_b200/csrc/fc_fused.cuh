@@ -119,6 +119,7 @@ __global__ void __launch_bounds__(TT) fc_td_fused_kernel(FcFusedArgs a) {
   issue_fwd(0);
   issue_fwd(1);
   issue_fwd(2);
+  const int wu = warp_uniform_idx();
 #pragma unroll 1
   for (int it = 0; it < 8; ++it) {
     const int slot = it & 3;
@@ -128,12 +129,11 @@ __global__ void __launch_bounds__(TT) fc_td_fused_kernel(FcFusedArgs a) {
     fence_async_proxy();
     __syncwarp();
     if (lane == 0) mbar_arrive(&full[slot]);
-    if (tid == 0) {
+    if (wu == 0) {
       mbar_wait(&full[slot], (it >> 2) & 1);
       issue_stage<true, true>(tmem + (uint32_t)(it >> 2) * FCF, sbase + slot * A_STAGE_BYTES, sbase + FC_OFF_B + slot * FC_B_STAGE,
                               idesc, (it & 3) == 0, &done[slot]);
     }
-    __syncwarp();
   }
   mbar_wait(&done[3], 1);             // stage 7's commit covers every MMA issued before it
   tc_fence_after();
@@ -262,7 +262,7 @@ __global__ void __launch_bounds__(TT) fc_td_fused_kernel(FcFusedArgs a) {
   // ---------------------------------------------------------------- data-gradient GEMM: dX[r,k] = sum_n dh[r,n] w4[k,n]
   issue_wd(3);                                   // the scratch in slot 3 is dead now
   tc_fence_after();
-  if (tid == 0) {                                // the A operand is complete (barrier above): only the weights arrive in stages
+  if (wu == 0) {                                 // the A operand is complete (barrier above): only the weights arrive in stages
 #pragma unroll
     for (int s = 0; s < 4; ++s) {
       mbar_wait(&wdbar[s], 0);
@@ -270,7 +270,6 @@ __global__ void __launch_bounds__(TT) fc_td_fused_kernel(FcFusedArgs a) {
                               s == 3 ? &fin : &done[s]);
     }
   }
-  __syncwarp();
   pdl_trigger();
   mbar_wait(&fin, 0);
   tc_fence_after();

@@ -1012,6 +1012,14 @@ static void launch_fwd_res(const umma::FwdArgsT& a, int npass, cudaStream_t st) 
   dim3 grid((unsigned)((a.B * G::ROWS + umma::TM - 1) / umma::TM), G::COUT / NTILE, npass);
   launch_pdl(umma::umma_fwd_res_kernel<G, NTILE, NK, NA>, grid, dim3(umma::TT), smem, st, 1, a);
 }
+template <class G, int NTILE>
+static void launch_fwd_res_u8(const umma::FwdArgsT& a, int npass, cudaStream_t st) {
+  constexpr size_t smem = umma::fwd_res_u8_smem_bytes<G, NTILE>();
+  static bool once = (set_smem(umma::umma_fwd_res_u8_kernel<G, NTILE>, smem), true);
+  (void)once;
+  dim3 grid((unsigned)((a.B * G::ROWS + umma::TM - 1) / umma::TM), G::COUT / NTILE, npass);
+  launch_pdl(umma::umma_fwd_res_u8_kernel<G, NTILE>, grid, dim3(umma::TT), smem, st, 1, a);
+}
 // Ring depth: a grid of at most one CTA per SM is latency-bound (deep ring, loads far ahead of the MMAs); a grid of
 // several waves wants two CTAs resident per SM (small ring).  (Splitting the reduction of a tile over a cluster with a
 // DSMEM reduction was measured slower at B=32: the cluster launch and its two cluster barriers cost more than the
@@ -1126,7 +1134,10 @@ static int run_trunk_tc(dqn_net_s* h, int npass, const void* const x[2], const i
     if (npass == 1) a.p[1] = a.p[0];
     StageScope sc(h, DQN_STAGE_FWD_CONV1 + l, st);
     switch (l) {
-      case 0: launch_fwd_tc<C1, uint8_t, 32, 4, 4>(a, npass, h->num_sms, st); break;
+      case 0:
+        if (h->no_resident) launch_fwd_tc<C1, uint8_t, 32, 4, 4>(a, npass, h->num_sms, st);
+        else launch_fwd_res_u8<C1, 32>(a, npass, st);
+        break;
       case 1:
         if (h->no_resident) launch_fwd_tc<C2, __nv_bfloat16, 64, 8, 4>(a, npass, h->num_sms, st);
         else launch_fwd_res<C2, 64, 2, 3>(a, npass, st);

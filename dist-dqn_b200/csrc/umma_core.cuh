@@ -96,6 +96,16 @@ __device__ __forceinline__ void mma_bf16(uint32_t tmem_d, uint64_t adesc, uint64
 __device__ __forceinline__ void mma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+// One lane of a converged warp (the tensor-core instructions take their operands from the uniform datapath: issuing
+// them under `if (tid == 0)` makes the compiler wrap every one of them in an elect loop).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
+__device__ __forceinline__ int warp_uniform_idx() { return __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0); }
+// descriptor of the same operand `bytes` further on (bytes % 16 == 0; the 14-bit address field cannot carry: smem < 256 KB)
+__device__ __forceinline__ uint64_t desc_advance(uint64_t d, uint32_t bytes) { return d + (uint64_t)(bytes >> 4); }
 // 32 consecutive accumulator columns of this thread's TMEM lane
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float v[32]) {
   uint32_t r[32];
@@ -133,19 +143,23 @@ __device__ __forceinline__ uint64_t make_desc_sw128(uint32_t saddr) {
 // byte offset of chunk c (8 reduction elements) of row i in a SWIZZLE_128B K-major stage
 __device__ __forceinline__ uint32_t sw128_off(int i, int c) { return (uint32_t)((i >> 3) * 1024 + (i & 7) * 128 + ((c ^ (i & 7)) << 4)); }
 
-// issue the 4 MMAs of one stage (thread 0 only) and commit them to `bar`.  *_SW: operand is in the swizzled
+// issue the 4 MMAs of one stage and commit them to `bar`.  Called by ALL lanes of one converged warp (the branch
+// leading here must be warp-uniform, see warp_uniform_idx); one elected lane issues.  *_SW: operand is in the swizzled
 // K-major layout (UMMA_K steps are 32 bytes apart) instead of the no-swizzle one (256 bytes apart).
 template <bool A_SW, bool B_SW>
 __device__ __forceinline__ void issue_stage(uint32_t tmem_d, uint32_t a_addr, uint32_t b_addr, uint32_t idesc, bool first,
                                             uint64_t* bar) {
   tc_fence_after();
+  if (elect_one()) {
+    const uint64_t ad0 = A_SW ? make_desc_sw128(a_addr) : make_desc(a_addr, 128, 1024);
+    const uint64_t bd0 = B_SW ? make_desc_sw128(b_addr) : make_desc(b_addr, 128, 1024);
 #pragma unroll
-  for (int j = 0; j < TK / 16; ++j) {
-    const uint64_t ad = A_SW ? make_desc_sw128(a_addr + j * 32) : make_desc(a_addr + j * 256, 128, 1024);
-    const uint64_t bd = B_SW ? make_desc_sw128(b_addr + j * 32) : make_desc(b_addr + j * 256, 128, 1024);
-    mma_bf16(tmem_d, ad, bd, idesc, (first && j == 0) ? 0u : 1u);
+    for (int j = 0; j < TK / 16; ++j)
+      mma_bf16(tmem_d, desc_advance(ad0, j * (A_SW ? 32 : 256)), desc_advance(bd0, j * (B_SW ? 32 : 256)), idesc,
+               (first && j == 0) ? 0u : 1u);
+    mma_commit(bar);
   }
-  mma_commit(bar);
+  __syncwarp();
 }
 
 // Weight operands live in global memory as "stage images": for a K-major operand matrix [rows][Kdim], stage s (64
@@ -422,6 +436,7 @@ __global__ void __launch_bounds__(TT) umma_fwd_kernel(FwdArgsT a) {
   };
 #pragma unroll
   for (int s = 0; s < PD; ++s) issue(s);
+  const int wu = warp_uniform_idx();
 #pragma unroll 1
   for (int it = 0; it < T; ++it) {
     const int slot = it % RSN, par = it & 1;
@@ -451,11 +466,10 @@ __global__ void __launch_bounds__(TT) umma_fwd_kernel(FwdArgsT a) {
     fence_async_proxy();
     __syncwarp();
     if ((tid & 31) == 0) mbar_arrive(&full[slot]);
-    if (tid == 0) {
+    if (wu == 0) {
       mbar_wait(&full[slot], (it / RSN) & 1);
       issue_stage<true, true>(tmem, a_addr, sbase + OFF_B + slot * B_STAGE, idesc, it == 0, &done[slot]);
     }
-    __syncwarp();
   }
   pdl_trigger();                                                // all loads issued: let the next kernel start its prologue
   // the last commit covers every MMA issued before it
@@ -557,6 +571,7 @@ __global__ void __launch_bounds__(TT) umma_fwd_res_kernel(FwdArgsT a) {
     bulk_g2s(sbase, x + (size_t)b0 * (R::SAMPLE_BYTES / 2), pbytes, &patchbar);
   }
   constexpr uint32_t idesc = make_idesc(TM, NTILE, false, false);
+  const int wu = warp_uniform_idx();
   mbar_wait(&patchbar, 0);
 #pragma unroll 1
   for (int bs = 0; bs < NBS; ++bs) {
@@ -579,24 +594,153 @@ __global__ void __launch_bounds__(TT) umma_fwd_res_kernel(FwdArgsT a) {
     fence_async_proxy();
     __syncwarp();
     if (lane == 0) mbar_arrive(&afull[as]);
-    if (tid == 0) {
+    if (wu == 0) {
       mbar_wait(&afull[as], (bs / NA) & 1);
       mbar_wait(&wfull[bs], 0);
       tc_fence_after();
+      if (elect_one()) {
+        const uint64_t ad0 = make_desc_sw128(sbase + OFF_A + as * R::A_SLOT), bd0 = make_desc_sw128(sbase + OFF_B + bs * NK * B_STAGE);
 #pragma unroll
-      for (int kb = 0; kb < NK; ++kb) {
-        const uint32_t a_addr = sbase + OFF_A + as * R::A_SLOT + kb * A_STAGE_BYTES;
-        const uint32_t b_addr = sbase + OFF_B + (bs * NK + kb) * B_STAGE;
+        for (int kb = 0; kb < NK; ++kb) {
 #pragma unroll
-        for (int j = 0; j < TK / 16; ++j)
-          mma_bf16(tmem, make_desc_sw128(a_addr + j * 32), make_desc_sw128(b_addr + j * 32), idesc, (bs | kb | j) ? 1u : 0u);
+          for (int j = 0; j < TK / 16; ++j)
+            mma_bf16(tmem, desc_advance(ad0, kb * A_STAGE_BYTES + j * 32), desc_advance(bd0, kb * B_STAGE + j * 32), idesc,
+                     (bs | kb | j) ? 1u : 0u);
+        }
+        mma_commit(&done[bs]);
       }
-      mma_commit(&done[bs]);
+      __syncwarp();
     }
-    __syncwarp();
   }
   pdl_trigger();
   mbar_wait(&done[NBS - 1], 0);
+  tc_fence_after();
+  fwd_epilogue<G, NTILE>(tmem, P, m0, n0, a.B, bias_sm);
+  teardown(tmem, tmem_cols(NTILE));
+}
+
+// ------------------------------------------------------------------------------------------------ forward, resident uint8 frames
+// conv1 on the uint8 frame stacks (network.py:395-407 with the float cast of the feed, dqn_agent.py:186-189, fused in).
+// A 128-row tile is 32 pool windows = at most 5 pool rows, i.e. a contiguous band of at most PATCH_ROWS input rows
+// (336 bytes each) -- fetched once by one bulk copy.  The whole reduction (K = 8*8*4 = 256) is ONE big stage: every
+// thread widens 8 chunks of 2 pixels x 4 frames to bf16 into the swizzled operand tile, then 16 MMAs, then the
+// pooled epilogue.
+template <class G>
+struct FwdResU8 {
+  static constexpr int PATCH_ROWS = 48;
+  static constexpr uint32_t ROW_BYTES = G::IW * G::CIN;                               // 336
+  static constexpr uint32_t PATCH_BYTES = round1k_c(PATCH_ROWS * ROW_BYTES);
+  static constexpr int T = G::K / TK;                                                 // 4 k-blocks
+  static_assert(G::CIN == 4 && ROW_BYTES % 16 == 0 && TK == 2 * G::KS * G::CIN, "one k-block = two filter rows of 8 pixels x 4 frames");
+};
+template <class G, int NTILE>
+__host__ __device__ constexpr uint32_t fwd_res_u8_smem_bytes() {
+  return SMEM_SLACK + FwdResU8<G>::PATCH_BYTES + FwdResU8<G>::T * (A_STAGE_BYTES + (uint32_t)NTILE * 128u);
+}
+
+template <class G, int NTILE>
+__global__ void __launch_bounds__(TT) umma_fwd_res_u8_kernel(FwdArgsT a) {
+  using R = FwdResU8<G>;
+  constexpr int T = R::T;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align_smem(smem_raw);
+  constexpr uint32_t B_STAGE = NTILE * 128;
+  constexpr uint32_t OFF_A = R::PATCH_BYTES, OFF_B = OFF_A + T * A_STAGE_BYTES;
+  __shared__ uint64_t bars[2];
+  __shared__ uint64_t afull, wfull, done, patchbar;
+  __shared__ uint32_t tmem_slot;
+  __shared__ float bias_sm[NTILE];
+  const FwdPassT P = a.p[blockIdx.z];
+  const uint8_t* __restrict__ x = static_cast<const uint8_t*>(P.x);
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int m0 = blockIdx.x * TM, n0 = blockIdx.y * NTILE;
+  if (tid == 0) {
+    mbar_init(&afull, TT / 32);
+    mbar_init(&wfull, 1);
+    mbar_init(&done, 1);
+    mbar_init(&patchbar, 1);
+  }
+  const uint32_t tmem = setup(bars, &tmem_slot, tmem_cols(NTILE));
+  const uint32_t sbase = smem_u32(smem);
+  if (tid == 0) {                     // all weights, before the PDL wait
+    const __nv_bfloat16* wimg = P.wt + (size_t)n0 * 64;
+    mbar_expect_tx(&wfull, T * B_STAGE);
+#pragma unroll
+    for (int kb = 0; kb < T; ++kb) bulk_g2s(sbase + OFF_B + kb * B_STAGE, wimg + (size_t)kb * (G::COUT * 64), B_STAGE, &wfull);
+  }
+  for (int j = tid; j < NTILE; j += TT) bias_sm[j] = __ldg(P.bias + n0 + j);
+  // the band of input rows this tile reads: from the first pool row of its first window to the last pool row of its
+  // last window (windows run sample-major, then row-major), clipped to the image
+  constexpr int WPS = G::PH * G::PW;                                   // pool windows per sample
+  const int w_first = m0 >> 2;
+  int w_last = (m0 + TM - 1) >> 2;
+  if (w_last > a.B * WPS - 1) w_last = a.B * WPS - 1;
+  const int bf = w_first / WPS, bl = w_last / WPS;
+  const int pyf = (w_first - bf * WPS) / G::PW, pyl = (w_last - bl * WPS) / G::PW;
+  int iy_lo = 2 * pyf * G::ST - G::PADH;
+  if (iy_lo < 0) iy_lo = 0;
+  int iy_hi = (2 * pyl + 1) * G::ST - G::PADH + G::KS - 1;
+  if (iy_hi > G::IH - 1) iy_hi = G::IH - 1;
+  const int grow_lo = bf * G::IH + iy_lo, grow_hi = bl * G::IH + iy_hi;      // global input-row indices (inclusive)
+  const int gc = tid & 7;
+  int poff[2], aiy0[2], aix0[2];
+  bool avalid[2];
+  uint32_t adst[2];
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    const int rr = (tid >> 3) + 64 * q;
+    const Row r = decode_row<G>(m0 + rr, a.B);
+    aiy0[q] = r.oy * G::ST - G::PADH;
+    aix0[q] = r.ox * G::ST - G::PADW;
+    avalid[q] = r.valid;
+    poff[q] = ((r.b * G::IH + aiy0[q] - grow_lo) * G::IW + aix0[q]) * G::CIN;        // byte offset in the band (may be < 0 at the border)
+    adst[q] = OFF_A + sw128_off(rr, gc);
+  }
+  pdl_wait();
+  if (tid == 0) {
+    const int nrows = grow_hi - grow_lo + 1;
+    if (nrows > R::PATCH_ROWS) __trap();
+    mbar_expect_tx(&patchbar, (uint32_t)nrows * R::ROW_BYTES);
+    bulk_g2s(sbase, x + (size_t)grow_lo * R::ROW_BYTES, (uint32_t)nrows * R::ROW_BYTES, &patchbar);
+  }
+  constexpr uint32_t idesc = make_idesc(TM, NTILE, false, false);
+  mbar_wait(&patchbar, 0);
+  // chunk gc of k-block kb: filter row ky = 2*kb + gc/4, pixels kx = 2*(gc%4), +1
+  const int kxo = 2 * (gc & 3), kyo = gc >> 2;
+#pragma unroll
+  for (int kb = 0; kb < T; ++kb) {
+    const int ky = 2 * kb + kyo;
+    const int delta = (ky * G::IW + kxo) * G::CIN;
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      const bool ok = avalid[q] && (unsigned)(aiy0[q] + ky) < (unsigned)G::IH && (unsigned)(aix0[q] + kxo) < (unsigned)G::IW;
+      uint4 v = make_uint4(0u, 0u, 0u, 0u);
+      if (ok) v = cvt_u8x8(*reinterpret_cast<const uint2*>(smem + poff[q] + delta));
+      *reinterpret_cast<uint4*>(smem + kb * A_STAGE_BYTES + adst[q]) = v;
+    }
+  }
+  fence_async_proxy();
+  __syncwarp();
+  if (lane == 0) mbar_arrive(&afull);
+  if (warp_uniform_idx() == 0) {
+    mbar_wait(&afull, 0);
+    mbar_wait(&wfull, 0);
+    tc_fence_after();
+    if (elect_one()) {
+      const uint64_t ad0 = make_desc_sw128(sbase + OFF_A), bd0 = make_desc_sw128(sbase + OFF_B);
+#pragma unroll
+      for (int kb = 0; kb < T; ++kb) {
+#pragma unroll
+        for (int j = 0; j < TK / 16; ++j)
+          mma_bf16(tmem, desc_advance(ad0, kb * A_STAGE_BYTES + j * 32), desc_advance(bd0, kb * B_STAGE + j * 32), idesc,
+                   (kb | j) ? 1u : 0u);
+      }
+      mma_commit(&done);
+    }
+  }
+  __syncwarp();
+  pdl_trigger();
+  mbar_wait(&done, 0);
   tc_fence_after();
   fwd_epilogue<G, NTILE>(tmem, P, m0, n0, a.B, bias_sm);
   teardown(tmem, tmem_cols(NTILE));
@@ -697,6 +841,7 @@ __global__ void __launch_bounds__(TT) umma_wgrad_kernel(WgradArgsT a) {
   };
   issue(0);
   issue(1);
+  const int wu = warp_uniform_idx();
   for (int it = 0; it < T; ++it) {
     const int slot = it & (RS - 1), par = it & 1;
     if (it >= 2) mbar_wait(&bars[par], ((it >> 1) - 1) & 1);
@@ -730,7 +875,7 @@ __global__ void __launch_bounds__(TT) umma_wgrad_kernel(WgradArgsT a) {
     }
     fence_async_proxy();
     __syncthreads();
-    if (tid == 0)
+    if (wu == 0)
       issue_stage<false, false>(tmem, sbase + OFF_OPA + par * A_STAGE_BYTES, sbase + OFF_OPB + par * B_STAGE, idesc, it == 0,
                                 &bars[par]);
   }
@@ -950,6 +1095,7 @@ __global__ void __launch_bounds__(TT) umma_dgrad_kernel(DgradArgsT a) {
   };
   issue(0);
   issue(1);
+  const int wu = warp_uniform_idx();
   for (int it = 0; it < T; ++it) {
     const int slot = it & (RS - 1), par = it & 1;
     if (it >= 2) mbar_wait(&bars[par], ((it >> 1) - 1) & 1);
@@ -973,7 +1119,7 @@ __global__ void __launch_bounds__(TT) umma_dgrad_kernel(DgradArgsT a) {
     }
     fence_async_proxy();
     __syncthreads();
-    if (tid == 0) {
+    if (wu == 0) {
       mbar_wait(&wfull[slot], (it >> 2) & 1);
       issue_stage<!G::POOL, true>(tmem, a_addr, sbase + OFF_B + slot * B_STAGE, idesc, it == 0, &bars[par]);
     }
@@ -1104,6 +1250,7 @@ __global__ void __launch_bounds__(TT) umma_dgrad_res_kernel(DgradArgsT a) {
     bulk_g2s(sbase + R::OFF_ARG, a.arg + (size_t)b0 * R::A_BYTES, nb * R::A_BYTES, &patchbar);
   }
   constexpr uint32_t idesc = make_idesc(TM, NTILE, false, false);
+  const int wu = warp_uniform_idx();
   mbar_wait(&patchbar, 0);
 #pragma unroll 1
   for (int bs = 0; bs < NBS; ++bs) {
@@ -1132,21 +1279,23 @@ __global__ void __launch_bounds__(TT) umma_dgrad_res_kernel(DgradArgsT a) {
     fence_async_proxy();
     __syncwarp();
     if (lane == 0) mbar_arrive(&afull[as]);
-    if (tid == 0) {
+    if (wu == 0) {
       mbar_wait(&afull[as], (bs / NA) & 1);
       mbar_wait(&wfull[bs], 0);
       tc_fence_after();
+      if (elect_one()) {
+        const uint64_t ad0 = make_desc_sw128(sbase + OFF_A + as * A_SLOT), bd0 = make_desc_sw128(sbase + OFF_B + bs * NK * B_STAGE);
 #pragma unroll
-      for (int kb = 0; kb < NK; ++kb) {
-        const uint32_t a_addr = sbase + OFF_A + as * A_SLOT + kb * A_STAGE_BYTES;
-        const uint32_t b_addr = sbase + OFF_B + (bs * NK + kb) * B_STAGE;
+        for (int kb = 0; kb < NK; ++kb) {
 #pragma unroll
-        for (int j = 0; j < TK / 16; ++j)
-          mma_bf16(tmem, make_desc_sw128(a_addr + j * 32), make_desc_sw128(b_addr + j * 32), idesc, (bs | kb | j) ? 1u : 0u);
+          for (int j = 0; j < TK / 16; ++j)
+            mma_bf16(tmem, desc_advance(ad0, kb * A_STAGE_BYTES + j * 32), desc_advance(bd0, kb * B_STAGE + j * 32), idesc,
+                     (bs | kb | j) ? 1u : 0u);
+        }
+        mma_commit(&done[bs]);
       }
-      mma_commit(&done[bs]);
+      __syncwarp();
     }
-    __syncwarp();
   }
   pdl_trigger();
   mbar_wait(&done[NBS - 1], 0);
