@@ -53,6 +53,14 @@ int64_t launch_count();
 #ifdef __CUDACC__
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+// Wait for the predecessor, then -- if this launch is a single wave (every CTA is already resident, so early dependents
+// cannot take shared memory / TMEM away from CTAs that still have to start) -- let the successor launch right away: it
+// runs its set-up and its weight prefetch in the shadow of this kernel's main loop and blocks in its own wait.
+// Multi-wave launches trigger late (after their main loop), as before.
+__device__ __forceinline__ void pdl_wait_then_trigger() {
+  pdl_wait();
+  if (gridDim.x * gridDim.y * gridDim.z <= 128u) pdl_trigger();
+}
 
 template <typename... KArgs, typename... Args>
 static inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,

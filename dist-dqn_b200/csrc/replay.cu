@@ -84,6 +84,7 @@ gather_stack4_u8_kernel(RingView rv, const int32_t* __restrict__ idx, int32_t k,
                         int32_t* __restrict__ actions, double* __restrict__ rewards,
                         uint8_t* __restrict__ terminals) {
   pdl_wait();
+  if (gridDim.x <= 1024u) pdl_trigger();      // single wave: the consumer may launch and run its set-up now (it waits for our completion)
   const int64_t total = (int64_t)k * chunks;
   const int64_t head = rv.state[0];
   const TransitionRec* meta = static_cast<const TransitionRec*>(rv.meta);

@@ -224,6 +224,18 @@ __device__ __forceinline__ uint4 cvt_u8x8(uint2 u) {     // 8 uint8 -> 8 bf16 (e
   return v;
 }
 
+// 8 uint8 -> 8 bf16 (exact) without the slow integer->float instruction: the byte goes into the low mantissa bits of
+// 2^23 (0x4B000000 | n == 8388608 + n), one subtraction leaves n.
+__device__ __forceinline__ uint4 widen_u8x8(uint2 u) {
+  const float k = 8388608.f;
+  uint4 v;
+  v.x = pack_bf16(__uint_as_float(__byte_perm(u.x, 0x4B000000u, 0x7540)) - k, __uint_as_float(__byte_perm(u.x, 0x4B000000u, 0x7541)) - k);
+  v.y = pack_bf16(__uint_as_float(__byte_perm(u.x, 0x4B000000u, 0x7542)) - k, __uint_as_float(__byte_perm(u.x, 0x4B000000u, 0x7543)) - k);
+  v.z = pack_bf16(__uint_as_float(__byte_perm(u.y, 0x4B000000u, 0x7540)) - k, __uint_as_float(__byte_perm(u.y, 0x4B000000u, 0x7541)) - k);
+  v.w = pack_bf16(__uint_as_float(__byte_perm(u.y, 0x4B000000u, 0x7542)) - k, __uint_as_float(__byte_perm(u.y, 0x4B000000u, 0x7543)) - k);
+  return v;
+}
+
 // Pool routing of 8 (already ReLU-gated) gradient values: keep element e iff the window's arg-max is `win`.
 __device__ __forceinline__ uint4 route_chunk(uint4 d, uint2 arg, int win) {
   uint32_t dw[4] = {d.x, d.y, d.z, d.w};
@@ -387,7 +399,7 @@ __global__ void __launch_bounds__(TT) umma_fwd_kernel(FwdArgsT a) {
   // gather mapping (lanes along the contiguous k direction): chunk id = tid + 512*q -> row id>>3, chunk id&7
   const Row grow0 = decode_row<G>(m0 + (tid >> 3), a.B), grow1 = decode_row<G>(m0 + 64 + (tid >> 3), a.B);
   const int gc = tid & 7;
-  pdl_wait();                                           // everything above overlapped the previous kernel
+  pdl_wait_then_trigger();                                           // everything above overlapped the previous kernel
   for (int j = tid; j < NTILE; j += TT) bias_sm[j] = __ldg(P.bias + n0 + j);
   // epilogue mapping: tile row tid&127
   const int arow = tid & (TM - 1);
@@ -564,7 +576,7 @@ __global__ void __launch_bounds__(TT) umma_fwd_res_kernel(FwdArgsT a) {
     poff[q] = (((r.b - b0) * G::IH + aiy0[q]) * G::IW + aix0[q]) * G::CIN * 2;   // byte offset in the patch (may be < 0 at the border)
     adst[q] = OFF_A + sw128_off(rr, gc);
   }
-  pdl_wait();
+  pdl_wait_then_trigger();
   if (tid == 0) {
     const uint32_t pbytes = (uint32_t)(b1 - b0 + 1) * R::SAMPLE_BYTES;
     mbar_expect_tx(&patchbar, pbytes);
@@ -622,14 +634,17 @@ __global__ void __launch_bounds__(TT) umma_fwd_res_kernel(FwdArgsT a) {
 // ------------------------------------------------------------------------------------------------ forward, resident uint8 frames
 // conv1 on the uint8 frame stacks (network.py:395-407 with the float cast of the feed, dqn_agent.py:186-189, fused in).
 // A 128-row tile is 32 pool windows = at most 5 pool rows, i.e. a contiguous band of at most PATCH_ROWS input rows
-// (336 bytes each) -- fetched once by one bulk copy.  The whole reduction (K = 8*8*4 = 256) is ONE big stage: every
-// thread widens 8 chunks of 2 pixels x 4 frames to bf16 into the swizzled operand tile, then 16 MMAs, then the
-// pooled epilogue.
+// (336 bytes each) -- fetched once by one bulk copy and widened to bf16 ONCE (every pixel is used by 4 windows; the
+// integer->float conversion instruction runs at 1/8 rate, so bytes are widened with a byte-permute into the mantissa of
+// 2^23 and one subtraction instead).  The whole reduction (K = 8*8*4 = 256) is ONE big stage: every thread copies 8
+// chunks of 2 pixels x 4 frames from the bf16 band into the swizzled operand tile, then 16 MMAs, then the pooled
+// epilogue.  The uint8 band is staged in the tail of the operand area, which is only written after the widening.
 template <class G>
 struct FwdResU8 {
-  static constexpr int PATCH_ROWS = 48;
+  static constexpr int PATCH_ROWS = 40;                                               // 5 pool rows: 8*5 + 4 rows minus the clipped border
   static constexpr uint32_t ROW_BYTES = G::IW * G::CIN;                               // 336
-  static constexpr uint32_t PATCH_BYTES = round1k_c(PATCH_ROWS * ROW_BYTES);
+  static constexpr uint32_t RAW_BYTES = round1k_c(PATCH_ROWS * ROW_BYTES);            // uint8 band (staged inside the operand area)
+  static constexpr uint32_t PATCH_BYTES = round1k_c(2 * PATCH_ROWS * ROW_BYTES);      // bf16 band
   static constexpr int T = G::K / TK;                                                 // 4 k-blocks
   static_assert(G::CIN == 4 && ROW_BYTES % 16 == 0 && TK == 2 * G::KS * G::CIN, "one k-block = two filter rows of 8 pixels x 4 frames");
 };
@@ -646,6 +661,8 @@ __global__ void __launch_bounds__(TT) umma_fwd_res_u8_kernel(FwdArgsT a) {
   uint8_t* smem = align_smem(smem_raw);
   constexpr uint32_t B_STAGE = NTILE * 128;
   constexpr uint32_t OFF_A = R::PATCH_BYTES, OFF_B = OFF_A + T * A_STAGE_BYTES;
+  constexpr uint32_t OFF_RAW = OFF_B - R::RAW_BYTES;                   // tail of the operand area (last k-block's tile)
+  static_assert(R::RAW_BYTES <= A_STAGE_BYTES, "the uint8 band must fit in the last operand tile");
   __shared__ uint64_t bars[2];
   __shared__ uint64_t afull, wfull, done, patchbar;
   __shared__ uint32_t tmem_slot;
@@ -696,15 +713,24 @@ __global__ void __launch_bounds__(TT) umma_fwd_res_u8_kernel(FwdArgsT a) {
     poff[q] = ((r.b * G::IH + aiy0[q] - grow_lo) * G::IW + aix0[q]) * G::CIN;        // byte offset in the band (may be < 0 at the border)
     adst[q] = OFF_A + sw128_off(rr, gc);
   }
-  pdl_wait();
+  pdl_wait_then_trigger();
   if (tid == 0) {
     const int nrows = grow_hi - grow_lo + 1;
     if (nrows > R::PATCH_ROWS) __trap();
     mbar_expect_tx(&patchbar, (uint32_t)nrows * R::ROW_BYTES);
-    bulk_g2s(sbase, x + (size_t)grow_lo * R::ROW_BYTES, (uint32_t)nrows * R::ROW_BYTES, &patchbar);
+    bulk_g2s(sbase + OFF_RAW, x + (size_t)grow_lo * R::ROW_BYTES, (uint32_t)nrows * R::ROW_BYTES, &patchbar);
   }
   constexpr uint32_t idesc = make_idesc(TM, NTILE, false, false);
   mbar_wait(&patchbar, 0);
+  // widen the band: 8 bytes -> 8 bf16 per step
+  {
+    const int nchunks = (grow_hi - grow_lo + 1) * (int)(R::ROW_BYTES / 8);
+    for (int c = tid; c < nchunks; c += TT) {
+      const uint2 u = *reinterpret_cast<const uint2*>(smem + OFF_RAW + c * 8);
+      *reinterpret_cast<uint4*>(smem + c * 16) = widen_u8x8(u);
+    }
+  }
+  __syncthreads();
   // chunk gc of k-block kb: filter row ky = 2*kb + gc/4, pixels kx = 2*(gc%4), +1
   const int kxo = 2 * (gc & 3), kyo = gc >> 2;
 #pragma unroll
@@ -715,7 +741,7 @@ __global__ void __launch_bounds__(TT) umma_fwd_res_u8_kernel(FwdArgsT a) {
     for (int q = 0; q < 2; ++q) {
       const bool ok = avalid[q] && (unsigned)(aiy0[q] + ky) < (unsigned)G::IH && (unsigned)(aix0[q] + kxo) < (unsigned)G::IW;
       uint4 v = make_uint4(0u, 0u, 0u, 0u);
-      if (ok) v = cvt_u8x8(*reinterpret_cast<const uint2*>(smem + poff[q] + delta));
+      if (ok) v = *reinterpret_cast<const uint4*>(smem + 2 * (poff[q] + delta));
       *reinterpret_cast<uint4*>(smem + kb * A_STAGE_BYTES + adst[q]) = v;
     }
   }
@@ -793,7 +819,7 @@ __global__ void __launch_bounds__(TT) umma_wgrad_kernel(WgradArgsT a) {
   for (int j = tid; j < NTILE; j += TT) bias_sm[j] = 0.f;
   const uint32_t tmem = setup(bars, &tmem_slot, tmem_cols(NTILE));
   const uint32_t sbase = smem_u32(smem);
-  pdl_wait();
+  pdl_wait_then_trigger();
   const int R = a.B * G::ROWS;
   const int r_begin = blockIdx.z * a.rows_per_split;
   const int r_end = min(R, r_begin + a.rows_per_split);
@@ -1045,7 +1071,7 @@ __global__ void __launch_bounds__(TT) umma_dgrad_kernel(DgradArgsT a) {
   static_assert(KD % TK == 0, "dgrad reduction must be a multiple of the stage depth");
   constexpr uint32_t idesc = make_idesc(TM, NTILE, false, false);
   const __nv_bfloat16* wimg = a.wd + (size_t)c0t * 64;      // stage image: CIN*64 elements per stage, rows c0t.. contiguous
-  pdl_wait();
+  pdl_wait_then_trigger();
   auto issue = [&](int it) {
     if (it < T) {
       const int slot = it & (RS - 1);
@@ -1242,7 +1268,7 @@ __global__ void __launch_bounds__(TT) umma_dgrad_res_kernel(DgradArgsT a) {
   int eb, eiy, eix;
   const bool mvalid = decode(row0 + (tid & (TM - 1)), eb, eiy, eix);
   const int m = (eb * G::IH + eiy) * G::IW + eix;
-  pdl_wait();
+  pdl_wait_then_trigger();
   if (tid == 0) {
     const uint32_t nb = (uint32_t)(b1 - b0 + 1);
     mbar_expect_tx(&patchbar, nb * (R::D_BYTES + R::A_BYTES));
