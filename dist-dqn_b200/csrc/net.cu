@@ -58,29 +58,42 @@ td_head_kernel(const float* __restrict__ h_on, const float* __restrict__ h_tg, c
   constexpr int F = FPL * 32;
   const int lane = threadIdx.x & 31;
   const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  // head weights of both nets -> shared memory BEFORE the PDL wait (last written by the previous step's optimizer):
+  // their L2 latency overlaps the tail of the fc forward kernel instead of sitting in the per-action loop
+  extern __shared__ float td_sm[];                       // [2][F*A + A]
+  float* ws_on = td_sm;
+  float* ws_tg = td_sm + (F * A + A);
   pdl_trigger();
+  for (int i = threadIdx.x; i < F * A; i += blockDim.x) { ws_on[i] = __ldg(w_on + i); ws_tg[i] = __ldg(w_tg + i); }
+  if (threadIdx.x < A) { ws_on[F * A + threadIdx.x] = __ldg(b_on + threadIdx.x); ws_tg[F * A + threadIdx.x] = __ldg(b_tg + threadIdx.x); }
   pdl_wait();
   if (blockIdx.x == 0 && threadIdx.x == 0) *step += 1;      // global_step (network.py:83, 198-202)
-  if (b >= B) return;
   float x[FPL], xt[FPL];
+  int act = 0;
+  double reward = 0.0;
+  bool terminal = false;
+  if (b < B) {
 #pragma unroll
-  for (int i = 0; i < FPL; ++i) {
-    x[i] = h_on[(size_t)b * F + lane + 32 * i];
-    xt[i] = h_tg[(size_t)b * F + lane + 32 * i];
+    for (int i = 0; i < FPL; ++i) {
+      x[i] = h_on[(size_t)b * F + lane + 32 * i];
+      xt[i] = h_tg[(size_t)b * F + lane + 32 * i];
+    }
+    act = actions[b];
+    reward = rewards[b];
+    terminal = terminals[b] != 0;
   }
-  const int act = actions[b];
-  const double reward = rewards[b];
-  const bool terminal = terminals[b] != 0;
+  __syncthreads();
+  if (b >= B) return;
   float q_sel = 0.f, maxq = 0.f;
   for (int a = 0; a < A; ++a) {
     float s = 0.f, st = 0.f;
 #pragma unroll
     for (int i = 0; i < FPL; ++i) {
-      s = fmaf(x[i], __ldg(w_on + (lane + 32 * i) * A + a), s);
-      st = fmaf(xt[i], __ldg(w_tg + (lane + 32 * i) * A + a), st);
+      s = fmaf(x[i], ws_on[(lane + 32 * i) * A + a], s);
+      st = fmaf(xt[i], ws_tg[(lane + 32 * i) * A + a], st);
     }
-    s = warp_sum(s) + b_on[a];
-    st = warp_sum(st) + b_tg[a];
+    s = warp_sum(s) + ws_on[F * A + a];
+    st = warp_sum(st) + ws_tg[F * A + a];
     if (qout && lane == 0) qout[(size_t)b * A + a] = s;
     if (a == 0 || st > maxq) maxq = st;
     if (a == act) q_sel = s;
@@ -91,7 +104,7 @@ td_head_kernel(const float* __restrict__ h_on, const float* __restrict__ h_tg, c
 #pragma unroll
   for (int i = 0; i < FPL; ++i) {
     const int j = lane + 32 * i;
-    const float d = gg * __ldg(w_on + j * A + act);
+    const float d = gg * ws_on[j * A + act];
     dh[(size_t)b * F + j] = d;
     if (dh_bf) dh_bf[(size_t)b * F + j] = __float2bfloat16_rn(x[i] > 0.f ? d : 0.f);   // ReLU-gated for the tensor-core path
   }
@@ -1281,7 +1294,7 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
     if (rc) return rc;
     const float* w5 = h->online + h->tensors[8].off;
     cudaStream_t sd = h->side;
-    cudaStream_t sh = fused ? h->side3 : h->side;      // head weight gradient + loss
+    cudaStream_t sh = h->side3;                        // head weight gradient, loss, fc weight gradient
     if (fused) {
       static bool once = (set_smem(umma::fc_td_fused_kernel, umma::FC_SMEM), true);
       (void)once;
@@ -1301,22 +1314,25 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
     } else {
     StageScope sc(h, DQN_STAGE_TD_HEAD, st);
     if (h->F == 256)
-      launch_pdl(td_head_kernel<8>, dim3((k + 7) / 8), dim3(256), 0, st, 1, h->act[0][3], h->act[1][3], w5, h->online + h->tensors[9].off,
+      launch_pdl(td_head_kernel<8>, dim3((k + 7) / 8), dim3(256), (size_t)2 * (256 * h->A + h->A) * 4, st, 1, h->act[0][3], h->act[1][3], w5, h->online + h->tensors[9].off,
                                                      h->target + h->tensors[8].off, h->target + h->tensors[9].off,
                                                      d_actions, d_rewards, d_term, k, h->A, h->hyper.gamma, h->hyper.loss,
                                                      d_q, h->se, h->g, h->dact[3],
                                                      h->precision == 1 ? h->dact_bf[3] : nullptr, h->step);
-    else
-      launch_pdl(td_head_kernel<16>, dim3((k + 7) / 8), dim3(256), 0, st, 1, h->act[0][3], h->act[1][3], w5, h->online + h->tensors[9].off,
+    else {
+      static bool once = (set_smem(td_head_kernel<16>, 160 * 1024), true);     // 2 x 512 x A floats can exceed the 48 KB default
+      (void)once;
+      launch_pdl(td_head_kernel<16>, dim3((k + 7) / 8), dim3(256), (size_t)2 * (512 * h->A + h->A) * 4, st, 1, h->act[0][3], h->act[1][3], w5, h->online + h->tensors[9].off,
                                                       h->target + h->tensors[8].off, h->target + h->tensors[9].off,
                                                       d_actions, d_rewards, d_term, k, h->A, h->hyper.gamma, h->hyper.loss,
                                                       d_q, h->se, h->g, h->dact[3],
                                                       h->precision == 1 ? h->dact_bf[3] : nullptr, h->step);
     }
-    // fork: head/fc/conv3/conv2 weight gradients on the side stream(s), data-gradient chain + conv1 wgrad on `st`
+    }
+    // fork: head + fc weight gradients on `sh`, conv3/conv2 weight gradients on `sd`, data-gradient chain + conv1 wgrad on `st`
     DQN_CUDA(cudaEventRecord(h->ev_fork[0], st));
     DQN_CUDA(cudaStreamWaitEvent(sd, h->ev_fork[0], 0));
-    if (fused) DQN_CUDA(cudaStreamWaitEvent(sh, h->ev_fork[0], 0));
+    DQN_CUDA(cudaStreamWaitEvent(sh, h->ev_fork[0], 0));
     {
     StageScope sc(h, DQN_STAGE_HEAD_WGRAD, sh);
     h->head_nsplit = (k + 31) / 32 > 16 ? 16 : (k + 31) / 32;
@@ -1330,7 +1346,6 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       StageScope sc(h, DQN_STAGE_LOSS, sh);
       launch_pdl(loss_kernel, dim3(1), dim3(256), 0, sh, 1, oa, h->se, k, d_loss);
     }
-    if (fused) DQN_CUDA(cudaEventRecord(h->ev_head, sh));
     // data-parallel: as soon as the gradients of conv3, fc and the head (segments 2..4, 72% of the parameters) exist,
     // a third stream publishes them and sums them over the ranks into the local flat gradient buffer, in the shadow
     // of the rest of the backward pass
@@ -1339,7 +1354,7 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       cudaStream_t s2 = h->side2;
       DQN_CUDA(cudaEventRecord(h->ev_x, sd));
       DQN_CUDA(cudaStreamWaitEvent(s2, h->ev_x, 0));
-      if (fused) DQN_CUDA(cudaStreamWaitEvent(s2, h->ev_head, 0));
+      DQN_CUDA(cudaStreamWaitEvent(s2, h->ev_head, 0));
       OptArgs ea;
       fill_segs(h, &ea, nsplit, false);
       ea.world = h->dp_world;
@@ -1362,7 +1377,8 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       return 0;
     };
     if (h->precision == 1) {
-      launch_wgrad_tc<F4, __nv_bfloat16, 128>(h, 3, h->act_bf[0][2], k, sd, &nsplit[3]);
+      launch_wgrad_tc<F4, __nv_bfloat16, 128>(h, 3, h->act_bf[0][2], k, sh, &nsplit[3]);
+      DQN_CUDA(cudaEventRecord(h->ev_head, sh));
       if (!fused) {                  // the fused kernel already produced the fc data gradient
         if (k <= 256) launch_dgrad_tc<F4, 64>(h, 3, k, st);
         else launch_dgrad_tc<F4, 256>(h, 3, k, st);
@@ -1374,7 +1390,8 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       launch_wgrad_tc<C2, __nv_bfloat16, 64>(h, 1, h->act_bf[0][0], k, sd, &nsplit[1]); if (h->no_resident) launch_dgrad_tc<C2, 32>(h, 1, k, st); else launch_dgrad_res<C2, 32, 4, 1>(h, 1, k, st);
       launch_wgrad_tc<C1, uint8_t, 32>(h, 0, d_states, k, st, &nsplit[0]);
     } else if (nat) {
-      launch_wgrad<NF, float>(h, 3, h->act[0][2], k, sd, &nsplit[3]); launch_dgrad<NF>(h, 3, k, st);
+      launch_wgrad<NF, float>(h, 3, h->act[0][2], k, sh, &nsplit[3]); launch_dgrad<NF>(h, 3, k, st);
+      DQN_CUDA(cudaEventRecord(h->ev_head, sh));
       if (fork_after_dgrad(1)) return DQN_ERR_CUDA;
       launch_wgrad<N3, float>(h, 2, h->act[0][1], k, sd, &nsplit[2]); launch_dgrad<N3>(h, 2, k, st);
       if (early_exchange()) return DQN_ERR_CUDA;
@@ -1383,7 +1400,8 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       if (u8) launch_wgrad<N1, uint8_t>(h, 0, d_states, k, st, &nsplit[0]);
       else launch_wgrad<N1, float>(h, 0, d_states, k, st, &nsplit[0]);
     } else {
-      launch_wgrad<F4, float>(h, 3, h->act[0][2], k, sd, &nsplit[3]); launch_dgrad<F4>(h, 3, k, st);
+      launch_wgrad<F4, float>(h, 3, h->act[0][2], k, sh, &nsplit[3]); launch_dgrad<F4>(h, 3, k, st);
+      DQN_CUDA(cudaEventRecord(h->ev_head, sh));
       if (fork_after_dgrad(1)) return DQN_ERR_CUDA;
       launch_wgrad<C3, float>(h, 2, h->act[0][1], k, sd, &nsplit[2]); launch_dgrad<C3>(h, 2, k, st);
       if (early_exchange()) return DQN_ERR_CUDA;
@@ -1396,7 +1414,7 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
     // join
     DQN_CUDA(cudaEventRecord(h->ev_join, sd));
     DQN_CUDA(cudaStreamWaitEvent(st, h->ev_join, 0));
-    if (fused) DQN_CUDA(cudaStreamWaitEvent(st, h->ev_head, 0));
+    DQN_CUDA(cudaStreamWaitEvent(st, h->ev_head, 0));
     DQN_CUDA(cudaGetLastError());
     if (mode == 2) {
       // late half of the exchange: conv1 and conv2 (segments 0, 1) are published here and summed by the optimizer
