@@ -57,7 +57,7 @@ def parse():
     ap.add_argument("--precision", default="bf16", choices=["fp32", "bf16"],
                     help="bf16 = tcgen05 tensor-core mode (parity 2e-2, default; cnn arch); fp32 = CUDA-core parity mode (1e-4)")
     ap.add_argument("--cpu-steps", type=int, default=20)
-    ap.add_argument("--e2e-steps", type=int, default=300)
+    ap.add_argument("--e2e-steps", type=int, default=2000)
     ap.add_argument("--skip-cpu", action="store_true")
     return ap.parse_args()
 

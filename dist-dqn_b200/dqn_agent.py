@@ -121,9 +121,15 @@ class DQNAgent(object):
             return
         indices = rm.sample_indices(minibatch_size)               # random.sample on the global generator
         want_loss = self._should_log_summary()
+        self._last_slot = None
         loss = self._device_step(minibatch_size, indices, want_loss)
         if want_loss:
-            if self.async_summary:
+            if self.async_summary and self._last_slot is not None:
+                # graph replay: the loss lands in the slot's pinned buffer when the slot's event fires
+                previous, self._pending = self._pending, (self._last_slot, self.training_steps)
+                if previous is not None:
+                    self._collect(previous)
+            elif self.async_summary:
                 self._read_loss_later(loss, self.training_steps)
             else:
                 self.last_loss = float(loss.item())
@@ -150,8 +156,12 @@ class DQNAgent(object):
 
     def _collect(self, pending):
         t, step = pending
-        self._loss_evt[t].synchronize()
-        self.last_loss = float(self._loss_pin[t].item())
+        if isinstance(t, dict):                                   # a graph slot
+            t['evt'].synchronize()
+            self.last_loss = float(t['loss_np'][0])
+        else:
+            self._loss_evt[t].synchronize()
+            self.last_loss = float(self._loss_pin[t].item())
         if self.summary_writer is not None:
             self.summary_writer.add_summary(self.last_loss, step)
 
@@ -196,10 +206,14 @@ class DQNAgent(object):
             pin.numpy()[:] = indices
             d_idx = torch.empty(k, dtype=torch.int32, device=self.network.device)
             graph = torch.cuda.CUDAGraph()
+            loss_pin = torch.zeros(1, dtype=torch.float32, pin_memory=True) if want_loss else None
             with torch.cuda.graph(graph):
                 d_idx.copy_(pin, non_blocking=True)
                 out = self._eager_step(k, d_idx, want_loss)
-            g.append(dict(graph=graph, out=out, pin=pin, pin_np=pin.numpy(), d_idx=d_idx, evt=torch.cuda.Event(), used=False))
+                if want_loss:                                     # the loss comes back inside the graph: no extra host call per update
+                    loss_pin.copy_(out, non_blocking=True)
+            g.append(dict(graph=graph, out=out, pin=pin, pin_np=pin.numpy(), d_idx=d_idx, evt=torch.cuda.Event(), used=False,
+                          loss_pin=loss_pin, loss_np=loss_pin.numpy() if want_loss else None))
         slot = g[self.training_steps & 1] if len(g) == 2 else g[-1]
         if slot['used']:
             slot['evt'].synchronize()                             # the previous replay of this graph has consumed its indices
@@ -208,6 +222,7 @@ class DQNAgent(object):
         slot['graph'].replay()
         slot['evt'].record()
         slot['used'] = True
+        self._last_slot = slot
         return slot['out']
 
     # ------------------------------------------------------------------ acting (dqn_agent.py:145-189)

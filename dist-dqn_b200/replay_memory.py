@@ -22,6 +22,7 @@ import numpy as np
 import _cabi as _c
 
 Batch = collections.namedtuple("Batch", "states next_states actions rewards terminals indices")
+_PUSH = _c.lib.dqn_replay_push
 
 
 class ReplayMemory(object):
@@ -105,14 +106,14 @@ class ReplayMemory(object):
         if (self._trusted and state is self._last_next and self._h is not None
                 and self._last_next_pos == self._frames_total - 1):
             # fast lane (the agent loop, dqn_agent.py:96-100): one new frame, one C call
-            S = self._stack[0]
-            if S > 1:
+            if self._scratch is not None:
                 np.copyto(self._scratch, observation[..., -1])
-                src = self._scratch
+                ptr = self._scratch_ptr                      # cached: ndarray.ctypes is a slow attribute
             else:
-                src = np.ascontiguousarray(observation)
-            _c.check(_c.lib.dqn_replay_push(self._h, src.ctypes.data, int(action), float(reward), 1 if terminal else 0),
-                     "ReplayMemory.add")
+                ptr = np.ascontiguousarray(observation).ctypes.data
+            rc = _PUSH(self._h, ptr, int(action), float(reward), 1 if terminal else 0)
+            if rc:
+                _c.check(rc, "ReplayMemory.add")
             self._last_next = observation
             self._last_next_pos += 1
             self._frames_total += 1
@@ -148,6 +149,7 @@ class ReplayMemory(object):
             self._size += 1
         if self._scratch is None and S > 1:
             self._scratch = np.empty(self._stack[1], self._stack[2])
+            self._scratch_ptr = self._scratch.ctypes.data
 
     def size(self):
         return self._size
