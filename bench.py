@@ -602,12 +602,15 @@ def run_e2e(args, cfg, net, rm, world, dev, DQNAgent, FrameBuffer, dist):
     loss = agent.last_loss
     assert loss is not None and np.isfinite(loss)
     agent._graphs.clear()
-    h2d = cfg.update_freq * (FRAME + 32) + 16 + batch * 4
+    # the step graph copies a fixed prefix of the pinned staging buffer: 8 frame slots + header + 8 records, and the indices
+    gi = rm.GRAPH_INGEST_FRAMES
+    h2d = gi * FRAME + 64 + gi * 32 + batch * 4
     return {"value": world * n / dt, "unit": "updates/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
             "steps": n, "ms_per_step": dt / n * 1e3,
             "path": "FrameBuffer.append/get_state + ReplayMemory.add x%d (host uint8 frames) + DQNAgent._train_minibatch "
-                    "(random.sample on host; every update's loss is copied to pinned host memory and collected one "
-                    "update later)" % cfg.update_freq}
+                    "(random.sample on host; one CUDA-graph launch per update moves the staged frames into the ring, "
+                    "gathers, updates and copies the loss to pinned host memory, where it is collected one update later)"
+                    % cfg.update_freq}
 
 
 _REAL_STDOUT = None

@@ -46,6 +46,8 @@ SIGNATURES = {
     "dqn_replay_add": (C.c_int, [c_vp, c_i64, c_i64, c_i32, c_f64, c_u8]),
     "dqn_replay_push": (C.c_int, [c_vp, c_vp, c_i32, c_f64, c_u8]),
     "dqn_replay_flush": (C.c_int, [c_vp, c_vp]),
+    "dqn_replay_seal": (C.c_int, [c_vp, C.POINTER(c_i32), c_vp]),
+    "dqn_replay_ingest_staged": (C.c_int, [c_vp, c_i32, c_vp, c_vp, c_i32, c_vp]),
     "dqn_replay_size": (C.c_int, [c_vp, C.POINTER(c_i64), C.POINTER(c_i64)]),
     "dqn_replay_next_frame_pos": (C.c_int, [c_vp, C.POINTER(c_i64)]),
     "dqn_replay_gather": (C.c_int, [c_vp, c_vp, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),

@@ -14,6 +14,7 @@
 #include "common.cuh"
 
 #include <atomic>
+#include <cstring>
 #include <new>
 #include <vector>
 
@@ -165,6 +166,40 @@ gather_generic_kernel(RingView rv, const int32_t* __restrict__ idx, int32_t k, i
   }
 }
 
+// Graph-embedded ingest: this kernel reads a pinned staging buffer of the host DIRECTLY (zero-copy over PCIe: header +
+// up to kGraphIngest records, up to kGraphIngest frames -- copy-engine memcpy nodes cost several microseconds each
+// inside a graph) and scatters it into the ring.  Block j moves frame j; block 0 also writes the records, the ring's
+// {head, size} and copies the sample indices of the update from pinned memory to the device.
+struct IngestHdr {
+  int32_t nframes, nrecs;
+  int64_t first_frame_pos, first_rec, head, size;
+  int64_t pad[3];
+};
+static_assert(sizeof(IngestHdr) == 64, "header is one 64-byte block");
+
+__global__ void __launch_bounds__(256)
+ingest_kernel(const uint8_t* __restrict__ meta_blk, const uint8_t* __restrict__ frames_blk, uint8_t* __restrict__ d_frames,
+              TransitionRec* __restrict__ d_meta, int64_t* __restrict__ d_state, int64_t fcap, int64_t cap, int32_t pitch,
+              const int32_t* __restrict__ host_idx, int32_t* __restrict__ d_idx, int32_t k) {
+  if (blockIdx.x == 0 && host_idx)
+    for (int i = threadIdx.x; i < k; i += blockDim.x) d_idx[i] = host_idx[i];
+  const IngestHdr hd = *reinterpret_cast<const IngestHdr*>(meta_blk);
+  const int j = blockIdx.x;
+  if (j < hd.nframes) {
+    const uint4* src = reinterpret_cast<const uint4*>(frames_blk + (size_t)j * pitch);
+    uint4* dst = reinterpret_cast<uint4*>(d_frames + ((hd.first_frame_pos + j) % fcap) * (int64_t)pitch);
+    for (int i = threadIdx.x; i < pitch / 16; i += blockDim.x) dst[i] = src[i];
+  }
+  if (j == 0 && (hd.nframes > 0 || hd.nrecs > 0)) {
+    const uint4* rs = reinterpret_cast<const uint4*>(meta_blk + sizeof(IngestHdr));
+    for (int i = threadIdx.x; i < hd.nrecs * 2; i += blockDim.x) {          // a record is two 16-byte halves
+      const int r = i >> 1;
+      reinterpret_cast<uint4*>(d_meta + (hd.first_rec + r) % cap)[i & 1] = rs[i];
+    }
+    if (threadIdx.x == 0) { d_state[0] = hd.head; d_state[1] = hd.size; }
+  }
+}
+
 }  // namespace dqn
 
 // ---------------------------------------------------------------------------------------------
@@ -175,11 +210,15 @@ using namespace dqn;
 namespace {
 constexpr int kStageFrames = 64;       // frames per pinned staging buffer
 constexpr int kStageRecs = 1024;       // transition records per pinned staging buffer
+constexpr int kStages = 3;             // pinned staging buffers (the host may run one update ahead of the GPU)
+constexpr int kGraphIngest = 8;        // frames / records a step graph ingests per replay (dqn_replay_seal)
+constexpr size_t kIngestMetaBytes = sizeof(IngestHdr) + kGraphIngest * sizeof(TransitionRec);
 
 struct Stage {
   uint8_t* frames = nullptr;   // pinned, kStageFrames x pitch
   TransitionRec* recs = nullptr;   // pinned
   int64_t* ring_state = nullptr;   // pinned {head,size}
+  uint8_t* ing = nullptr;          // pinned: IngestHdr + kGraphIngest records (graph-embedded ingest)
   int64_t first_frame_pos = 0;
   int nframes = 0;
   int64_t first_rec = 0;   // total_adds index of recs[0]
@@ -200,7 +239,7 @@ struct dqn_replay_s {
   int64_t total_frames = 0;   // frames ever appended (= next frame position)
   std::vector<int64_t> need;  // per record slot: oldest frame position the transition references
   int64_t last_need = 0;
-  Stage stage[2];
+  Stage stage[kStages];
   int cur = 0;
   cudaStream_t last_stream = nullptr;
   int sticky = 0;
@@ -253,7 +292,7 @@ static int flush_impl(dqn_replay_s* h, cudaStream_t stream) {
   DQN_CUDA(cudaEventRecord(s.done, stream));
   s.in_flight = true;
   s.nframes = s.nrecs = 0;
-  h->cur ^= 1;
+  h->cur = (h->cur + 1) % kStages;
   h->last_stream = stream;
   int rc = wait_stage(h->stage[h->cur]);   // the buffer we are about to fill must be idle
   if (rc) return rc;
@@ -290,10 +329,13 @@ extern "C" int dqn_replay_create(dqn_replay_t* out, int64_t capacity, int64_t fr
   if (e == cudaSuccess) e = cudaMalloc(&h->d_meta, (size_t)h->cap * sizeof(TransitionRec));
   if (e == cudaSuccess) e = cudaMalloc(&h->d_state, 2 * sizeof(int64_t));
   if (e == cudaSuccess) e = cudaMemset(h->d_state, 0, 2 * sizeof(int64_t));
-  for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
+
+  for (int i = 0; i < kStages && e == cudaSuccess; ++i) {
     e = cudaMallocHost(&h->stage[i].frames, (size_t)kStageFrames * h->pitch);
     if (e == cudaSuccess) e = cudaMallocHost(&h->stage[i].recs, kStageRecs * sizeof(TransitionRec));
     if (e == cudaSuccess) e = cudaMallocHost(&h->stage[i].ring_state, 2 * sizeof(int64_t));
+    if (e == cudaSuccess) e = cudaMallocHost(&h->stage[i].ing, kIngestMetaBytes);
+    if (e == cudaSuccess) memset(h->stage[i].ing, 0, kIngestMetaBytes);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->stage[i].done, cudaEventDisableTiming);
   }
   if (e != cudaSuccess) {
@@ -311,10 +353,12 @@ extern "C" int dqn_replay_destroy(dqn_replay_t h) {
   DeviceGuard g(h->device);
   cudaDeviceSynchronize();
   cudaFree(h->d_frames); cudaFree(h->d_meta); cudaFree(h->d_state);
-  for (int i = 0; i < 2; ++i) {
+
+  for (int i = 0; i < kStages; ++i) {
     if (h->stage[i].frames) cudaFreeHost(h->stage[i].frames);
     if (h->stage[i].recs) cudaFreeHost(h->stage[i].recs);
     if (h->stage[i].ring_state) cudaFreeHost(h->stage[i].ring_state);
+    if (h->stage[i].ing) cudaFreeHost(h->stage[i].ing);
     if (h->stage[i].done) cudaEventDestroy(h->stage[i].done);
   }
   delete h;
@@ -428,6 +472,44 @@ extern "C" int dqn_replay_flush(dqn_replay_t h, dqn_stream_t stream) {
   DQN_REQUIRE(h, DQN_ERR_INVALID, "flush: NULL handle");
   DeviceGuard g(h->device);
   return flush_impl(h, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int dqn_replay_seal(dqn_replay_t h, int32_t* stage, dqn_stream_t stream) {
+  DQN_REQUIRE(h && stage, DQN_ERR_INVALID, "seal: NULL argument");
+  DeviceGuard g(h->device);
+  const int i = h->cur;
+  Stage& s = h->stage[i];
+  IngestHdr* hd = reinterpret_cast<IngestHdr*>(s.ing);
+  *stage = i;
+  if (s.nframes > kGraphIngest || s.nrecs > kGraphIngest) {
+    // too much for the fixed-size copy of the graph: flush now (eager copies), the graph's ingest sees an empty header
+    hd->nframes = 0; hd->nrecs = 0;
+    return flush_impl(h, stream ? static_cast<cudaStream_t>(stream) : h->last_stream);   // NULL: the stream of the last gather / flush
+  }
+  hd->nframes = s.nframes; hd->nrecs = s.nrecs;
+  hd->first_frame_pos = s.first_frame_pos; hd->first_rec = s.first_rec;
+  const int64_t sz = live_size(h);
+  hd->head = (h->total_adds - sz) % h->cap; hd->size = sz;
+  if (s.nrecs) memcpy(s.ing + sizeof(IngestHdr), s.recs, (size_t)s.nrecs * sizeof(TransitionRec));
+  s.nframes = s.nrecs = 0;
+  s.in_flight = false;                  // completion of the graph that reads this buffer is the caller's to track
+  h->cur = (h->cur + 1) % kStages;
+  if (stream) h->last_stream = static_cast<cudaStream_t>(stream);
+  return wait_stage(h->stage[h->cur]);  // the buffer we are about to fill may still be the source of an eager flush
+}
+
+extern "C" int dqn_replay_ingest_staged(dqn_replay_t h, int32_t stage, const int32_t* pinned_idx, int32_t* d_idx, int32_t k,
+                                        dqn_stream_t stream) {
+  DQN_REQUIRE(h && stage >= 0 && stage < kStages, DQN_ERR_INVALID, "ingest_staged: bad argument");
+  DeviceGuard g(h->device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  Stage& s = h->stage[stage];
+  DQN_REQUIRE((pinned_idx == nullptr) == (d_idx == nullptr) && k >= 0, DQN_ERR_INVALID, "ingest_staged: index pointers");
+  dqn::count_launch();
+  ingest_kernel<<<kGraphIngest, 256, 0, st>>>(s.ing, s.frames, h->d_frames, h->d_meta, h->d_state, h->fcap, h->cap, h->pitch,
+                                              pinned_idx, d_idx, k);
+  DQN_CUDA(cudaGetLastError());
+  return 0;
 }
 
 extern "C" int dqn_replay_size(dqn_replay_t h, int64_t* size, int64_t* capacity) {

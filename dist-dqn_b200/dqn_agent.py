@@ -71,6 +71,7 @@ class DQNAgent(object):
         # and picked up when update s+1 is launched, so the host never idles on the GPU (flush_summaries() drains it)
         self.async_summary = bool(getattr(config, 'async_summary', True))
         self._pending = None
+        self._stage_evt = [None, None, None]
 
         self._prefill_replay_memory(config.replay_start_size)     # dqn_agent.py:47
         self._update_target_network()                             # dqn_agent.py:50 (step 0 always syncs)
@@ -171,24 +172,29 @@ class DQNAgent(object):
             pending, self._pending = self._pending, None
             self._collect(pending)
 
-    def _eager_step(self, k, d_idx, want_loss):
+    def _eager_step(self, k, d_idx, want_loss, loss_out=None):
         net, rm = self.network, self.replay_memory
         if self._world == 1:
-            return net.train_step(rm, k, d_indices=d_idx, want_loss=want_loss)
+            return net.train_step(rm, k, d_indices=d_idx, want_loss=want_loss, loss_out=loss_out)
         if getattr(net, 'peers_connected', False):     # gradient exchange fused into the optimizer (NVLink peer loads)
-            return net.dp_train_step(rm, k, d_indices=d_idx, want_loss=want_loss)
+            return net.dp_train_step(rm, k, d_indices=d_idx, want_loss=want_loss, loss_out=loss_out)
         import torch.distributed as dist
         batch = rm.gather(d_idx)
         loss, _ = net.backward_on_batch(batch, want_loss=want_loss)
         dist.all_reduce(net.flat_buffer('grad'))                  # sum; grad_scale = 1/world applied by the update
         net.apply_gradients()
+        if want_loss and loss_out is not None:
+            loss_out.copy_(loss, non_blocking=True)
+            return loss_out
         return loss
 
     def _device_step(self, k, indices, want_loss):
-        """One update for the given logical sample indices (host list).  After two eager calls per (k, want_loss) the
-        step is replayed as a CUDA graph whose first node copies the indices from pinned host memory, so a replay
-        costs the host one small memcpy into that pinned buffer and one graph launch.  Two graphs alternate so that
-        the pinned buffer of the update in flight is never overwritten."""
+        """One update for the given logical sample indices (host list).  The first call per (k, want_loss) runs eagerly;
+        afterwards the step is replayed as a CUDA graph that (1) moves the frames / transitions staged by
+        ``ReplayMemory.add`` since the last update from pinned memory into the ring, (2) copies the indices from pinned
+        memory, (3) runs gather + update, (4) copies the loss back to pinned memory.  A replay costs the host:
+        ``seal`` (header writes), a 128-byte copy and one graph launch.  One graph per pinned staging buffer (three
+        rotate), so neither the staging buffer nor the index buffer of the update in flight is overwritten."""
         import torch
         rm = self.replay_memory
         if not self.use_cuda_graph:
@@ -196,32 +202,34 @@ class DQNAgent(object):
         key = (k, bool(want_loss))
         g = self._graphs.get(key)
         if g is None:
-            # first call per shape runs eagerly (loads kernels, sizes buffers); the next ones are captured
-            self._graphs[key] = []
+            self._graphs[key] = {}
             return self._eager_step(k, rm.upload_indices(indices), want_loss)
-        if len(g) < 2:
-            rm.flush()
+        stage = rm.seal()                                         # staged frames of buffer `stage` ride along with this update
+        other = self._stage_evt[(stage + 1) % 3]
+        if other is not None:
+            other.synchronize()                                   # adds now refill the next buffer: its last reader (two updates back) must be done
+        slot = g.get(stage)
+        if slot is None:
             torch.cuda.synchronize()
             pin = torch.empty(k, dtype=torch.int32, pin_memory=True)
-            pin.numpy()[:] = indices
             d_idx = torch.empty(k, dtype=torch.int32, device=self.network.device)
             graph = torch.cuda.CUDAGraph()
             loss_pin = torch.zeros(1, dtype=torch.float32, pin_memory=True) if want_loss else None
             with torch.cuda.graph(graph):
-                d_idx.copy_(pin, non_blocking=True)
-                out = self._eager_step(k, d_idx, want_loss)
-                if want_loss:                                     # the loss comes back inside the graph: no extra host call per update
-                    loss_pin.copy_(out, non_blocking=True)
-            g.append(dict(graph=graph, out=out, pin=pin, pin_np=pin.numpy(), d_idx=d_idx, evt=torch.cuda.Event(), used=False,
-                          loss_pin=loss_pin, loss_np=loss_pin.numpy() if want_loss else None))
-        slot = g[self.training_steps & 1] if len(g) == 2 else g[-1]
-        if slot['used']:
+                # no copy-engine nodes (several microseconds each inside a graph): the ingest kernel reads the pinned
+                # staging buffer and the pinned indices itself, the loss kernel writes the pinned loss word itself
+                rm.ingest_staged(stage, pin, d_idx)
+                out = self._eager_step(k, d_idx, want_loss, loss_pin)
+            slot = dict(graph=graph, out=out, pin=pin, pin_np=pin.numpy(), d_idx=d_idx, evt=torch.cuda.Event(), used=False,
+                        loss_pin=loss_pin, loss_np=loss_pin.numpy() if want_loss else None)
+            g[stage] = slot
+        elif slot['used']:
             slot['evt'].synchronize()                             # the previous replay of this graph has consumed its indices
         slot['pin_np'][:] = indices
-        rm.flush()                                                # staged frames go in before the graph reads the ring
         slot['graph'].replay()
         slot['evt'].record()
         slot['used'] = True
+        self._stage_evt[stage] = slot['evt']
         self._last_slot = slot
         return slot['out']
 

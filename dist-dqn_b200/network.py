@@ -252,13 +252,16 @@ class Network(object):
         _c.check(_c.lib.dqn_net_download(self._h, _c.BUF['grad'], flat.ctypes.data, flat.size), 'get_grads')
         return self._unflatten(flat)
 
-    def train_step(self, replay_memory, k, d_indices=None, want_loss=False):
-        """Sample-to-update in one C call: gather (ring -> stacks) + the whole update."""
+    def train_step(self, replay_memory, k, d_indices=None, want_loss=False, loss_out=None):
+        """Sample-to-update in one C call: gather (ring -> stacks) + the whole update.  ``loss_out``: a 1-element
+        float32 tensor the loss kernel writes to instead of the network's own device scalar (a pinned host tensor
+        works: the device writes it over PCIe, which saves a copy node in a captured step)."""
         if d_indices is None:
             d_indices = replay_memory.upload_indices(replay_memory.sample_indices(k))
+        out = (loss_out if loss_out is not None else self._loss) if want_loss else None
         _c.check(_c.lib.dqn_train_step(self._h, replay_memory.handle, d_indices.data_ptr(), int(k),
-                                       self._loss.data_ptr() if want_loss else None, _c.current_stream()), 'train_step')
-        return self._loss if want_loss else None
+                                       out.data_ptr() if want_loss else None, _c.current_stream()), 'train_step')
+        return out
 
     # ------------------------------------------------------------------ checkpoint / resume
     def save(self, path, extra=None):
@@ -309,13 +312,14 @@ class Network(object):
                                         k, self._loss.data_ptr() if want_loss else None, _c.current_stream()), 'dp_step')
         return self._loss if want_loss else None
 
-    def dp_train_step(self, replay_memory, k, d_indices=None, want_loss=False):
+    def dp_train_step(self, replay_memory, k, d_indices=None, want_loss=False, loss_out=None):
         if d_indices is None:
             d_indices = replay_memory.upload_indices(replay_memory.sample_indices(k))
+        out = (loss_out if loss_out is not None else self._loss) if want_loss else None
         _c.check(_c.lib.dqn_train_step_dp(self._h, replay_memory.handle, d_indices.data_ptr(), int(k),
-                                          self._loss.data_ptr() if want_loss else None, _c.current_stream()),
+                                          out.data_ptr() if want_loss else None, _c.current_stream()),
                  'dp_train_step')
-        return self._loss if want_loss else None
+        return out
 
     def sync_target(self):
         """The assign ops of network.py:251-252 as one device memcpy."""

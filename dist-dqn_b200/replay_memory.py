@@ -42,6 +42,8 @@ class ReplayMemory(object):
         self._size = 0               # host mirror of the ring's counters (saves ctypes round trips on the hot path)
         self._frames_total = 0
         self._scratch = None
+        self._stage_out = _c.c_i32()
+        self._stage_ref = _c.C.byref(self._stage_out)
 
     # ------------------------------------------------------------------ construction of the ring
     @staticmethod
@@ -260,3 +262,21 @@ class ReplayMemory(object):
     def flush(self):
         if self._h is not None:
             _c.check(_c.lib.dqn_replay_flush(self._h, _c.current_stream()), "ReplayMemory.flush")
+
+    # graph-embedded ingest (see include/dqn_b200.h): the step graph itself moves the staged frames to the ring
+    GRAPH_INGEST_FRAMES = 8
+
+    def seal(self):
+        """Host-only: publishes the current staging buffer for the step graph and switches to the other one;
+        returns the index of the sealed buffer."""
+        rc = _c.lib.dqn_replay_seal(self._h, self._stage_ref, None)     # the stream only matters for the eager fallback
+        if rc:
+            _c.check(rc, "ReplayMemory.seal")
+        return self._stage_out.value
+
+    def ingest_staged(self, stage, pinned_idx=None, d_idx=None):
+        """Enqueues (capturable) the kernel that scatters staging buffer ``stage`` into the ring; optionally the same
+        kernel copies the sample indices from a pinned host tensor to a device tensor."""
+        k = 0 if pinned_idx is None else int(pinned_idx.numel())
+        _c.check(_c.lib.dqn_replay_ingest_staged(self._h, int(stage), _c.ptr(pinned_idx), _c.ptr(d_idx), k,
+                                                 _c.current_stream()), "ReplayMemory.ingest_staged")

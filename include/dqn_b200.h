@@ -113,6 +113,21 @@ int dqn_replay_add(dqn_replay_t h, int64_t state_pos, int64_t next_pos, int32_t 
 int dqn_replay_push(dqn_replay_t h, const void* host_frame, int32_t action, double reward, uint8_t terminal);
 /* Sends staged frames + records to the device (async H2D on stream). Called by gather itself. */
 int dqn_replay_flush(dqn_replay_t h, dqn_stream_t stream);
+
+/* Graph-embedded ingest (no reference counterpart: it removes the per-update host calls of the H2D path that
+ * ReplayMemory.add feeds, replay_memory.py:22-23).
+ * dqn_replay_seal is host-only work: it publishes the header of the current pinned staging buffer (frame / record
+ * counts and positions, ring head and size), switches staging to the next of the 3 buffers (round robin) and returns
+ * the index (0..2) of the sealed one in *stage.  A buffer holding more than 8 frames or 8 records is flushed eagerly on `stream` instead and
+ * its header reads empty.  Before the next dqn_replay_push the caller must know that the last
+ * dqn_replay_ingest_staged of the NEXT buffer ((*stage + 1) % 3) has completed (its pinned memory is refilled from now
+ * on).
+ * dqn_replay_ingest_staged enqueues ONE kernel with fixed addresses (capturable in a CUDA graph) that reads staging
+ * buffer `stage` straight from pinned host memory and scatters its frames / records into the ring; if pinned_idx is
+ * given (pinned host memory, k int32) it also copies the update's sample indices to d_idx. */
+int dqn_replay_seal(dqn_replay_t h, int32_t* stage, dqn_stream_t stream);
+int dqn_replay_ingest_staged(dqn_replay_t h, int32_t stage, const int32_t* pinned_idx, int32_t* d_idx, int32_t k,
+                             dqn_stream_t stream);
 /* ReplayMemory.size / capacity (replay_memory.py:25-29); host-side counters, no sync. */
 int dqn_replay_size(dqn_replay_t h, int64_t* size, int64_t* capacity);
 /* Frame-ring position that the next appended frame will get. */

@@ -101,6 +101,44 @@ def test_atari_shaped_agent_loop_with_cuda_graph():
     assert 0.1 <= agent.random_action_prob < 1.0
 
 
+def test_graph_embedded_ingest_keeps_the_ring_identical_to_the_reference_deque():
+    """The captured step moves the frames staged by ReplayMemory.add into the ring itself (dqn_replay_seal /
+    dqn_replay_ingest_staged).  After a graph-driven agent loop -- including episode starts, which stage a full stack --
+    the ring must hold exactly what the reference's deque(maxlen) holds (replay_memory.py:19-29), bit for bit."""
+    _cuda()
+    import collections
+    import envs
+    from dqn_agent import DQNAgent
+    from network import Network, Session
+    from replay_memory import ReplayMemory
+    cfg = _control_config(network='cnn', optimizer='rmsprop', lr=0.00025, minibatch_size=32, max_batch=32, num_episodes=4,
+                          max_steps_per_episode=50, replay_memory_capacity=150, target_update_freq=20, reward_discount=0.99,
+                          frames_per_state=4, resize_width=84, resize_height=84, update_freq=4, replay_start_size=40,
+                          summary_freq=3, init_random_action_prob=1.0, precision='bf16')
+    random.seed(3)
+    env = envs.SyntheticAtariEnv('SyntheticPong-v0', num_actions=6, seed=9, min_len=20, max_len=45)
+    net = Network.create_network(cfg, DQNAgent.get_input_shape(env, cfg), env.action_space.n)
+    rm = ReplayMemory(cfg.replay_memory_capacity, trusted=True)
+    mirror = collections.deque(maxlen=cfg.replay_memory_capacity)
+    real_add = rm.add
+
+    def add(state, action, reward, observation, terminal):
+        mirror.append((np.array(state, copy=True), int(action), float(reward), np.array(observation, copy=True), bool(terminal)))
+        real_add(state, action, reward, observation, terminal)
+
+    rm.add = add
+    agent = DQNAgent(env, net, Session(), rm, cfg)
+    agent.train(cfg.num_episodes, cfg.max_steps_per_episode)
+    assert agent.training_steps >= 30 and len(agent._graphs) >= 1       # the graph path ran (and wrapped the ring: 150 < adds)
+    assert rm.size() == len(mirror) == cfg.replay_memory_capacity
+    b = rm.sample(rm.size(), indices=list(range(rm.size())))
+    states, nexts = b.states.cpu().numpy(), b.next_states.cpu().numpy()
+    acts, rews, terms = b.actions.cpu().numpy(), b.rewards.cpu().numpy(), b.terminals.cpu().numpy()
+    for i, (s0, a0, r0, s1, t0) in enumerate(mirror):
+        assert np.array_equal(states[i], s0) and np.array_equal(nexts[i], s1), i
+        assert acts[i] == a0 and rews[i] == r0 and bool(terms[i]) == t0, i
+
+
 def test_batched_greedy_act_1024_envs():
     """BASELINE config 5: greedy actions for 1024 synthetic env states in one call (chunks of max_batch)."""
     _cuda()
