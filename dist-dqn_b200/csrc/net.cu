@@ -738,7 +738,7 @@ extern "C" int dqn_net_create(dqn_net_t* out, int32_t arch, const int32_t* in_sh
       l.K = K; l.N = N; l.rows = rows; l.in_elems = in_e; l.out_elems = out_e; l.w_tensor = 2 * i;
       const int base = (K / BM) * (N / BN);
       int ms = (3 * h->num_sms + base - 1) / base;
-      l.maxsplit = ms < 1 ? 1 : (ms > 96 ? 96 : ms);
+      l.maxsplit = ms < 1 ? 1 : (ms > h->num_sms ? h->num_sms : ms);
     };
     if (!nat) {
       setL(0, C1::K, C1::COUT, C1::ROWS, 84 * 84 * 4, C1::OUT_PER_SAMPLE);
@@ -1060,6 +1060,27 @@ static void launch_wgrad_tc(dqn_net_s* h, int l, const void* x, int B, cudaStrea
   {
     StageScope sc(h, DQN_STAGE_WGRAD_FC + 2 * (3 - l), st);
     launch_pdl(umma::umma_wgrad_kernel<G, TIn, NTILE>, grid, dim3(umma::TT), smem, st, 1, a);
+  }
+  *nsplit_out = ns;
+}
+
+// conv1 weight gradient with the frames resident in shared memory: one CTA per run of consecutive 128-row tiles
+template <class G>
+static void launch_wgrad_res_u8(dqn_net_s* h, const void* x, int B, cudaStream_t st, int* nsplit_out) {
+  constexpr size_t smem = umma::WgradResU8<G>::SMEM;
+  static_assert(smem <= 227 * 1024, "does not fit in shared memory");
+  static bool once = (set_smem(umma::umma_wgrad_res_u8_kernel<G>, smem), true);
+  (void)once;
+  const GemmLayer& L = h->L[0];
+  const int tiles = (B * G::ROWS + umma::TM - 1) / umma::TM;
+  int ns = L.maxsplit < tiles ? L.maxsplit : tiles;
+  if (ns > h->num_sms) ns = h->num_sms;
+  const int per = (tiles + ns - 1) / ns;
+  ns = (tiles + per - 1) / per;
+  umma::WgradArgsT a{x, h->dact_bf[0], h->arg[0][0], L.partial, B, per * umma::TM};
+  {
+    StageScope sc(h, DQN_STAGE_WGRAD_CONV1, st);
+    launch_pdl(umma::umma_wgrad_res_u8_kernel<G>, dim3(ns), dim3(umma::TT), smem, st, 1, a);
   }
   *nsplit_out = ns;
 }
@@ -1388,7 +1409,8 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       if (early_exchange()) return DQN_ERR_CUDA;
       if (fork_after_dgrad(2)) return DQN_ERR_CUDA;
       launch_wgrad_tc<C2, __nv_bfloat16, 64>(h, 1, h->act_bf[0][0], k, sd, &nsplit[1]); if (h->no_resident) launch_dgrad_tc<C2, 32>(h, 1, k, st); else launch_dgrad_res<C2, 32, 4, 1>(h, 1, k, st);
-      launch_wgrad_tc<C1, uint8_t, 32>(h, 0, d_states, k, st, &nsplit[0]);
+      if (h->no_resident) launch_wgrad_tc<C1, uint8_t, 32>(h, 0, d_states, k, st, &nsplit[0]);
+      else launch_wgrad_res_u8<C1>(h, d_states, k, st, &nsplit[0]);
     } else if (nat) {
       launch_wgrad<NF, float>(h, 3, h->act[0][2], k, sh, &nsplit[3]); launch_dgrad<NF>(h, 3, k, st);
       DQN_CUDA(cudaEventRecord(h->ev_head, sh));

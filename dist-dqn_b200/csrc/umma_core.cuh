@@ -140,6 +140,13 @@ __device__ __forceinline__ uint32_t mnmajor_off(int g, int r) { return (uint32_t
 __device__ __forceinline__ uint64_t make_desc_sw128(uint32_t saddr) {
   return make_desc(saddr, 16, 1024) | ((uint64_t)2 << 61);
 }
+// SWIZZLE_128B MN-major descriptor: the atom is 64 MN-elements (128 bytes, 16-byte chunks XOR-ed with k%8) x 8 k-rows 128
+// bytes apart; LBO = distance between 64-element blocks along MN, SBO = distance between 8-row groups along K.  A
+// [rows][64] tile stored as a SWIZZLE_128B K-major image (sw128_off) IS this layout with the roles of the axes swapped
+// (rows = K): the forward A tiles double as the transposed operand of the weight gradient.
+__device__ __forceinline__ uint64_t make_desc_sw128_mn(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  return make_desc(saddr, lbo_bytes, sbo_bytes) | ((uint64_t)2 << 61);
+}
 // byte offset of chunk c (8 reduction elements) of row i in a SWIZZLE_128B K-major stage
 __device__ __forceinline__ uint32_t sw128_off(int i, int c) { return (uint32_t)((i >> 3) * 1024 + (i & 7) * 128 + ((c ^ (i & 7)) << 4)); }
 
@@ -944,6 +951,186 @@ __global__ void __launch_bounds__(TT) umma_wgrad_kernel(WgradArgsT a) {
     for (int j = tid; j < NTILE; j += TT) out[(size_t)G::K * G::COUT + n0 + j] = bias_sm[j];
   }
   teardown(tmem, tmem_cols(NTILE));
+}
+
+// ------------------------------------------------------------------------------------------------ weight gradient, resident uint8 frames
+// conv1 weight gradient  dW[k][n] = sum_rows X[row][k] * dZ[row][n]  (k = (ky,kx,frame) 0..255, n = 0..31) with the rows
+// in the same pool-window order as the forward pass.  A CTA walks over consecutive 128-row tiles (32 pool windows):
+//   * per tile three bulk copies, issued one tile ahead: the band of uint8 input rows (as in umma_fwd_res_u8_kernel),
+//     the 32 windows' gated gradients (2 KB) and arg-max bytes (1 KB);
+//   * the band is widened to bf16 once; A = X^T is built with 16-byte shared->shared copies as four [128 rows][64 k]
+//     SWIZZLE_128B images (the forward pass's A tiles, read MN-major here: 128-byte contiguous operand reads); B = dZ
+//     with the pool routing applied, in the no-swizzle MN-major layout (chunk (n/8, row) at (n/8)*2048 + (row/8)*128 +
+//     (row%8)*16);
+//   * 16 MMAs per tile (2 halves of k x 8 steps of 16 rows) accumulate into TMEM over ALL tiles of the CTA; one fp32
+//     partial [(256+1) x 32] per CTA at the end (summed in fixed order by the optimizer).
+template <class G>
+struct WgradResU8 {
+  using F = FwdResU8<G>;
+  static constexpr uint32_t BAND_BYTES = F::PATCH_BYTES;                 // bf16 band
+  static constexpr uint32_t RAW_BYTES = F::RAW_BYTES;                    // uint8 band, double-buffered
+  static constexpr uint32_t GRAD_BYTES = 32 * G::COUT * 2;               // 32 windows x COUT bf16
+  static constexpr uint32_t ARG_BYTES = 32 * G::COUT;
+  static constexpr uint32_t A_BYTES = G::K * TM * 2;                     // 256 x 128 bf16 = 64 KB
+  static constexpr uint32_t B_BYTES = G::COUT * TM * 2;                  // 32 x 128 bf16 = 8 KB
+  static constexpr uint32_t OFF_A = BAND_BYTES, OFF_B = OFF_A + A_BYTES, OFF_RAW = OFF_B + B_BYTES;
+  static constexpr uint32_t OFF_GRAD = OFF_RAW + 2 * RAW_BYTES, OFF_ARG = OFF_GRAD + 2 * round1k_c(GRAD_BYTES);
+  static constexpr uint32_t SMEM = SMEM_SLACK + OFF_ARG + 2 * round1k_c(ARG_BYTES);
+  static_assert(G::K == 256 && G::COUT == 32 && G::POOL, "written for the reference conv1 (8x8x4 -> 32, pooled)");
+};
+
+// input-row band of the 128-row tile starting at row m0 (see umma_fwd_res_u8_kernel): global row indices b*IH + iy, inclusive
+template <class G>
+__device__ __forceinline__ void conv1_band(int m0, int B, int& grow_lo, int& grow_hi, int& w_first, int& w_last) {
+  constexpr int WPS = G::PH * G::PW;
+  w_first = m0 >> 2;
+  w_last = (m0 + TM - 1) >> 2;
+  if (w_last > B * WPS - 1) w_last = B * WPS - 1;
+  const int bf = w_first / WPS, bl = w_last / WPS;
+  const int pyf = (w_first - bf * WPS) / G::PW, pyl = (w_last - bl * WPS) / G::PW;
+  int iy_lo = 2 * pyf * G::ST - G::PADH;
+  if (iy_lo < 0) iy_lo = 0;
+  int iy_hi = (2 * pyl + 1) * G::ST - G::PADH + G::KS - 1;
+  if (iy_hi > G::IH - 1) iy_hi = G::IH - 1;
+  grow_lo = bf * G::IH + iy_lo;
+  grow_hi = bl * G::IH + iy_hi;
+}
+
+template <class G>
+__global__ void __launch_bounds__(TT) umma_wgrad_res_u8_kernel(WgradArgsT a) {
+  using R = WgradResU8<G>;
+  using F = FwdResU8<G>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align_smem(smem_raw);
+  __shared__ uint64_t bars[2];
+  __shared__ uint64_t ldbar[2];       // a tile's band + gradients + arg-max have landed
+  __shared__ uint64_t done;           // the MMAs of a tile have completed
+  __shared__ uint32_t tmem_slot;
+  __shared__ float bias_part[TT / 32][G::COUT];
+  const uint8_t* __restrict__ x = static_cast<const uint8_t*>(a.x);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) {
+    mbar_init(&ldbar[0], 1);
+    mbar_init(&ldbar[1], 1);
+    mbar_init(&done, 1);
+  }
+  const uint32_t tmem = setup(bars, &tmem_slot, 64);     // two 128 x 32 accumulators (k halves)
+  const uint32_t sbase = smem_u32(smem);
+  const int R_total = a.B * G::ROWS;
+  const int r_begin = blockIdx.x * a.rows_per_split;                   // rows_per_split is a multiple of 128
+  const int r_end = min(R_total, r_begin + a.rows_per_split);
+  const int nt = (r_end - r_begin + TM - 1) / TM;
+  auto issue_loads = [&](int t) {     // thread 0: the three bulk copies of tile t into buffer t&1
+    const int m0 = r_begin + t * TM, buf = t & 1;
+    int glo, ghi, wf, wl;
+    conv1_band<G>(m0, a.B, glo, ghi, wf, wl);
+    const int nrows = ghi - glo + 1, nw = wl - wf + 1;
+    if (nrows > F::PATCH_ROWS) __trap();
+    const uint32_t bb = (uint32_t)nrows * F::ROW_BYTES, gb = (uint32_t)nw * G::COUT * 2, ab = (uint32_t)nw * G::COUT;
+    mbar_expect_tx(&ldbar[buf], bb + gb + ab);
+    bulk_g2s(sbase + R::OFF_RAW + buf * R::RAW_BYTES, x + (size_t)glo * F::ROW_BYTES, bb, &ldbar[buf]);
+    bulk_g2s(sbase + R::OFF_GRAD + buf * round1k_c(R::GRAD_BYTES), a.dactg + (size_t)wf * G::COUT, gb, &ldbar[buf]);
+    bulk_g2s(sbase + R::OFF_ARG + buf * round1k_c(R::ARG_BYTES), a.arg + (size_t)wf * G::COUT, ab, &ldbar[buf]);
+  };
+  pdl_wait_then_trigger();
+  if (tid == 0 && nt > 0) issue_loads(0);
+  // build mapping: tile row r = tid & 127 (lanes along the rows: conflict-free stores), chunk column cq = tid >> 7
+  const int r = tid & (TM - 1), cq = tid >> 7;
+  const uint32_t rdst = (uint32_t)((r >> 3) * 128 + (r & 7) * 16);
+  float colsum[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) colsum[e] = 0.f;
+  constexpr uint32_t idesc = make_idesc(TM, G::COUT, true, true);
+  const int wu = warp_uniform_idx();
+#pragma unroll 1
+  for (int t = 0; t < nt; ++t) {
+    const int m0 = r_begin + t * TM, buf = t & 1;
+    if (tid == 0 && t + 1 < nt) issue_loads(t + 1);                    // buffer (t+1)&1 was consumed by tile t-1 (barrier below)
+    int glo, ghi, wf, wl;
+    conv1_band<G>(m0, a.B, glo, ghi, wf, wl);
+    const Row row = decode_row<G>(m0 + r, a.B);
+    const int iy0 = row.oy * G::ST - G::PADH, ix0 = row.ox * G::ST - G::PADW;
+    const int poff = ((row.b * G::IH + iy0 - glo) * G::IW + ix0) * G::CIN;        // uint8 offset in the band (may be < 0)
+    mbar_wait(&ldbar[buf], (t >> 1) & 1);
+    {
+      const int nchunks = (ghi - glo + 1) * (int)(F::ROW_BYTES / 8);
+      const uint8_t* raw = smem + R::OFF_RAW + buf * R::RAW_BYTES;
+      for (int c = tid; c < nchunks; c += TT) *reinterpret_cast<uint4*>(smem + c * 16) = widen_u8x8(*reinterpret_cast<const uint2*>(raw + c * 8));
+    }
+    if (t > 0) mbar_wait(&done, (t - 1) & 1);                          // the previous tile's MMAs have read A and B
+    __syncthreads();
+    // A = X^T: chunk gg (k = 8*gg..8*gg+7: filter row gg/4, pixels 2*(gg%4), +1) of row r
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      const int gg = cq + 4 * q;
+      const int ky = gg >> 2, kx = 2 * (gg & 3);
+      const bool ok = row.valid && (unsigned)(iy0 + ky) < (unsigned)G::IH && (unsigned)(ix0 + kx) < (unsigned)G::IW;
+      uint4 v = make_uint4(0u, 0u, 0u, 0u);
+      if (ok) v = *reinterpret_cast<const uint4*>(smem + 2 * (poff + (ky * G::IW + kx) * G::CIN));
+      *reinterpret_cast<uint4*>(smem + R::OFF_A + (gg >> 3) * A_STAGE_BYTES + sw128_off(r, gg & 7)) = v;
+    }
+    // B = dZ: channels 8*cq..8*cq+7 of row r, routed through the pool (gradient goes to the arg-max position only)
+    {
+      uint4 z = make_uint4(0u, 0u, 0u, 0u);
+      if (row.valid) {
+        const int wl_ = (m0 + r) >> 2;                                  // this row's pool window
+        const uint4 d = *reinterpret_cast<const uint4*>(smem + R::OFF_GRAD + buf * round1k_c(R::GRAD_BYTES) + ((wl_ - wf) * G::COUT + cq * 8) * 2);
+        const uint2 ag = *reinterpret_cast<const uint2*>(smem + R::OFF_ARG + buf * round1k_c(R::ARG_BYTES) + (wl_ - wf) * G::COUT + cq * 8);
+        z = route_chunk(d, ag, r & 3);
+        add_chunk(colsum, z);
+      }
+      *reinterpret_cast<uint4*>(smem + R::OFF_B + cq * 2048 + rdst) = z;
+    }
+    fence_async_proxy();
+    __syncthreads();
+    if (wu == 0) {
+      tc_fence_after();
+      if (elect_one()) {
+        const uint64_t bd0 = make_desc(sbase + R::OFF_B, 128, 2048);
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt) {
+          // k half mt = images 2*mt, 2*mt+1 (LBO = one image); 16 rows per MMA = two 8-row groups (SBO = 1024)
+          const uint64_t ad0 = make_desc_sw128_mn(sbase + R::OFF_A + mt * 2 * A_STAGE_BYTES, A_STAGE_BYTES, 1024);
+#pragma unroll
+          for (int j = 0; j < TM / 16; ++j)
+            mma_bf16(tmem + mt * 32, desc_advance(ad0, j * 2048), desc_advance(bd0, j * 256), idesc, (t | j) ? 1u : 0u);
+        }
+        mma_commit(&done);
+      }
+      __syncwarp();
+    }
+  }
+  pdl_trigger();
+  float* out = a.partial + (size_t)blockIdx.x * ((size_t)(G::K + 1) * G::COUT);
+  if (nt > 0) {
+    mbar_wait(&done, (nt - 1) & 1);
+    tc_fence_after();
+    if ((warp >> 2) < 2) {                                              // warps 0-3: k 0..127, warps 4-7: k 128..255
+      const int mt = warp >> 2, k = mt * 128 + (warp & 3) * 32 + lane;
+      float v[32];
+      tmem_ld32(tmem + ((uint32_t)((warp & 3) * 32) << 16) + mt * 32, v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        *reinterpret_cast<float4*>(out + (size_t)k * G::COUT + 4 * j) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    }
+  } else {
+    for (int i = tid; i < G::K * G::COUT; i += TT) out[i] = 0.f;
+  }
+  // bias gradient = column sums of dZ: lanes hold different rows of the same 8 channels -> warp sum, then a fixed-order
+  // sum over the 4 warps of each channel group
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    float v = colsum[e];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) bias_part[warp][e] = v;
+  }
+  __syncthreads();
+  if (tid < G::COUT) {
+    const int g = tid >> 3, e = tid & 7;                                // warps 4g..4g+3 hold channel group g
+    out[(size_t)G::K * G::COUT + tid] = ((bias_part[4 * g][e] + bias_part[4 * g + 1][e]) + bias_part[4 * g + 2][e]) + bias_part[4 * g + 3][e];
+  }
+  teardown(tmem, 64);
 }
 
 // ------------------------------------------------------------------------------------------------ data gradient

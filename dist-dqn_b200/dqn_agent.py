@@ -11,6 +11,7 @@ all-reduce inside the same graph (the reference's --sync semantics, network.py:1
 """
 from __future__ import annotations
 
+import atexit
 import json
 import logging
 import os
@@ -26,15 +27,27 @@ from stats import Stats
 
 class SummaryWriter(object):
     """Scalar summaries as JSON lines under ``logdir`` (stands in for tf.train.SummaryWriter,
-    dqn_agent.py:39; only the 'loss' scalar exists in the reference, network.py:154-155)."""
+    dqn_agent.py:39; only the 'loss' scalar exists in the reference, network.py:154-155).  Like the TF writer, which
+    queues events for a background thread, ``add_summary`` does not touch the disk: lines are buffered and written out
+    every ``flush_every`` summaries, on ``flush()`` and at exit."""
 
-    def __init__(self, logdir):
+    def __init__(self, logdir, flush_every=256):
         os.makedirs(logdir, exist_ok=True)
         self._f = open(os.path.join(logdir, 'summaries.jsonl'), 'a')
+        self._lines = []
+        self._flush_every = flush_every
+        atexit.register(self.flush)
 
     def add_summary(self, value, step):
-        self._f.write(json.dumps({'step': int(step), 'loss': float(value)}) + '\n')
-        self._f.flush()
+        self._lines.append('{"step": %d, "loss": %r}\n' % (step, float(value)))
+        if len(self._lines) >= self._flush_every:
+            self.flush()
+
+    def flush(self):
+        if self._lines and not self._f.closed:
+            self._f.write(''.join(self._lines))
+            self._f.flush()
+        self._lines = []
 
 
 class DQNAgent(object):
@@ -171,6 +184,8 @@ class DQNAgent(object):
         if self._pending is not None:
             pending, self._pending = self._pending, None
             self._collect(pending)
+        if self.summary_writer is not None:
+            self.summary_writer.flush()
 
     def _eager_step(self, k, d_idx, want_loss, loss_out=None):
         net, rm = self.network, self.replay_memory
