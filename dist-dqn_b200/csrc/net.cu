@@ -739,6 +739,7 @@ extern "C" int dqn_net_create(dqn_net_t* out, int32_t arch, const int32_t* in_sh
       const int base = (K / BM) * (N / BN);
       int ms = (3 * h->num_sms + base - 1) / base;
       l.maxsplit = ms < 1 ? 1 : (ms > h->num_sms ? h->num_sms : ms);
+      if (i == 0) l.maxsplit = h->num_sms;      // conv1's resident weight-gradient kernel: one CTA per SM
     };
     if (!nat) {
       setL(0, C1::K, C1::COUT, C1::ROWS, 84 * 84 * 4, C1::OUT_PER_SAMPLE);
