@@ -476,10 +476,10 @@ def peaks():
 
 
 def _traffic(name, batch):
-    """DRAM bytes per launch of `name` from the committed ncu --set full capture (taken at B=32), else None."""
+    """DRAM bytes per launch of `name` from the committed ncu --set full captures (taken at B=32 and B=512), else None."""
     try:
         t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-        return t["dram_bytes_per_launch"].get(name) if batch == 32 else None
+        return t["dram_bytes_per_launch"].get(str(batch), {}).get(name)
     except Exception:
         return None
 
@@ -489,8 +489,12 @@ def roofline(kernels, arch, batch, nparams):
     if not kernels:
         return None
     hbm, burst, sustained, src = peaks()
-    name = max(kernels, key=lambda k: kernels[k])
-    us = kernels[name]
+    # only kernels on the critical path of the step (the head / fc / conv3 / conv2 weight gradients and the loss run on
+    # forked streams in the shadow of the data-gradient chain)
+    side = ("head_wgrad", "loss", "wgrad_fc", "wgrad_conv3", "wgrad_conv2")
+    crit = {k: v for k, v in kernels.items() if k not in side} or kernels
+    name = max(crit, key=lambda k: crit[k])
+    us = crit[name]
     macs = MACS[arch]
     layer = {"conv1": 0, "conv2": 1, "conv3": 2, "fc": 3}
     if name.startswith(("fwd_", "wgrad_", "dgrad_")):
@@ -501,7 +505,9 @@ def roofline(kernels, arch, batch, nparams):
         return {"kernel": name, "bound": "tensor", "achieved": ach, "peak": sustained, "unit": "TFLOP/s",
                 "frac": ach / sustained, "traffic": _traffic(name, batch), "us_per_launch": us,
                 "peak_source": src + " bf16 sustained",
-                "note": "implicit GEMM measured against the bf16 tensor-pipe peak (fp32 mode runs on CUDA cores)"}
+                "note": "implicit GEMM measured against the bf16 tensor-pipe peak (fp32 mode runs on CUDA cores); durations "
+                        "come from an instrumented eager pass (CUDA events around every launch, no PDL overlap), which adds "
+                        "several microseconds per launch at batch 32 -- the fraction is meaningful at --batch 512"}
     if name == "gather":
         byts = GATHER_BYTES * batch
     elif name in ("optimizer", "reduce_grad"):
