@@ -256,8 +256,8 @@ def run_b200(args):
     batch = args.batch or 32            # same per-GPU minibatch at every N (weak scaling); --batch 512 = large-batch sweep
     steps = args.steps or (2000 if batch <= 64 else 300)
     warmup = max(3, args.warmup if args.warmup is not None else 50)
-    if args.arch != "cnn":
-        args.precision = "fp32"                     # the tensor-core kernels cover the reference conv net
+    if args.arch not in ("cnn", "nature"):
+        args.precision = "fp32"                     # the tensor-core kernels cover the two conv nets
     cfg = atari_config(batch, args.arch, args.precision)
     cfg.device_index = local
 

@@ -1076,7 +1076,8 @@ static void launch_wgrad_res_u8(dqn_net_s* h, const void* x, int B, cudaStream_t
   const int tiles = (B * G::ROWS + umma::TM - 1) / umma::TM;
   int ns = L.maxsplit < tiles ? L.maxsplit : tiles;
   if (ns > h->num_sms) ns = h->num_sms;
-  const int per = (tiles + ns - 1) / ns;
+  int per = (tiles + ns - 1) / ns;
+  if (per < 2 && tiles > 32) per = 2;      // every partial is read back by the reduce / optimizer kernels: not too many of them
   ns = (tiles + per - 1) / per;
   umma::WgradArgsT a{x, h->dact_bf[0], h->arg[0][0], L.partial, B, per * umma::TM};
   {
@@ -1168,6 +1169,19 @@ static int run_trunk_tc(dqn_net_s* h, int npass, const void* const x[2], const i
     }
     if (npass == 1) a.p[1] = a.p[0];
     StageScope sc(h, DQN_STAGE_FWD_CONV1 + l, st);
+    if (h->arch == DQN_ARCH_NATURE) {
+      // Nature variant (VALID convs, no pooling, fc 512): conv1 and fc through the ring kernel, conv2/conv3 resident
+      switch (l) {
+        case 0: launch_fwd_tc<N1, uint8_t, 32, 4, 4>(a, npass, h->num_sms, st); break;
+        case 1: launch_fwd_res<N2, 64, 2, 2>(a, npass, st); break;
+        case 2: launch_fwd_res<N3, 64, 3, 2>(a, npass, st); break;
+        case 3:
+          if (B <= 128) launch_fwd_tc<NF, __nv_bfloat16, 64, 4, 2>(a, npass, h->num_sms, st);
+          else launch_fwd_tc<NF, __nv_bfloat16, 256, 4, 2>(a, npass, h->num_sms, st);
+          break;
+      }
+      continue;
+    }
     switch (l) {
       case 0:
         if (h->no_resident) launch_fwd_tc<C1, uint8_t, 32, 4, 4>(a, npass, h->num_sms, st);
@@ -1398,7 +1412,17 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       DQN_CUDA(cudaStreamWaitEvent(sd, h->ev_fork[i], 0));
       return 0;
     };
-    if (h->precision == 1) {
+    if (h->precision == 1 && nat) {
+      launch_wgrad_tc<NF, __nv_bfloat16, 128>(h, 3, h->act_bf[0][2], k, sh, &nsplit[3]);
+      DQN_CUDA(cudaEventRecord(h->ev_head, sh));
+      launch_dgrad_tc<NF, 64>(h, 3, k, st);
+      if (fork_after_dgrad(1)) return DQN_ERR_CUDA;
+      launch_wgrad_tc<N3, __nv_bfloat16, 64>(h, 2, h->act_bf[0][1], k, sd, &nsplit[2]); launch_dgrad_tc<N3, 64>(h, 2, k, st);
+      if (early_exchange()) return DQN_ERR_CUDA;
+      if (fork_after_dgrad(2)) return DQN_ERR_CUDA;
+      launch_wgrad_tc<N2, __nv_bfloat16, 64>(h, 1, h->act_bf[0][0], k, sd, &nsplit[1]); launch_dgrad_tc<N2, 32>(h, 1, k, st);
+      launch_wgrad_tc<N1, uint8_t, 32>(h, 0, d_states, k, st, &nsplit[0]);
+    } else if (h->precision == 1) {
       launch_wgrad_tc<F4, __nv_bfloat16, 128>(h, 3, h->act_bf[0][2], k, sh, &nsplit[3]);
       DQN_CUDA(cudaEventRecord(h->ev_head, sh));
       if (!fused) {                  // the fused kernel already produced the fc data gradient
@@ -1632,8 +1656,8 @@ extern "C" int dqn_net_set_precision(dqn_net_t h, int32_t precision) {
   DQN_REQUIRE(h, DQN_ERR_INVALID, "set_precision: NULL handle");
   DQN_REQUIRE(precision == 0 || precision == 1, DQN_ERR_INVALID, "precision must be 0 (fp32) or 1 (bf16 tensor cores)");
   if (precision == 1) {
-    DQN_REQUIRE(h->arch == DQN_ARCH_CNN && h->in_dtype == DQN_U8, DQN_ERR_UNSUPPORTED,
-                "the bf16 tensor-core path covers the reference conv net (DQN_ARCH_CNN) fed uint8 frames");
+    DQN_REQUIRE((h->arch == DQN_ARCH_CNN || h->arch == DQN_ARCH_NATURE) && h->in_dtype == DQN_U8, DQN_ERR_UNSUPPORTED,
+                "the bf16 tensor-core path covers the conv nets (DQN_ARCH_CNN, DQN_ARCH_NATURE) fed uint8 frames");
     DeviceGuard g(h->device);
     if (!h->wt_bf[0]) {
       size_t wt = 0, wd = 0;

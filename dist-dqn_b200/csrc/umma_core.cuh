@@ -1263,10 +1263,9 @@ __global__ void __launch_bounds__(TT) umma_dgrad_kernel(DgradArgsT a) {
     if (it < T) {
       const int slot = it & (RS - 1);
       int nq, t;
-      if constexpr (S2) {        // stage = one of the class's taps: ky = (1-cy) + 2a, kx = (1-cx) + 2b  (pad is 1)
-        static_assert(!S2 || (G::PADH == 1 && G::PADW == 1), "parity classes assume pad 1");
+      if constexpr (S2) {        // stage = one of the class's taps: ky = ((cy+pad)&1) + 2a, kx = ((cx+pad)&1) + 2b
         const int ta = it / (G::KS / 2), tb = it % (G::KS / 2);
-        t = ((1 - cy) + 2 * ta) * G::KS + (1 - cx) + 2 * tb;
+        t = (((cy + G::PADH) & 1) + 2 * ta) * G::KS + ((cx + G::PADW) & 1) + 2 * tb;
         nq = gc;
       } else {
         const int kc8 = it * 8 + gc;
