@@ -1196,7 +1196,8 @@ static int run_trunk_tc(dqn_net_s* h, int npass, const void* const x[2], const i
         else launch_fwd_res<C3, 64, 3, 2>(a, npass, st);
         break;
       case 3:          // few rows: narrow tiles spread the weight traffic over more SMs (a lone CTA is bound by its SM's L2 port)
-        if (B <= 256) launch_fwd_tc<F4, __nv_bfloat16, 64, 4, 4>(a, npass, h->num_sms, st);
+        if (B <= 64) launch_fwd_tc<F4, __nv_bfloat16, 32, 4, 4>(a, npass, h->num_sms, st);
+        else if (B <= 256) launch_fwd_tc<F4, __nv_bfloat16, 64, 4, 4>(a, npass, h->num_sms, st);
         else launch_fwd_tc<F4, __nv_bfloat16, 256, 4, 4>(a, npass, h->num_sms, st);
         break;
     }
@@ -1426,7 +1427,8 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       launch_wgrad_tc<F4, __nv_bfloat16, 128>(h, 3, h->act_bf[0][2], k, sh, &nsplit[3]);
       DQN_CUDA(cudaEventRecord(h->ev_head, sh));
       if (!fused) {                  // the fused kernel already produced the fc data gradient
-        if (k <= 256) launch_dgrad_tc<F4, 64>(h, 3, k, st);
+        if (k <= 64) launch_dgrad_tc<F4, 32>(h, 3, k, st);
+        else if (k <= 256) launch_dgrad_tc<F4, 64>(h, 3, k, st);
         else launch_dgrad_tc<F4, 256>(h, 3, k, st);
         if (fork_after_dgrad(1)) return DQN_ERR_CUDA;
       }
