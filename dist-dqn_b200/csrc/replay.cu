@@ -181,21 +181,24 @@ __global__ void __launch_bounds__(256)
 ingest_kernel(const uint8_t* __restrict__ meta_blk, const uint8_t* __restrict__ frames_blk, uint8_t* __restrict__ d_frames,
               TransitionRec* __restrict__ d_meta, int64_t* __restrict__ d_state, int64_t fcap, int64_t cap, int32_t pitch,
               const int32_t* __restrict__ host_idx, int32_t* __restrict__ d_idx, int32_t k) {
-  if (blockIdx.x == 0 && host_idx)
-    for (int i = threadIdx.x; i < k; i += blockDim.x) d_idx[i] = host_idx[i];
+  pdl_trigger();                                  // the gather may launch now; it waits for this grid's completion itself
+  // grid (ceil(pitch/16/256), kGraphIngest): block (x, j) moves 256 16-byte chunks of frame slot j.  Every PCIe read is
+  // issued before the header is examined (a stale frame slot is harmless to read), so a block pays one host round
+  // trip, not two.
+  const int j = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool first = blockIdx.x == 0 && blockIdx.y == 0;
+  uint4 v = make_uint4(0u, 0u, 0u, 0u), rec = make_uint4(0u, 0u, 0u, 0u);
+  int32_t myidx = 0;
+  if (i < pitch / 16) v = reinterpret_cast<const uint4*>(frames_blk + (size_t)j * pitch)[i];
+  if (first && (int)threadIdx.x < 16) rec = reinterpret_cast<const uint4*>(meta_blk + sizeof(IngestHdr))[threadIdx.x];   // 8 records
+  if (first && host_idx)
+    for (int q = threadIdx.x; q < k; q += blockDim.x) { myidx = host_idx[q]; d_idx[q] = myidx; }
   const IngestHdr hd = *reinterpret_cast<const IngestHdr*>(meta_blk);
-  const int j = blockIdx.x;
-  if (j < hd.nframes) {
-    const uint4* src = reinterpret_cast<const uint4*>(frames_blk + (size_t)j * pitch);
-    uint4* dst = reinterpret_cast<uint4*>(d_frames + ((hd.first_frame_pos + j) % fcap) * (int64_t)pitch);
-    for (int i = threadIdx.x; i < pitch / 16; i += blockDim.x) dst[i] = src[i];
-  }
-  if (j == 0 && (hd.nframes > 0 || hd.nrecs > 0)) {
-    const uint4* rs = reinterpret_cast<const uint4*>(meta_blk + sizeof(IngestHdr));
-    for (int i = threadIdx.x; i < hd.nrecs * 2; i += blockDim.x) {          // a record is two 16-byte halves
-      const int r = i >> 1;
-      reinterpret_cast<uint4*>(d_meta + (hd.first_rec + r) % cap)[i & 1] = rs[i];
-    }
+  if (j < hd.nframes && i < pitch / 16)
+    reinterpret_cast<uint4*>(d_frames + ((hd.first_frame_pos + j) % fcap) * (int64_t)pitch)[i] = v;
+  if (first && (hd.nframes > 0 || hd.nrecs > 0)) {
+    if ((int)threadIdx.x < hd.nrecs * 2)           // a record is two 16-byte halves
+      reinterpret_cast<uint4*>(d_meta + (hd.first_rec + (threadIdx.x >> 1)) % cap)[threadIdx.x & 1] = rec;
     if (threadIdx.x == 0) { d_state[0] = hd.head; d_state[1] = hd.size; }
   }
 }
@@ -506,8 +509,9 @@ extern "C" int dqn_replay_ingest_staged(dqn_replay_t h, int32_t stage, const int
   Stage& s = h->stage[stage];
   DQN_REQUIRE((pinned_idx == nullptr) == (d_idx == nullptr) && k >= 0, DQN_ERR_INVALID, "ingest_staged: index pointers");
   dqn::count_launch();
-  ingest_kernel<<<kGraphIngest, 256, 0, st>>>(s.ing, s.frames, h->d_frames, h->d_meta, h->d_state, h->fcap, h->cap, h->pitch,
-                                              pinned_idx, d_idx, k);
+  static_assert(kGraphIngest * 2 <= 16, "block (0,0) moves the records with its first 16 threads");
+  ingest_kernel<<<dim3((h->pitch / 16 + 255) / 256, kGraphIngest), 256, 0, st>>>(s.ing, s.frames, h->d_frames, h->d_meta, h->d_state,
+                                                                              h->fcap, h->cap, h->pitch, pinned_idx, d_idx, k);
   DQN_CUDA(cudaGetLastError());
   return 0;
 }
