@@ -213,7 +213,16 @@ __device__ __forceinline__ float seg_grad(const Seg& s, int i) {
 __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs a) {
   pdl_wait();
   const Seg s = a.seg[blockIdx.y];
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  // bf16 mode, weight part of a conv / fc tensor: the block owns a tile of 8 reduction rows x 32 output columns instead
+  // of 256 consecutive elements (K*N is a multiple of 256, N of 32), so that the refreshed [n][k] stage image is
+  // written as 16-byte chunks of 8 consecutive k (through shared memory) instead of 2-byte writes 128 bytes apart
+  const bool tiled = s.wt != nullptr && (int)(blockIdx.x * blockDim.x) < s.K * s.N;
+  __shared__ __nv_bfloat16 wtile[8][32 + 2];
+  if (tiled) {
+    const int ntn = s.N >> 5, kt = blockIdx.x / ntn, nt = blockIdx.x - kt * ntn;
+    i = (kt * 8 + (int)(threadIdx.x >> 5)) * s.N + nt * 32 + (int)(threadIdx.x & 31);
+  }
   __shared__ float lr_t_s;
   if (a.opt == DQN_OPT_ADAM) {
     if (threadIdx.x == 0) {
@@ -298,10 +307,17 @@ __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs a) {
     } break;
   }
   a.w[p] = w;
-  if (s.wt && i < s.K * s.N) {
+  if (tiled) {
     const int k = i / s.N, n = i - k * s.N;
     const __nv_bfloat16 v = __float2bfloat16_rn(w);
-    s.wt[umma::img_index(n, k, s.N)] = v;
+    wtile[threadIdx.x >> 5][threadIdx.x & 31] = v;
+    __syncthreads();
+    if (threadIdx.x < 32) {              // column n of the tile: its 8 consecutive k are one 16-byte chunk of the image
+      __align__(16) __nv_bfloat16 c8[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) c8[e] = wtile[e][threadIdx.x];
+      *reinterpret_cast<uint4*>(s.wt + umma::img_index(n, k, s.N)) = *reinterpret_cast<const uint4*>(c8);   // thread < 32: k = 8*kt
+    }
     if (s.wd) {
       const int t = k / s.CIN, c = k - t * s.CIN;
       s.wd[umma::img_index(c, t * s.N + n, s.CIN)] = v;
