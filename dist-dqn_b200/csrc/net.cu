@@ -1043,11 +1043,16 @@ static void launch_fwd_res(const umma::FwdArgsT& a, int npass, cudaStream_t st) 
   launch_pdl(umma::umma_fwd_res_kernel<G, NTILE, NK, NA>, grid, dim3(umma::TT), smem, st, 1, a);
 }
 template <class G, int NTILE>
-static void launch_fwd_res_u8(const umma::FwdArgsT& a, int npass, cudaStream_t st) {
+static void launch_fwd_res_u8(umma::FwdArgsT a, int npass, int num_sms, cudaStream_t st) {
   constexpr size_t smem = umma::fwd_res_u8_smem_bytes<G, NTILE>();
   static bool once = (set_smem(umma::umma_fwd_res_u8_kernel<G, NTILE>, smem), true);
   (void)once;
-  dim3 grid((unsigned)((a.B * G::ROWS + umma::TM - 1) / umma::TM), G::COUT / NTILE, npass);
+  // one wave of CTAs (two fit per SM), each walking over consecutive tiles of the combined (pass, tile) space
+  const int total = ((a.B * G::ROWS + umma::TM - 1) / umma::TM) * npass;
+  const int per = (total + 2 * num_sms - 1) / (2 * num_sms);
+  a.npass = npass;
+  a.tiles_per_cta = per;
+  dim3 grid((unsigned)((total + per - 1) / per), 1, 1);
   launch_pdl(umma::umma_fwd_res_u8_kernel<G, NTILE>, grid, dim3(umma::TT), smem, st, 1, a);
 }
 // Ring depth: a grid of at most one CTA per SM is latency-bound (deep ring, loads far ahead of the MMAs); a grid of
@@ -1173,6 +1178,8 @@ static int run_trunk_tc(dqn_net_s* h, int npass, const void* const x[2], const i
   for (int l = 0; l < nlayers; ++l) {
     umma::FwdArgsT a;
     a.B = B;
+    a.npass = npass;
+    a.tiles_per_cta = 1;
     for (int p = 0; p < npass; ++p) {
       const int id = pass_id[p];
       const float* params = id == 0 ? h->online : h->target;
@@ -1201,7 +1208,7 @@ static int run_trunk_tc(dqn_net_s* h, int npass, const void* const x[2], const i
     switch (l) {
       case 0:
         if (h->no_resident) launch_fwd_tc<C1, uint8_t, 32, 4, 4>(a, npass, h->num_sms, st);
-        else launch_fwd_res_u8<C1, 32>(a, npass, st);
+        else launch_fwd_res_u8<C1, 32>(a, npass, h->num_sms, st);
         break;
       case 1:
         if (h->no_resident) launch_fwd_tc<C2, __nv_bfloat16, 64, 8, 4>(a, npass, h->num_sms, st);

@@ -302,6 +302,8 @@ struct FwdPassT {
 struct FwdArgsT {
   FwdPassT p[2];
   int B;
+  int npass;            // umma_fwd_res_u8_kernel only: passes folded into blockIdx.x ...
+  int tiles_per_cta;    // ... and consecutive tiles per CTA
 };
 
 // Forward epilogue: TMEM -> bias + ReLU (+ 2x2 max-pool and arg-max) -> bf16 NHWC (+ optional fp32 copy).
@@ -655,15 +657,33 @@ struct FwdResU8 {
   static constexpr int T = G::K / TK;                                                 // 4 k-blocks
   static_assert(G::CIN == 4 && ROW_BYTES % 16 == 0 && TK == 2 * G::KS * G::CIN, "one k-block = two filter rows of 8 pixels x 4 frames");
 };
+// input-row band of the 128-row tile starting at row m0 (see umma_fwd_res_u8_kernel): global row indices b*IH + iy, inclusive
+template <class G>
+__device__ __forceinline__ void conv1_band(int m0, int B, int& grow_lo, int& grow_hi, int& w_first, int& w_last) {
+  constexpr int WPS = G::PH * G::PW;
+  w_first = m0 >> 2;
+  w_last = (m0 + TM - 1) >> 2;
+  if (w_last > B * WPS - 1) w_last = B * WPS - 1;
+  const int bf = w_first / WPS, bl = w_last / WPS;
+  const int pyf = (w_first - bf * WPS) / G::PW, pyl = (w_last - bl * WPS) / G::PW;
+  int iy_lo = 2 * pyf * G::ST - G::PADH;
+  if (iy_lo < 0) iy_lo = 0;
+  int iy_hi = (2 * pyl + 1) * G::ST - G::PADH + G::KS - 1;
+  if (iy_hi > G::IH - 1) iy_hi = G::IH - 1;
+  grow_lo = bf * G::IH + iy_lo;
+  grow_hi = bl * G::IH + iy_hi;
+}
+
 template <class G, int NTILE>
 __host__ __device__ constexpr uint32_t fwd_res_u8_smem_bytes() {
   return SMEM_SLACK + FwdResU8<G>::PATCH_BYTES + FwdResU8<G>::T * (A_STAGE_BYTES + (uint32_t)NTILE * 128u);
 }
 
 template <class G, int NTILE>
-__global__ void __launch_bounds__(TT) umma_fwd_res_u8_kernel(FwdArgsT a) {
+__global__ void __launch_bounds__(TT, 2) umma_fwd_res_u8_kernel(FwdArgsT a) {      // 2 CTAs/SM: at most 64 registers
   using R = FwdResU8<G>;
   constexpr int T = R::T;
+  static_assert(G::COUT == NTILE, "one tile spans all output channels");
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align_smem(smem_raw);
   constexpr uint32_t B_STAGE = NTILE * 128;
@@ -674,10 +694,13 @@ __global__ void __launch_bounds__(TT) umma_fwd_res_u8_kernel(FwdArgsT a) {
   __shared__ uint64_t afull, wfull, done, patchbar;
   __shared__ uint32_t tmem_slot;
   __shared__ float bias_sm[NTILE];
-  const FwdPassT P = a.p[blockIdx.z];
-  const uint8_t* __restrict__ x = static_cast<const uint8_t*>(P.x);
   const int tid = threadIdx.x, lane = tid & 31;
-  const int m0 = blockIdx.x * TM, n0 = blockIdx.y * NTILE;
+  // A CTA walks over `tiles_per_cta` consecutive tiles of the combined (pass, 128-row tile) space: set-up, TMEM
+  // allocation and (per pass) the weights are paid once, and the next tile's band is fetched under the epilogue.
+  const int mtiles = (a.B * G::ROWS + TM - 1) / TM;
+  const int total = mtiles * a.npass;
+  const int g_begin = blockIdx.x * a.tiles_per_cta;
+  const int g_end = min(total, g_begin + a.tiles_per_cta);
   if (tid == 0) {
     mbar_init(&afull, TT / 32);
     mbar_init(&wfull, 1);
@@ -686,96 +709,122 @@ __global__ void __launch_bounds__(TT) umma_fwd_res_u8_kernel(FwdArgsT a) {
   }
   const uint32_t tmem = setup(bars, &tmem_slot, tmem_cols(NTILE));
   const uint32_t sbase = smem_u32(smem);
-  if (tid == 0) {                     // all weights, before the PDL wait
-    const __nv_bfloat16* wimg = P.wt + (size_t)n0 * 64;
+  // kernel parameters are selected field by field (indexing a.p[] with a run-time value would copy it to local memory)
+  auto pass_of = [&](int pass) {
+    FwdPassT P;
+    P.x = pass ? a.p[1].x : a.p[0].x;
+    P.wt = pass ? a.p[1].wt : a.p[0].wt;
+    P.bias = pass ? a.p[1].bias : a.p[0].bias;
+    P.out = pass ? a.p[1].out : a.p[0].out;
+    P.out_f32 = nullptr;
+    P.arg = pass ? a.p[1].arg : a.p[0].arg;
+    return P;
+  };
+  auto load_weights = [&](int pass) {    // thread 0: all k-blocks of the pass's weight image
+    const __nv_bfloat16* wimg = pass ? a.p[1].wt : a.p[0].wt;
     mbar_expect_tx(&wfull, T * B_STAGE);
 #pragma unroll
     for (int kb = 0; kb < T; ++kb) bulk_g2s(sbase + OFF_B + kb * B_STAGE, wimg + (size_t)kb * (G::COUT * 64), B_STAGE, &wfull);
-  }
-  for (int j = tid; j < NTILE; j += TT) bias_sm[j] = __ldg(P.bias + n0 + j);
-  // the band of input rows this tile reads: from the first pool row of its first window to the last pool row of its
-  // last window (windows run sample-major, then row-major), clipped to the image
-  constexpr int WPS = G::PH * G::PW;                                   // pool windows per sample
-  const int w_first = m0 >> 2;
-  int w_last = (m0 + TM - 1) >> 2;
-  if (w_last > a.B * WPS - 1) w_last = a.B * WPS - 1;
-  const int bf = w_first / WPS, bl = w_last / WPS;
-  const int pyf = (w_first - bf * WPS) / G::PW, pyl = (w_last - bl * WPS) / G::PW;
-  int iy_lo = 2 * pyf * G::ST - G::PADH;
-  if (iy_lo < 0) iy_lo = 0;
-  int iy_hi = (2 * pyl + 1) * G::ST - G::PADH + G::KS - 1;
-  if (iy_hi > G::IH - 1) iy_hi = G::IH - 1;
-  const int grow_lo = bf * G::IH + iy_lo, grow_hi = bl * G::IH + iy_hi;      // global input-row indices (inclusive)
-  const int gc = tid & 7;
+  };
+  // per-tile state, prepared one tile ahead (under the previous tile's MMAs, or before the PDL wait for the first tile)
+  int glo = 0, ghi = 0, m0 = 0, pass = 0;
   int poff[2], aiy0[2], aix0[2];
   bool avalid[2];
-  uint32_t adst[2];
-#pragma unroll
-  for (int q = 0; q < 2; ++q) {
-    const int rr = (tid >> 3) + 64 * q;
-    const Row r = decode_row<G>(m0 + rr, a.B);
-    aiy0[q] = r.oy * G::ST - G::PADH;
-    aix0[q] = r.ox * G::ST - G::PADW;
-    avalid[q] = r.valid;
-    poff[q] = ((r.b * G::IH + aiy0[q] - grow_lo) * G::IW + aix0[q]) * G::CIN;        // byte offset in the band (may be < 0 at the border)
-    adst[q] = OFF_A + sw128_off(rr, gc);
-  }
-  pdl_wait_then_trigger();
-  if (tid == 0) {
-    const int nrows = grow_hi - grow_lo + 1;
-    if (nrows > R::PATCH_ROWS) __trap();
-    mbar_expect_tx(&patchbar, (uint32_t)nrows * R::ROW_BYTES);
-    bulk_g2s(sbase + OFF_RAW, x + (size_t)grow_lo * R::ROW_BYTES, (uint32_t)nrows * R::ROW_BYTES, &patchbar);
-  }
-  constexpr uint32_t idesc = make_idesc(TM, NTILE, false, false);
-  mbar_wait(&patchbar, 0);
-  // widen the band: 8 bytes -> 8 bf16 per step
-  {
-    const int nchunks = (grow_hi - grow_lo + 1) * (int)(R::ROW_BYTES / 8);
-    for (int c = tid; c < nchunks; c += TT) {
-      const uint2 u = *reinterpret_cast<const uint2*>(smem + OFF_RAW + c * 8);
-      *reinterpret_cast<uint4*>(smem + c * 16) = widen_u8x8(u);
-    }
-  }
-  __syncthreads();
-  // chunk gc of k-block kb: filter row ky = 2*kb + gc/4, pixels kx = 2*(gc%4), +1
-  const int kxo = 2 * (gc & 3), kyo = gc >> 2;
-#pragma unroll
-  for (int kb = 0; kb < T; ++kb) {
-    const int ky = 2 * kb + kyo;
-    const int delta = (ky * G::IW + kxo) * G::CIN;
+  const int gc = tid & 7;
+  auto prep = [&](int g) {
+    pass = g / mtiles;
+    m0 = (g - pass * mtiles) * TM;
+    int wf, wl;
+    conv1_band<G>(m0, a.B, glo, ghi, wf, wl);
 #pragma unroll
     for (int q = 0; q < 2; ++q) {
-      const bool ok = avalid[q] && (unsigned)(aiy0[q] + ky) < (unsigned)G::IH && (unsigned)(aix0[q] + kxo) < (unsigned)G::IW;
-      uint4 v = make_uint4(0u, 0u, 0u, 0u);
-      if (ok) v = *reinterpret_cast<const uint4*>(smem + 2 * (poff[q] + delta));
-      *reinterpret_cast<uint4*>(smem + kb * A_STAGE_BYTES + adst[q]) = v;
+      const Row r = decode_row<G>(m0 + (tid >> 3) + 64 * q, a.B);
+      aiy0[q] = r.oy * G::ST - G::PADH;
+      aix0[q] = r.ox * G::ST - G::PADW;
+      avalid[q] = r.valid;
+      poff[q] = ((r.b * G::IH + aiy0[q] - glo) * G::IW + aix0[q]) * G::CIN;      // byte offset in the band (may be < 0 at the border)
     }
-  }
-  fence_async_proxy();
-  __syncwarp();
-  if (lane == 0) mbar_arrive(&afull);
-  if (warp_uniform_idx() == 0) {
-    mbar_wait(&afull, 0);
-    mbar_wait(&wfull, 0);
-    tc_fence_after();
-    if (elect_one()) {
-      const uint64_t ad0 = make_desc_sw128(sbase + OFF_A), bd0 = make_desc_sw128(sbase + OFF_B);
+  };
+  auto load_band = [&]() {               // thread 0: the input-row band of the prepared tile
+    const int nrows = ghi - glo + 1;
+    if (nrows > R::PATCH_ROWS) __trap();
+    mbar_expect_tx(&patchbar, (uint32_t)nrows * R::ROW_BYTES);
+    bulk_g2s(sbase + OFF_RAW, static_cast<const uint8_t*>(pass ? a.p[1].x : a.p[0].x) + (size_t)glo * R::ROW_BYTES,
+             (uint32_t)nrows * R::ROW_BYTES, &patchbar);
+  };
+  int cur_pass = g_begin < g_end ? g_begin / mtiles : 0;
+  int wphase = 0;
+  if (tid == 0 && g_begin < g_end) load_weights(cur_pass);           // before the PDL wait: weights do not depend on the predecessor
+  for (int j = tid; j < NTILE; j += TT) bias_sm[j] = __ldg((cur_pass ? a.p[1].bias : a.p[0].bias) + j);
+  if (g_begin < g_end) prep(g_begin);
+  const uint32_t adst[2] = {OFF_A + sw128_off(tid >> 3, gc), OFF_A + sw128_off((tid >> 3) + 64, gc)};
+  pdl_wait_then_trigger();
+  if (tid == 0 && g_begin < g_end) load_band();
+  constexpr uint32_t idesc = make_idesc(TM, NTILE, false, false);
+  const int kxo = 2 * (gc & 3), kyo = gc >> 2;                         // chunk gc of k-block kb: filter row 2*kb + gc/4, pixels 2*(gc%4), +1
+  const int wu = warp_uniform_idx();
+#pragma unroll 1
+  for (int g = g_begin; g < g_end; ++g) {
+    const int t = g - g_begin;
+    mbar_wait(&patchbar, t & 1);
+    {   // widen the band: 8 bytes -> 8 bf16 per step (all readers of the previous tile's band are past its MMAs)
+      const int nchunks = (ghi - glo + 1) * (int)(R::ROW_BYTES / 8);
+      for (int c = tid; c < nchunks; c += TT)
+        *reinterpret_cast<uint4*>(smem + c * 16) = widen_u8x8(*reinterpret_cast<const uint2*>(smem + OFF_RAW + c * 8));
+    }
+    __syncthreads();
 #pragma unroll
-      for (int kb = 0; kb < T; ++kb) {
+    for (int kb = 0; kb < T; ++kb) {
+      const int ky = 2 * kb + kyo;
+      const int delta = (ky * G::IW + kxo) * G::CIN;
 #pragma unroll
-        for (int j = 0; j < TK / 16; ++j)
-          mma_bf16(tmem, desc_advance(ad0, kb * A_STAGE_BYTES + j * 32), desc_advance(bd0, kb * B_STAGE + j * 32), idesc,
-                   (kb | j) ? 1u : 0u);
+      for (int q = 0; q < 2; ++q) {
+        const bool ok = avalid[q] && (unsigned)(aiy0[q] + ky) < (unsigned)G::IH && (unsigned)(aix0[q] + kxo) < (unsigned)G::IW;
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (ok) v = *reinterpret_cast<const uint4*>(smem + 2 * (poff[q] + delta));
+        *reinterpret_cast<uint4*>(smem + kb * A_STAGE_BYTES + adst[q]) = v;
       }
-      mma_commit(&done);
+    }
+    fence_async_proxy();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&afull);
+    if (wu == 0) {
+      mbar_wait(&afull, t & 1);           // every warp has built its part (and finished the previous tile's epilogue)
+      mbar_wait(&wfull, wphase);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint64_t ad0 = make_desc_sw128(sbase + OFF_A), bd0 = make_desc_sw128(sbase + OFF_B);
+#pragma unroll
+        for (int kb = 0; kb < T; ++kb) {
+#pragma unroll
+          for (int j = 0; j < TK / 16; ++j)
+            mma_bf16(tmem, desc_advance(ad0, kb * A_STAGE_BYTES + j * 32), desc_advance(bd0, kb * B_STAGE + j * 32), idesc,
+                     (kb | j) ? 1u : 0u);
+        }
+        mma_commit(&done);
+      }
+      __syncwarp();
+    }
+    if (g + 1 == g_end) pdl_trigger();
+    // this tile's output coordinates; then prepare the next tile while the MMAs run
+    const int e_pass = pass, e_m0 = m0;
+    if (g + 1 < g_end) prep(g + 1);
+    mbar_wait(&done, t & 1);
+    tc_fence_after();
+    // operands are free again: fetch the next tile's band (and, at the online/target boundary, the other weights)
+    if (tid == 0 && g + 1 < g_end) {
+      load_band();
+      if (pass != e_pass) load_weights(pass);
+    }
+    fwd_epilogue<G, NTILE>(tmem, pass_of(e_pass), e_m0, 0, a.B, bias_sm);
+    tc_fence_before();
+    if (pass != e_pass) {                 // uniform over the CTA
+      wphase ^= 1;
+      __syncthreads();                    // everyone is done with the old bias
+      for (int j = tid; j < NTILE; j += TT) bias_sm[j] = __ldg((pass ? a.p[1].bias : a.p[0].bias) + j);
+      __syncthreads();
     }
   }
-  __syncwarp();
-  pdl_trigger();
-  mbar_wait(&done, 0);
-  tc_fence_after();
-  fwd_epilogue<G, NTILE>(tmem, P, m0, n0, a.B, bias_sm);
   teardown(tmem, tmem_cols(NTILE));
 }
 
@@ -978,23 +1027,6 @@ struct WgradResU8 {
   static constexpr uint32_t SMEM = SMEM_SLACK + OFF_ARG + 2 * round1k_c(ARG_BYTES);
   static_assert(G::K == 256 && G::COUT == 32 && G::POOL, "written for the reference conv1 (8x8x4 -> 32, pooled)");
 };
-
-// input-row band of the 128-row tile starting at row m0 (see umma_fwd_res_u8_kernel): global row indices b*IH + iy, inclusive
-template <class G>
-__device__ __forceinline__ void conv1_band(int m0, int B, int& grow_lo, int& grow_hi, int& w_first, int& w_last) {
-  constexpr int WPS = G::PH * G::PW;
-  w_first = m0 >> 2;
-  w_last = (m0 + TM - 1) >> 2;
-  if (w_last > B * WPS - 1) w_last = B * WPS - 1;
-  const int bf = w_first / WPS, bl = w_last / WPS;
-  const int pyf = (w_first - bf * WPS) / G::PW, pyl = (w_last - bl * WPS) / G::PW;
-  int iy_lo = 2 * pyf * G::ST - G::PADH;
-  if (iy_lo < 0) iy_lo = 0;
-  int iy_hi = (2 * pyl + 1) * G::ST - G::PADH + G::KS - 1;
-  if (iy_hi > G::IH - 1) iy_hi = G::IH - 1;
-  grow_lo = bf * G::IH + iy_lo;
-  grow_hi = bl * G::IH + iy_hi;
-}
 
 template <class G>
 __global__ void __launch_bounds__(TT) umma_wgrad_res_u8_kernel(WgradArgsT a) {
