@@ -204,10 +204,32 @@ __device__ __forceinline__ float ld_relaxed_sys(const float* p) {
   return v;
 }
 
+// Sum of the weight-gradient partials of element i in a fixed order (deterministic).  Up to ~150 partials (one per CTA
+// of the conv1 weight-gradient kernel) sit 33 KB apart: a plain loop is a chain of L2 round trips (measured 8.6 us for
+// 61 partials), so 16 loads are kept in flight and summed as a fixed tree.
 __device__ __forceinline__ float seg_grad(const Seg& s, int i) {
-  float gsum = 0.f;
-  for (int k = 0; k < s.nsplit; ++k) gsum += s.partial[(size_t)k * s.stride + i];
-  return gsum;
+  const float* p = s.partial + i;
+  const size_t st = (size_t)s.stride;
+  if (s.nsplit <= 2) return s.nsplit == 2 ? p[0] + p[st] : p[0];
+  float total = 0.f;
+  int k = 0;
+  for (; k + 16 <= s.nsplit; k += 16) {
+    const float* q = p + (size_t)k * st;
+    const float v0 = q[0], v1 = q[st], v2 = q[2 * st], v3 = q[3 * st], v4 = q[4 * st], v5 = q[5 * st], v6 = q[6 * st], v7 = q[7 * st];
+    const float v8 = q[8 * st], v9 = q[9 * st], v10 = q[10 * st], v11 = q[11 * st], v12 = q[12 * st], v13 = q[13 * st],
+                v14 = q[14 * st], v15 = q[15 * st];
+    total += (((v0 + v1) + (v2 + v3)) + ((v4 + v5) + (v6 + v7))) + (((v8 + v9) + (v10 + v11)) + ((v12 + v13) + (v14 + v15)));
+  }
+  if (k < s.nsplit) {                       // tail: up to 15 partials, still loaded together
+    const float* q = p + (size_t)k * st;
+    const int n = s.nsplit - k;
+    float v[16];
+#pragma unroll
+    for (int u = 0; u < 16; ++u) v[u] = u < n ? q[(size_t)u * st] : 0.f;
+    total += (((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]))) +
+             (((v[8] + v[9]) + (v[10] + v[11])) + ((v[12] + v[13]) + (v[14] + v[15])));
+  }
+  return total;
 }
 
 __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs a) {
@@ -348,9 +370,9 @@ __global__ void __launch_bounds__(256) reduce_grad_kernel(OptArgs a, float* __re
   if (pub.peer_flags) {
     // the last block to finish tells every rank (system-scope release) that this rank's gradient is complete
     __shared__ bool last;
-    __threadfence();
-    __syncthreads();
+    __syncthreads();                      // the block's stores happen-before thread 0's fence (one fence per block, not 256)
     if (threadIdx.x == 0) {
+      __threadfence();
       const unsigned int total = gridDim.x * gridDim.y;
       last = atomicAdd(pub.done_counter, 1u) == total - 1;
     }
@@ -358,8 +380,8 @@ __global__ void __launch_bounds__(256) reduce_grad_kernel(OptArgs a, float* __re
     if (last) {
       if (threadIdx.x == 0) *pub.done_counter = 0;
       if ((int)threadIdx.x < pub.world) {
-        __threadfence_system();
-        const unsigned long long v = (unsigned long long)*a.step;
+        __threadfence();                  // acquire side of the counter: every block's stores are visible here
+        const unsigned long long v = (unsigned long long)*a.step;   // the release store below is the system-scope fence
         asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(pub.peer_flags[threadIdx.x] + 8 * pub.flag_slot + pub.rank),
                      "l"(v)
                      : "memory");
