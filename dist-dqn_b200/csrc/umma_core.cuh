@@ -3,25 +3,30 @@
 // Same math and the same fused epilogues as gemm_core.cuh (reference: src/network.py:395-424 and the
 // TF gradients of those ops); operands are bf16 (uint8 frames are exact in bf16), accumulation fp32.
 //
-// How a tile is computed
-//   * 512 threads gather the operands (im2col of NHWC activations, transposed weights, or the pool-routed
-//     output gradient) as 16-byte chunks of 8 bf16.  Lanes run along the contiguous direction of global memory
-//     (8 lanes = one 128-byte run), so a warp touches a handful of lines instead of 32.
-//   * operands that need no arithmetic go straight into the UMMA SWIZZLE_128B K-major layout
-//     (row i at (i/8)*1024 + (i%8)*128, 16-byte chunk c at position c ^ (i%8)): forward A/B, dgrad B, fc dgrad A.
-//   * operands that need arithmetic (uint8 frames -> bf16, pool routing of gradients) or a transpose (wgrad, whose
-//     operands are MN-major) land in a padded raw ring and are rewritten shared->shared into the NO-SWIZZLE
-//     canonical layout (8x16-byte core matrices; K-major chunk (i,r/8) at (i/8)*1024 + (r/8)*128 + (i%8)*16,
-//     MN-major chunk (i/8, r) at (i/8)*1024 + (r/8)*128 + (r%8)*16).
-//   * the gather is asynchronous: every thread issues cp.async (16- or 8-byte, zero-filled outside the image)
-//     for stages i+1 and i+2 while stage i is consumed, into a 4-slot ring.  bf16 operands land directly in
-//     their canonical position; uint8 frames and pool-routed gradients land in a raw ring and are converted /
-//     masked shared->shared by the thread that fetched them, just before the MMA.
-//   * one thread issues 4 tcgen05.mma (M=128, N=tile width, K=16) per stage and commits them to an
-//     mbarrier; slots are recycled when the MMAs of stage i-2 have completed.
-//   * 4 warps read the accumulator with tcgen05.ld (warp w owns TMEM lanes 32w..32w+31, lane = tile row)
-//     and run the epilogue: bias + ReLU + 2x2 max-pool across 4 neighbouring lanes (forward), fp32 partial
-//     sums (wgrad), bf16 gradient (dgrad).
+// Two kernel families (DESIGN.md section 4 has the measurements behind the choices):
+//
+// RESIDENT-INPUT kernels (umma_fwd_res_kernel, umma_fwd_res_u8_kernel, umma_dgrad_res_kernel,
+// umma_wgrad_res_u8_kernel) -- the conv layers of the training step:
+//   * the tile's input (a contiguous NHWC block of a few samples, or a band of <= 40 uint8 frame rows) is fetched once
+//     with a bulk async copy (cp.async.bulk, completion counted on an mbarrier); all weight stages are fetched the same
+//     way, before the PDL wait;
+//   * operand tiles are built shared->shared (16-byte copies into the SWIZZLE_128B K-major layout: row i at
+//     (i/8)*1024 + (i%8)*128, chunk c at position c ^ (i%8); uint8 frames are widened to bf16 once per tile; pooled
+//     gradients are routed to their arg-max position on the way) in big stages of several 64-deep k-blocks;
+//   * one elected lane of warp 0 issues the stage's tcgen05.mma (M=128, N=tile width, K=16) back to back and commits
+//     them to an mbarrier; the conv1 kernels walk over consecutive tiles per CTA.
+// RING kernels (umma_fwd_kernel, umma_wgrad_kernel, umma_dgrad_kernel) -- fc layers, conv2/conv3 weight gradients, the
+// Nature variant's conv1, and everything when DQN_NO_RESIDENT=1:
+//   * 512 threads gather the operands (im2col of NHWC activations or the pool-routed output gradient) as 16-byte
+//     chunks with cp.async into an N-slot ring several stages ahead; lanes run along the contiguous direction of global
+//     memory.  Operands that need no arithmetic land directly in the swizzled layout; uint8 frames, pool-routed
+//     gradients and the MN-major wgrad operands land in a padded raw ring and are rewritten shared->shared (no-swizzle
+//     canonical layout: K-major chunk (i,r/8) at (i/8)*1024 + (r/8)*128 + (i%8)*16, MN-major chunk (i/8, r) at
+//     (i/8)*1024 + (r/8)*128 + (r%8)*16).
+// Both: weights live in global memory as pre-swizzled stage images (img_index) so that a stage's weight tile is one
+// bulk copy; accumulators live in TMEM; warp w reads TMEM lanes 32*(w%4).. with tcgen05.ld (lane = tile row) and runs
+// the epilogue: bias + ReLU + 2x2 max-pool across 4 neighbouring lanes (forward), fp32 partial sums (wgrad), ReLU-gated
+// bf16 gradient (dgrad).
 #pragma once
 #include <cuda_bf16.h>
 #include <cstdint>

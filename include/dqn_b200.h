@@ -175,7 +175,8 @@ int dqn_net_set_global_step(dqn_net_t h, int64_t step);
 /* Arithmetic of the conv / fully-connected GEMMs (north_star's two modes; no reference counterpart, TF ran fp32):
  * 0 = fp32 on CUDA cores, the parity mode (<= 1e-4 vs the oracle);
  * 1 = bf16 operands on the tcgen05 tensor cores with fp32 accumulation, fp32 master weights, fp32 optimizer
- *     (<= 2e-2 vs the oracle).  DQN_ARCH_CNN with uint8 input only.  Allocates its bf16 buffers on first use. */
+ *     (<= 2e-2 vs the oracle).  DQN_ARCH_CNN and DQN_ARCH_NATURE with uint8 input.  Allocates its bf16 buffers on
+ *     first use. */
 int dqn_net_set_precision(dqn_net_t h, int32_t precision);
 
 /* DQNAgent._predict_q_values (dqn_agent.py:176-189): forward of n states through the online
