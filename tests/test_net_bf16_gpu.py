@@ -154,3 +154,14 @@ def test_bf16_three_rmsprop_updates():
         assert rel_err(g, e) < 1.5 * TOL, (i, rel_err(g, e))
         assert rel_err(g, x) < 5e-2, (i, rel_err(g, x))
     assert net.get_global_step() == 3
+
+
+@pytest.mark.parametrize("env", ["DQN_NO_RESIDENT", "DQN_FUSED_FC"])
+def test_bf16_alternative_kernel_paths(env, monkeypatch):
+    """The env-gated variants stay correct: DQN_NO_RESIDENT=1 runs every conv layer through the ring kernels (im2col
+    gathers from L2), DQN_FUSED_FC=1 runs fc forward + TD head + fc data gradient as one launch.  The switch is read
+    when the network handle is created."""
+    monkeypatch.setenv(env, "1")
+    test_bf16_loss_and_gradients(6, 70)
+    test_bf16_forward(4, 37)
+
