@@ -759,12 +759,17 @@ __global__ void __launch_bounds__(TT, 2) umma_fwd_res_u8_kernel(FwdArgsT a) {   
   };
   int cur_pass = g_begin < g_end ? g_begin / mtiles : 0;
   int wphase = 0;
-  if (tid == 0 && g_begin < g_end) load_weights(cur_pass);           // before the PDL wait: weights do not depend on the predecessor
-  for (int j = tid; j < NTILE; j += TT) bias_sm[j] = __ldg((cur_pass ? a.p[1].bias : a.p[0].bias) + j);
   if (g_begin < g_end) prep(g_begin);
   const uint32_t adst[2] = {OFF_A + sw128_off(tid >> 3, gc), OFF_A + sw128_off((tid >> 3) + 64, gc)};
   pdl_wait_then_trigger();
-  if (tid == 0 && g_begin < g_end) load_band();
+  // conv1 can be the first kernel after the previous update's optimizer (no gather in between when the caller passes
+  // stacks directly), so unlike the deeper layers it reads weights and bias only after the wait; they arrive together
+  // with the band
+  if (tid == 0 && g_begin < g_end) {
+    load_weights(cur_pass);
+    load_band();
+  }
+  for (int j = tid; j < NTILE; j += TT) bias_sm[j] = __ldg((cur_pass ? a.p[1].bias : a.p[0].bias) + j);
   constexpr uint32_t idesc = make_idesc(TM, NTILE, false, false);
   const int kxo = 2 * (gc & 3), kyo = gc >> 2;                         // chunk gc of k-block kb: filter row 2*kb + gc/4, pixels 2*(gc%4), +1
   const int wu = warp_uniform_idx();
