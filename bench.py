@@ -585,7 +585,7 @@ def run_e2e(args, cfg, net, rm, world, dev, DQNAgent, FrameBuffer, dist):
         for _ in range(cfg.update_freq):
             fb.append(pool[fi % 256]); fi += 1
             nxt = fb.get_state()
-            rm.add(state, fi % A_PONG, float(fi % 3 - 1), nxt, False)
+            rm.add(state, fi % A_PONG, float(fi % 3 - 1), nxt, False, newest=fb.frames[-1])     # as DQNAgent._record does
             state = nxt
         agent._train_minibatch(batch)          # summary_freq=1 -> the loss of every update is read back to the host
         return agent.last_loss                 # (asynchronously: it is picked up while the next update is prepared)

@@ -85,6 +85,10 @@ class DQNAgent(object):
         self.async_summary = bool(getattr(config, 'async_summary', True))
         self._pending = None
         self._stage_evt = [None, None, None]
+        # our ReplayMemory takes the newest frame as a contiguous array (saves a strided copy per env step); any other
+        # object with the reference's 5-argument add() keeps working
+        self._pass_newest = (config.frames_per_state > 1 and getattr(replay_memory, '_trusted', False)
+                             and type(replay_memory).__name__ == 'ReplayMemory' and hasattr(replay_memory, 'seal'))
 
         self._prefill_replay_memory(config.replay_start_size)     # dqn_agent.py:47
         self._update_target_network()                             # dqn_agent.py:50 (step 0 always syncs)
@@ -125,7 +129,10 @@ class DQNAgent(object):
     def _record(self, state, action, reward, observation, done):
         self.frame_buffer.append(observation)
         next_state = self.frame_buffer.get_state()
-        self.replay_memory.add(state, action, reward, next_state, done)
+        if self._pass_newest:
+            self.replay_memory.add(state, action, reward, next_state, done, newest=self.frame_buffer.frames[-1])
+        else:
+            self.replay_memory.add(state, action, reward, next_state, done)
         return next_state
 
     # ------------------------------------------------------------------ the hot path (dqn_agent.py:108-143)

@@ -103,13 +103,15 @@ class ReplayMemory(object):
         self._frames_total = pos.value + frames.shape[0]
         return pos.value
 
-    def add(self, state, action, reward, observation, terminal):
-        """replay_memory.py:22-23.  ``observation`` is the next state."""
+    def add(self, state, action, reward, observation, terminal, newest=None):
+        """replay_memory.py:22-23.  ``observation`` is the next state.  ``newest`` (optional extension, trusted mode
+        only): the newest frame of ``observation`` as its own contiguous array -- what ``FrameBuffer.frames[-1]`` holds --
+        which saves the strided extraction of ``observation[..., -1]``."""
         if (self._trusted and state is self._last_next and self._h is not None
                 and self._last_next_pos == self._frames_total - 1):
             # fast lane (the agent loop, dqn_agent.py:96-100): one new frame, one C call
             if self._scratch is not None:
-                np.copyto(self._scratch, observation[..., -1])
+                np.copyto(self._scratch, observation[..., -1] if newest is None else newest)
                 ptr = self._scratch_ptr                      # cached: ndarray.ctypes is a slow attribute
             else:
                 ptr = np.ascontiguousarray(observation).ctypes.data

@@ -122,9 +122,11 @@ def test_graph_embedded_ingest_keeps_the_ring_identical_to_the_reference_deque()
     mirror = collections.deque(maxlen=cfg.replay_memory_capacity)
     real_add = rm.add
 
-    def add(state, action, reward, observation, terminal):
+    def add(state, action, reward, observation, terminal, **kw):
         mirror.append((np.array(state, copy=True), int(action), float(reward), np.array(observation, copy=True), bool(terminal)))
-        real_add(state, action, reward, observation, terminal)
+        if 'newest' in kw:                                            # the agent's shortcut must be the stack's last frame
+            assert np.array_equal(kw['newest'], observation[..., -1])
+        real_add(state, action, reward, observation, terminal, **kw)
 
     rm.add = add
     agent = DQNAgent(env, net, Session(), rm, cfg)
