@@ -63,6 +63,38 @@ def test_framebuffer_matches_reference(golden_dir):
     assert int(g["fb0_raises"][0]) == 1 and str(e.value) == str(g["fb0_msg"])
 
 
+def test_product_framebuffer_matches_reference_fixture(golden_dir):
+    """The shipped FrameBuffer (dist-dqn_b200/frame_buffer.py, pure host code) against what the reference's own class
+    returned (frame_buffer.py:27-57), plus the property the agent's shortcut relies on: ``frames[-1]`` is the newest
+    frame, i.e. the last channel of ``get_state()``."""
+    from frame_buffer import FrameBuffer
+    g = _load(golden_dir, "framebuffer.npz")
+    fr = g["frames"]
+    fb = FrameBuffer(4)
+    assert fb.get_state() is None
+    for i in range(6):
+        fb.append(fr[i])
+        st = fb.get_state()
+        assert np.array_equal(st, g["fb4_after%d" % i])
+        assert np.array_equal(fb.frames[-1], st[..., -1]) and fb.frames[-1] is not None
+    fb.clear()
+    assert fb.get_state() is None
+    fb.append(fr[6])
+    st = fb.get_state()
+    assert np.array_equal(st, g["fb4_restart"])
+    assert [st.shape[0], st.shape[1], st.shape[2], st.strides[0], st.strides[1], st.strides[2],
+            int(st.flags["C_CONTIGUOUS"])] == list(g["fb4_meta"])
+    fb1 = FrameBuffer(1)
+    fb1.append(fr[0]); fb1.append(fr[1])
+    assert np.array_equal(fb1.get_state(), g["fb1_state"])
+    fb2 = FrameBuffer(2, preprocessor=lambda f: (f // 2).astype(np.uint8))
+    fb2.append(fr[2]); fb2.append(fr[3]); fb2.append(fr[4])
+    assert np.array_equal(fb2.get_state(), g["fb2_pre_state"])
+    with pytest.raises(RuntimeError) as e:
+        FrameBuffer(0)
+    assert str(e.value) == str(g["fb0_msg"])
+
+
 @pytest.mark.parametrize("name", ["small", "atari", "vec"])
 def test_episode_script_matches_reference(golden_dir, name):
     g = _load(golden_dir, "episode_script_%s.npz" % name)
