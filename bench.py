@@ -56,7 +56,11 @@ def parse():
                     help="gradient exchange at N>1: fused into the optimizer over NVLink peer memory, or NCCL all-reduce")
     ap.add_argument("--precision", default="bf16", choices=["fp32", "bf16"],
                     help="bf16 = tcgen05 tensor-core mode (parity 2e-2, default; cnn arch); fp32 = CUDA-core parity mode (1e-4)")
-    ap.add_argument("--cpu-steps", type=int, default=20)
+    ap.add_argument("--config", type=int, default=2, choices=[1, 2, 3, 4, 5],
+                    help="BASELINE.json config: 1 CartPole MLP (B=32 and 100), 2 conv net B=32 (default, the driver's line), "
+                         "3 conv net B=512/GPU, 4 replay gather sweep k=32..8192, 5 Breakout shape: 1024-env greedy act + "
+                         "B=512 step + target sync")
+    ap.add_argument("--cpu-steps", type=int, default=100)
     ap.add_argument("--e2e-steps", type=int, default=2000)
     ap.add_argument("--skip-cpu", action="store_true")
     return ap.parse_args()
@@ -160,9 +164,10 @@ def fill_ring(rm_handle, capacity, seed, dev, stream):
 
 
 # ----------------------------------------------------------------------------------------------- reference arm
-def reference_steps_per_s(arch, batch, steps, warmup, capacity=1000000, pool=8192, seed=0):
+def reference_steps_per_s(arch, batch, steps, warmup, capacity=1000000, pool=8192, seed=0, one_thread_steps=0):
     """The reference's step on the host CPU: oracle port (TensorFlow cannot run on this image), all threads.
-    deque of `capacity` tuples over a pool of `pool` distinct 84x84x4 uint8 stacks, 4 adds + 1 update per step."""
+    deque of `capacity` tuples over a pool of `pool` distinct 84x84x4 uint8 stacks, 4 adds + 1 update per step.
+    one_thread_steps > 0: afterwards the same loop with torch limited to one thread (returned as a 4th value)."""
     import torch
     from oracle.replay_ref import ReplayRef
     from oracle.torch_ref import CpuBaselineAgent
@@ -196,6 +201,15 @@ def reference_steps_per_s(arch, batch, steps, warmup, capacity=1000000, pool=819
     for _ in range(steps):
         one()
     dt = time.perf_counter() - t0
+    if one_thread_steps:
+        torch.set_num_threads(1)
+        one()
+        t1 = time.perf_counter()
+        for _ in range(one_thread_steps):
+            one()
+        single = one_thread_steps / (time.perf_counter() - t1)
+        torch.set_num_threads(cores)
+        return steps / dt, dt / steps * 1e3, cores, single
     return steps / dt, dt / steps * 1e3, cores
 
 
@@ -203,20 +217,23 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    batch = args.batch or 32
+    batch = args.batch or (512 if args.config in (3, 5) else 32)
     steps = args.steps or 20
     warmup = args.warmup if args.warmup is not None else 3
-    v, ms, cores = reference_steps_per_s(args.arch, batch, steps, warmup)
-    sample = "%d updates of batch %d (4 adds + 1 update each) on a 1M-entry deque over 8192 distinct stacks" % (steps, batch)
+    # one timed "step" of this arm is a bounded sample of `per` updates, so that even --steps 20 times >= 100 updates
+    per = max(1, -(-100 // steps)) if batch <= 64 else 1
+    v, ms, cores = reference_steps_per_s(args.arch, batch, steps * per, warmup)
+    sample = ("%d steps x %d updates of batch %d (4 adds + 1 update each) on a 1M-entry deque over 8192 distinct stacks"
+              % (steps, per, batch))
     line = {
         "impl": "reference", "metric": "Nature-DQN minibatch updates/sec", "value": v, "unit": "updates/s",
-        "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": ms, "higher_is_better": True,
+        "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": ms * per, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args.arch, batch, args.gpus, 1000000),
         "cpu_baseline": {"value": v, "unit": "updates/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "reference-on-CPU (restated): TensorFlow is not installable here; oracle/torch_ref.py transcribes "
-                "dqn_agent.py:108-143 on torch-CPU fp32",
+                "dqn_agent.py:108-143 on torch-CPU fp32; run-to-run spread on this pool's hosts is about 160-185 updates/s",
     }
     emit(line)
 
@@ -232,28 +249,161 @@ def workload_config(arch, batch, n, capacity):
 
 
 # ----------------------------------------------------------------------------------------------- own arm
-def run_b200(args):
+def _setup(args):
+    """Process-level set-up shared by every config: build, device, process group."""
     import torch
     import torch.distributed as dist
     import __graft_entry__ as ge
     ge.build()
+    import data_parallel as dp
+    rank, local, world = dp.world_info()
+    if world != args.gpus and world == 1 and args.gpus > 1:
+        raise SystemExit("--gpus %d needs torchrun --nproc-per-node %d" % (args.gpus, args.gpus))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dp.init(device=dev)
+    return torch, dist, dp, rank, local, world, dev
+
+
+def _teardown(world, dist, torch):
+    """Ordered shutdown (graphs that hold NCCL kernels and the peer mappings go before the communicator), then a
+    normal return: the interpreter exits through its usual path."""
+    import gc
+    gc.collect()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    sys.stdout.flush()
+    sys.stderr.flush()
+
+
+def _timed_steps(torch, dist, world, rank, local, dev, step, warmup, steps, after_step=None):
+    """`warmup` untimed steps, then EXACTLY `steps` timed ones between CUDA events, bracketed by barrier + synchronize.
+    The clock sampler (an nvidia-smi child of rank 0) is started BEFORE the pre-timing barrier, and three more untimed
+    synchronised steps follow the barrier, so that no rank enters the timed region while another is still busy on the
+    host.  Returns (ms_total as max over ranks, [per-rank ms], clocks)."""
+    sampler = ClockSampler(local)
+    for i in range(warmup):
+        step(i)
+    torch.cuda.synchronize()
+    if rank == 0:
+        sampler.start()
+    if world > 1:
+        dist.barrier()
+    for i in range(3):
+        step(i)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(warmup, warmup + steps):
+        step(i)
+        if after_step is not None:
+            after_step(i - warmup)
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    clocks = sampler.stop() if rank == 0 else None
+    ms = e0.elapsed_time(e1)
+    per_rank = [ms]
+    if world > 1:
+        t = torch.zeros(world, device=dev)
+        t[rank] = ms
+        dist.all_reduce(t)
+        per_rank = [float(x) for x in t.tolist()]
+    return max(per_rank), per_rank, clocks
+
+
+def _kernel_times(torch, c, net, run_one, nprof=30):
+    """us per launch of every kernel of a step, from an instrumented eager pass (CUDA events around every launch)."""
+    c.check(c.lib.dqn_net_set_timing(net.handle, 2))
+    for i in range(nprof):
+        run_one(i)
+        c.check(c.lib.dqn_net_timing_collect(net.handle))
+    c.check(c.lib.dqn_net_set_timing(net.handle, 0))
+    kernels = {}
+    tot, cnt = c.c_f64(), c.c_i32()
+    s = 0
+    while True:
+        name = c.lib.dqn_stage_name(s)
+        if not name:
+            break
+        c.lib.dqn_net_timing_read(net.handle, s, c.C.byref(tot), c.C.byref(cnt))
+        if cnt.value:
+            kernels[name.decode()] = tot.value / cnt.value * 1e3
+        s += 1
+    floor = c.c_f64()
+    c.check(c.lib.dqn_net_timing_floor(net.handle, c.current_stream(), c.C.byref(floor)))
+    return kernels, floor.value
+
+
+def _dp_check(torch, dist, dp, network, cfg, rm, batch, d_idx, precision):
+    """Untimed self-check of the data-parallel step (the driver's test box has one GPU): from the same weights, one
+    update through the peer-memory exchange and one through backward -> NCCL all-reduce -> apply must give the same
+    weights, and every rank must hold bit-identical weights and bf16 operand images afterwards."""
+    a = network.Network.create_network(cfg, (84, 84, 4), A_PONG, num_replicas=dist.get_world_size())
+    b = network.Network.create_network(cfg, (84, 84, 4), A_PONG, num_replicas=dist.get_world_size())
+    dp.setup_network(a, cfg, mode="peer")
+    dp.setup_network(b, cfg, mode="nccl")
+    dp.train_step(a, rm, batch, d_idx)
+    dp.train_step(b, rm, batch, d_idx)
+    torch.cuda.synchronize()
+    wa, wb = a.flat_buffer("online").clone(), b.flat_buffer("online").clone()
+    rel = float(((wa - wb).abs().max() / wb.abs().max()).item())
+    ref = wa.clone()
+    dist.broadcast(ref, 0)
+    same = bool(torch.equal(ref, wa))
+    q = a.predict(rm.gather(d_idx).states[:8])            # through the refreshed bf16 operand images
+    qr = q.clone()
+    dist.broadcast(qr, 0)
+    t = torch.tensor([rel, 0.0 if same else 1.0, 0.0 if torch.equal(q, qr) else 1.0], device=wa.device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    a.dp_status()
+    ok = t[0].item() < 2e-5 and t[1].item() == 0.0 and t[2].item() == 0.0
+    del a, b
+    return {"result": "ok" if ok else "FAILED", "peer_vs_nccl_max_rel": float(t[0].item()),
+            "weights_identical_across_ranks": t[1].item() == 0.0, "q_identical_across_ranks": t[2].item() == 0.0,
+            "precision": precision}
+
+
+def run_b200(args):
+    torch, dist, dp, rank, local, world, dev = _setup(args)
+    if args.config == 1:
+        line = run_config1(args, torch, dev)
+    elif args.config == 4:
+        line = run_config4(args, torch, dev)
+    elif args.config == 5:
+        line = run_config5(args, torch, dist, dp, rank, local, world, dev)
+    else:
+        line = run_update_bench(args, torch, dist, dp, rank, local, world, dev)
+    if rank == 0 and line is not None:
+        emit(line)
+    _teardown(world, dist, torch)
+
+
+def _make_ring(args, torch, c, replay_memory, rank, local, dev):
+    rm = replay_memory.ReplayMemory(args.capacity, device=local, trusted=True)
+    rm._ensure(np.zeros((84, 84, 4), np.uint8))       # the first add fixes shape/dtype; then bulk-fill on the device
+    fill_ring(rm.handle, args.capacity, 100 + rank, dev, c.current_stream())
+    torch.cuda.synchronize()
+    rm._resync()
+    assert rm.size() == args.capacity, rm.size()
+    return rm
+
+
+def run_update_bench(args, torch, dist, dp, rank, local, world, dev):
+    """Configs 2 (B=32, the driver's line) and 3 (B=512 per GPU)."""
     import _cabi as c
     import network
     import replay_memory
     from dqn_agent import DQNAgent
     from frame_buffer import FrameBuffer
-
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if world != args.gpus:
-        if world == 1 and args.gpus > 1:
-            raise SystemExit("--gpus %d needs torchrun --nproc-per-node %d" % (args.gpus, args.gpus))
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-    batch = args.batch or 32            # same per-GPU minibatch at every N (weak scaling); --batch 512 = large-batch sweep
+    batch = args.batch or (512 if args.config == 3 else 32)      # same per-GPU minibatch at every N (weak scaling)
     steps = args.steps or (2000 if batch <= 64 else 300)
     warmup = max(3, args.warmup if args.warmup is not None else 50)
     if args.arch not in ("cnn", "nature"):
@@ -262,42 +412,25 @@ def run_b200(args):
     cfg.device_index = local
 
     net = network.Network.create_network(cfg, (84, 84, 4), A_PONG, num_replicas=world)
-    if world > 1:
-        dist.broadcast(net.flat_buffer("online"), 0)
-        net.sync_target()
-        net.set_hyper(cfg, grad_scale=1.0 / world)
-        if args.dp == "peer":
-            net.connect_peers()
-    rm = replay_memory.ReplayMemory(args.capacity, device=local, trusted=True)
-    # create the ring through the shell (first add fixes shape/dtype), then bulk-fill it on the device
-    seed_state = np.zeros((84, 84, 4), np.uint8)
-    rm._ensure(seed_state)
+    dp.setup_network(net, cfg, mode=args.dp)
     side = torch.cuda.Stream(device=dev)
     with torch.cuda.stream(side):
-        fill_ring(rm.handle, args.capacity, 100 + rank, dev, c.current_stream())
-        torch.cuda.synchronize()
-        rm._resync()
+        rm = _make_ring(args, torch, c, replay_memory, rank, local, dev)
         size = rm.size()
-        assert size == args.capacity, size
-
         # sample indices for every step, drawn with the reference's own sampler and uploaded before timing
         random.seed(1234 + rank)
         total_steps = warmup + steps
         idx_table = torch.tensor([random.sample(range(size), batch) for _ in range(total_steps)], dtype=torch.int32,
                                  device=dev)
         d_idx = torch.empty(batch, dtype=torch.int32, device=dev)
-        grad = net.flat_buffer("grad")
 
         def eager_step(want_loss=False):
-            if world == 1:
-                net.train_step(rm, batch, d_indices=d_idx, want_loss=want_loss)
-            elif net.peers_connected:
-                net.dp_train_step(rm, batch, d_indices=d_idx, want_loss=want_loss)
-            else:
-                b = rm.gather(d_idx)
-                net.backward_on_batch(b, want_loss=want_loss)
-                dist.all_reduce(grad)
-                net.apply_gradients()
+            dp.train_step(net, rm, batch, d_idx, want_loss=want_loss)
+
+        dp_check = None
+        if world > 1 and args.dp == "peer":
+            d_idx.copy_(idx_table[0])
+            dp_check = _dp_check(torch, dist, dp, network, cfg, rm, batch, d_idx, args.precision)
 
         # kernels per step (eager launches are counted by the library)
         d_idx.copy_(idx_table[0])
@@ -321,32 +454,11 @@ def run_b200(args):
             else:
                 eager_step()
 
-        for i in range(warmup):
-            step(i)
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-        sampler = ClockSampler(local)
-        if rank == 0:
-            sampler.start()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for i in range(warmup, warmup + steps):
-            step(i)
-            if (i - warmup) % 10000 == 9999:
+        def after(j):
+            if j % 10000 == 9999:
                 net.sync_target()                       # ATARI preset: target sync every 10000 updates
-        e1.record()
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-        clocks = sampler.stop() if rank == 0 else None
-        ms_total = e0.elapsed_time(e1)
-        if world > 1:
-            t = torch.tensor([ms_total], device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms_total = float(t.item())
+
+        ms_total, per_rank_ms, clocks = _timed_steps(torch, dist, world, rank, local, dev, step, warmup, steps, after)
         ms_per_step = ms_total / steps
         # whole-job aggregate: per-GPU minibatches of `batch` samples processed per second, summed over ranks
         # (one synchronous update = `world` such minibatches)
@@ -354,40 +466,16 @@ def run_b200(args):
         samples_per_s = world * batch * steps / (ms_total / 1e3)
 
         # ---- per-kernel durations (instrumented eager pass over fresh indices) -> roofline of the dominant kernel
-        roof, kernels = None, {}
-        if rank == 0 or world > 1:
-            c.check(c.lib.dqn_net_set_timing(net.handle, 2))
-            nprof = 30
-            g_evt0, g_evt1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            gather_ms = 0.0
-            for i in range(nprof):
-                d_idx.copy_(idx_table[(warmup + i) % total_steps])
-                if world > 1 and not net.peers_connected:
-                    g_evt0.record()
-                    b = rm.gather(d_idx)
-                    g_evt1.record()
-                    net.backward_on_batch(b)
-                    dist.all_reduce(grad)
-                    net.apply_gradients()
-                else:
-                    eager_step()
-                c.check(c.lib.dqn_net_timing_collect(net.handle))
-                if world > 1 and not net.peers_connected:
-                    gather_ms += g_evt0.elapsed_time(g_evt1)
-            c.check(c.lib.dqn_net_set_timing(net.handle, 0))
-            tot, cnt = c.c_f64(), c.c_i32()
-            s = 0
-            while True:
-                name = c.lib.dqn_stage_name(s)
-                if not name:
-                    break
-                c.lib.dqn_net_timing_read(net.handle, s, c.C.byref(tot), c.C.byref(cnt))
-                if cnt.value:
-                    kernels[name.decode()] = tot.value / cnt.value * 1e3        # us per launch
-                s += 1
-            if world > 1 and not net.peers_connected:
-                kernels["gather"] = gather_ms / nprof * 1e3
-            roof = roofline(kernels, args.arch, batch, net.flat_size)
+        def prof_one(i):
+            d_idx.copy_(idx_table[(warmup + i) % total_steps])
+            eager_step()
+        kernels, floor_us = _kernel_times(torch, c, net, prof_one)
+        roof = roofline(kernels, args.arch, batch, net.flat_size, floor_us)
+
+        # ---- the same at the large batch (config 3's per-GPU batch), where the GEMM kernels are no longer latency-bound
+        roof_large, large = None, None
+        if world == 1 and batch != 512 and args.arch == "cnn" and not args.skip_cpu:
+            roof_large, large = large_batch_block(args, torch, c, network, rm, dev, side)
 
         # ---- the other precision mode, same workload, for the record (N=1 only; short)
         other = None
@@ -414,57 +502,323 @@ def run_b200(args):
                      "steps": nother}
             del og, onet
 
-        # ---- gather-only throughput at a large batch (second half of BASELINE.json's metric)
+        # ---- gather-only throughput (second half of BASELINE.json's metric)
         gather_info = None
         if rank == 0:
-            gather_info = gather_sweep(rm, dev)
+            gather_info = gather_sweep(rm, dev, ks=(512, 8192))
 
     # ---- end to end through the public API (host frames in, loss out, every step)
     e2e = run_e2e(args, cfg, net, rm, world, dev, DQNAgent, FrameBuffer, dist if world > 1 else None)
+    if world > 1 and net.peers_connected:
+        net.dp_status()
 
     # CUDA graphs that hold NCCL kernels must be gone before the communicator is torn down
     graph = None
     torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
     if rank != 0:
-        _finish(world, dist)
-        return
+        return None
     cpu = None
     if world == 1 and not args.skip_cpu:
-        v, ms, cores = reference_steps_per_s(args.arch, batch, args.cpu_steps, 3)
-        cpu = {"value": v, "unit": "updates/s", "cores": cores, "kind": "port",
+        v, ms, cores, single = reference_steps_per_s(args.arch, batch, args.cpu_steps if batch <= 64 else 10, 3,
+                                                     one_thread_steps=20 if batch <= 64 else 3)
+        cpu = {"value": v, "unit": "updates/s", "cores": cores, "kind": "port", "one_thread_value": single,
                "sample": "%d updates of batch %d (4 adds + 1 update each) on a 1M-entry deque over 8192 distinct stacks; "
-                         "oracle/torch_ref.py (torch-CPU fp32) because TensorFlow cannot run here" % (args.cpu_steps, batch)}
-    line = {
+                         "oracle/torch_ref.py (torch-CPU fp32) because TensorFlow cannot run here; run-to-run spread on "
+                         "this pool's hosts is about 160-185 updates/s at batch 32" % (args.cpu_steps if batch <= 64 else 10, batch)}
+    return {
         "metric": "Nature-DQN minibatch updates/sec", "value": value, "unit": "updates/s", "n_gpus": world,
         "steps": steps, "warmup": warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
         "config": workload_config(args.arch, batch, world, args.capacity),
-        "samples_per_s": samples_per_s,
+        "samples_per_s": samples_per_s, "per_rank_ms_per_step": [m / steps for m in per_rank_ms],
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches_per_step * steps),
         "launches_per_step": int(launches_per_step), "cuda_graph": not args.no_graph,
-        "roofline": roof, "cpu_baseline": cpu, "kernels_us": kernels, "gather": gather_info,
-        "precision": args.precision, "other_precision_mode": other,
-        "dp_exchange": (args.dp if world > 1 else None),
+        "roofline": roof, "roofline_large_batch": roof_large, "large_batch": large,
+        "cpu_baseline": cpu, "kernels_us": kernels, "event_floor_us": floor_us,
+        "gather": gather_info, "precision": args.precision, "other_precision_mode": other,
+        "dp_exchange": (args.dp if world > 1 else None), "dp_check": dp_check,
     }
-    emit(line)
-    _finish(world, dist)
 
 
+def large_batch_block(args, torch, c, network, rm, dev, side, batch=512, steps=100):
+    """B=512 on the same ring in the same run: graph-replayed updates/s and the roofline of its dominant kernel."""
+    cfg = atari_config(batch, args.arch, args.precision)
+    cfg.device_index = dev.index
+    net = network.Network.create_network(cfg, (84, 84, 4), A_PONG)
+    size = rm.size()
+    random.seed(4321)
+    tab = torch.tensor([random.sample(range(size), batch) for _ in range(steps + 13)], dtype=torch.int32, device=dev)
+    d_idx = torch.empty(batch, dtype=torch.int32, device=dev)
+    d_idx.copy_(tab[0])
+    for _ in range(3):
+        net.train_step(rm, batch, d_indices=d_idx)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=side):
+        net.train_step(rm, batch, d_indices=d_idx)
+    for i in range(10):
+        d_idx.copy_(tab[i], non_blocking=True); g.replay()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        d_idx.copy_(tab[10 + i], non_blocking=True); g.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+
+    def prof_one(i):
+        d_idx.copy_(tab[i % (steps + 13)])
+        net.train_step(rm, batch, d_indices=d_idx)
+    kernels, floor_us = _kernel_times(torch, c, net, prof_one, nprof=20)
+    roof = roofline(kernels, args.arch, batch, net.flat_size, floor_us)
+    flops = 2.0 * batch * (4 * sum(MACS[args.arch]) - MACS[args.arch][0])    # fwd x2 + wgrad + dgrad (no conv1 dgrad)
+    del g, net
+    return roof, {"minibatch": batch, "value": 1e3 / ms, "unit": "updates/s", "ms_per_step": ms, "steps": steps,
+                  "samples_per_s": batch * 1e3 / ms, "step_tflops": flops / (ms * 1e-3) / 1e12, "kernels_us": kernels}
 
 
-def _finish(world, dist):
-    """Leave without running interpreter teardown: destroying NCCL communicators and CUDA graphs in arbitrary
-    order at exit can hang."""
-    sys.stdout.flush()
-    sys.stderr.flush()
-    if world > 1:
-        try:
-            dist.barrier()
-        except Exception:
-            pass
-    os._exit(0)
+# ----------------------------------------------------------------------------------------------- other configs
+def _event_time(torch, fn, n, warm=3):
+    for i in range(warm):
+        fn(i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(n):
+        fn(warm + i)
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / n          # ms per call
+
+
+def run_config1(args, torch, dev):
+    """Config 1: CartPole-v0, SimpleNetwork 4-20-20-2, CONTROL preset (scripts/dqn_params.sh), minibatch 32 and 100.
+    `value`: graph-replayed updates/s (gather from the ring + fused MLP forward/backward + Adam) at B=32;
+    `e2e`: the real agent loop on the cart-pole environment (env.step on the host, one update per env step)."""
+    import _cabi as c
+    import envs
+    import network
+    import replay_memory
+    from dqn_agent import DQNAgent
+    from network import Session
+
+    def cfg_for(batch):
+        return argparse.Namespace(
+            network="simple", optimizer="adam", lr=0.001, reg_param=0.001, momentum=0.9, rmsprop_decay=0.95,
+            minibatch_size=batch, max_batch=batch, num_episodes=10000, max_steps_per_episode=200,
+            replay_memory_capacity=50000, target_update_freq=3000, reward_discount=0.9, init_random_action_prob=0.5,
+            min_random_action_prob=0.1, random_action_explore_steps=50000, frames_per_state=1, resize_width=0,
+            resize_height=0, update_freq=1, replay_start_size=0, summary_freq=100, loss="mse", seed=0, input_dtype=None,
+            device_index=dev.index, cuda_graph=True, precision="fp32", logdir=tempfile.mkdtemp(prefix="dqn_bench_"))
+    env = envs.make("CartPole-v0", seed=0)
+    rm = replay_memory.ReplayMemory(50000, device=dev.index)
+    rng = np.random.default_rng(0)
+    s = env.reset()
+    for _ in range(20000):                       # real cart-pole transitions under the uniform-random policy
+        a = int(rng.integers(0, 2))
+        s2, r, done, _ = env.step(a)
+        rm.add(s, a, r, s2, done)
+        s = env.reset() if done else s2
+    steps = args.steps or 5000
+    res = {}
+    side = torch.cuda.Stream(device=dev)
+    with torch.cuda.stream(side):
+        for batch in (32, 100):
+            net = network.Network.create_network(cfg_for(batch), (4,), 2)
+            random.seed(3)
+            tab = torch.tensor([random.sample(range(rm.size()), batch) for _ in range(512)], dtype=torch.int32, device=dev)
+            d_idx = torch.empty(batch, dtype=torch.int32, device=dev)
+            d_idx.copy_(tab[0])
+            for _ in range(3):
+                net.train_step(rm, batch, d_indices=d_idx)
+            n0 = c.lib.dqn_launch_count()
+            net.train_step(rm, batch, d_indices=d_idx)
+            launches = c.lib.dqn_launch_count() - n0
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=side):
+                net.train_step(rm, batch, d_indices=d_idx)
+
+            def one(i):
+                d_idx.copy_(tab[i % 512], non_blocking=True)
+                g.replay()
+            ms = _event_time(torch, one, steps, warm=20)
+            res[batch] = {"value": 1e3 / ms, "unit": "updates/s", "us_per_step": ms * 1e3, "launches_per_step": int(launches)}
+            del g, net
+    # end to end: the agent loop itself (epsilon-greedy act on the device, env.step on the host, add, update)
+    cfg = cfg_for(32)
+    random.seed(0)
+    net = network.Network.create_network(cfg, (4,), 2)
+    agent = DQNAgent(envs.make("CartPole-v0", seed=1), net, Session(), replay_memory.ReplayMemory(50000, device=dev.index),
+                     cfg, enable_summary=True)
+    agent.train(5, 200)
+    torch.cuda.synchronize()
+    u0, t0 = agent.training_steps, time.perf_counter()
+    agent.train(60, 200)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    e2e_updates = agent.training_steps - u0
+    # CPU baseline: the oracle's transcription of the reference step on the same network
+    from oracle.replay_ref import ReplayRef
+    from oracle.torch_ref import CpuBaselineAgent
+    import torch as _t
+    cores = len(os.sched_getaffinity(0))
+    _t.set_num_threads(cores)
+    ref_rm = ReplayRef(50000)
+    env2 = envs.make("CartPole-v0", seed=0)
+    s = env2.reset()
+    for _ in range(20000):
+        a = int(rng.integers(0, 2))
+        s2, r, done, _ = env2.step(a)
+        ref_rm.add(s, a, r, s2, done)
+        s = env2.reset() if done else s2
+    ref = CpuBaselineAgent("simple", (4,), 2, "adam", 0.001, 0.001, 0.9, target_update_freq=3000, seed=0)
+    for _ in range(20):
+        ref.train_minibatch(ref_rm, 32)
+    t1 = time.perf_counter()
+    ncpu = 2000
+    for _ in range(ncpu):
+        ref.train_minibatch(ref_rm, 32)
+    cpu_v = ncpu / (time.perf_counter() - t1)
+    return {
+        "metric": "CartPole MLP minibatch updates/sec", "value": res[32]["value"], "unit": "updates/s", "n_gpus": 1,
+        "steps": steps, "warmup": 20, "ms_per_step": res[32]["us_per_step"] / 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "real CartPole-v0 transitions (built-in cart-pole physics)",
+        "config": {"workload": "CartPole-v0, SimpleNetwork 4-20-20-2, Adam lr 1e-3, gamma 0.9, 50k-transition ring, minibatch 32 "
+                               "(and 100 under minibatch_100)", "minibatch_per_gpu": 32,
+                   "cache": "launch/latency-bound: three small kernels per update, no roofline fraction claimed"},
+        "minibatch_100": res[100], "launches_per_step": res[32]["launches_per_step"],
+        "gpu_launches": res[32]["launches_per_step"] * steps,
+        "e2e": {"value": e2e_updates / dt, "unit": "updates/s", "h2d_bytes_per_step": 32 + 32 + 32 * 4,
+                "d2h_bytes_per_step": 4, "steps": e2e_updates,
+                "path": "DQNAgent.train on the cart-pole env: _pick_action (device forward when greedy), env.step on the host, "
+                        "ReplayMemory.add, _train_minibatch every env step"},
+        "roofline": None,
+        "cpu_baseline": {"value": cpu_v, "unit": "updates/s", "cores": cores, "kind": "port",
+                         "sample": "%d updates of batch 32 through oracle/torch_ref.py + oracle/replay_ref.py" % ncpu},
+    }
+
+
+def run_config4(args, torch, dev):
+    """Config 4: ReplayMemory sample + gather sweep on a 1M-transition uint8 ring, k = 32 ... 8192."""
+    import _cabi as c
+    import replay_memory
+    rm = _make_ring(args, torch, c, replay_memory, 0, dev.index, dev)
+    ks = (32, 64, 128, 256, 512, 1024, 2048, 4096, 8192)
+    n0 = c.lib.dqn_launch_count()
+    g = gather_sweep(rm, dev, ks=ks, iters=100)
+    launches = c.lib.dqn_launch_count() - n0
+    hbm, _, _, src = peaks()
+    # end to end through the reference-facing call: ReplayMemory.get_minibatch(k) -- host index draw, H2D indices, gather,
+    # both stacks + scalars copied back to host memory as the reference's tuples hold them
+    k = 512
+    random.seed(5)
+    for _ in range(2):
+        rm.get_minibatch(k)
+    t0 = time.perf_counter()
+    n = 20
+    for _ in range(n):
+        nt, t = rm.get_minibatch(k)
+        cnt = sum(1 for _ in nt) + sum(1 for _ in t)
+    dt = (time.perf_counter() - t0) / n
+    assert cnt == k
+    # CPU baseline: the reference's own ReplayMemory (restated) + the float32 feed conversion of both stacks
+    from oracle.replay_ref import ReplayRef
+    rng = np.random.default_rng(0)
+    pool = [rng.integers(0, 256, (84, 84, 4), dtype=np.uint8) for _ in range(4096)]
+    ref = ReplayRef(1000000)
+    for i in range(1000000):
+        ref.add(pool[i % 4096], 0, 0.0, pool[(i + 1) % 4096], False)
+    t1 = time.perf_counter()
+    ncpu = 5
+    for _ in range(ncpu):
+        nt, t = ref.get_minibatch(k)
+        items = list(nt) + list(t)
+        np.asarray([x[0] for x in items], dtype=np.float32)
+        np.asarray([x[3] for x in items], dtype=np.float32)
+    cpu_dt = (time.perf_counter() - t1) / ncpu
+    top = g
+    return {
+        "metric": "replay gather GB/s", "value": top["achieved_gbs"], "unit": "GB/s", "n_gpus": 1, "steps": 100, "warmup": 3,
+        "ms_per_step": top["us_per_launch"] / 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "ReplayMemory sample+gather: 1M-transition uint8 84x84 frame ring, both 84x84x4 stacks + "
+                               "action/reward/terminal per sampled transition, k=8192 (sweep k=32..8192 under gather.sweep)",
+                   "k": 8192, "cache": "inputs larger than L2: random transitions from a 14.1 GB frame ring"},
+        "gather": g, "gpu_launches": int(launches),
+        "roofline": {"kernel": "gather_stack4_u8_kernel", "bound": "hbm", "achieved": top["achieved_gbs"], "peak": hbm,
+                     "unit": "GB/s", "frac": top["achieved_gbs"] / hbm, "traffic": None, "peak_source": src,
+                     "algorithmic_bytes_per_transition": GATHER_BYTES},
+        "e2e": {"value": GATHER_BYTES * k / dt / 1e9, "unit": "GB/s", "k": k, "h2d_bytes_per_step": 4 * k,
+                "d2h_bytes_per_step": k * (2 * 4 * FRAME + 13), "ms_per_call": dt * 1e3,
+                "path": "ReplayMemory.get_minibatch(512): random.sample on the host, H2D indices, gather kernel, D2H of both "
+                        "stacks and the scalars, python tuples (the reference's return type)"},
+        "cpu_baseline": {"value": GATHER_BYTES * k / cpu_dt / 1e9, "unit": "GB/s", "cores": 1, "kind": "port",
+                         "sample": "%d x (get_minibatch(512) on a 1M-entry deque + float32 conversion of both stack lists), "
+                                   "oracle/replay_ref.py" % ncpu, "ms_per_call": cpu_dt * 1e3},
+    }
+
+
+def run_config5(args, torch, dist, dp, rank, local, world, dev):
+    """Config 5: Breakout shape (4 actions): batched greedy act for 1024 synthetic env states (split over the GPUs),
+    one B=512/GPU train step, one target sync -- each timed, and their sum."""
+    import _cabi as c
+    import network
+    import replay_memory
+    A, batch, envs_total = 4, 512, 1024
+    per_gpu = envs_total // world
+    cfg = atari_config(batch, args.arch, args.precision)
+    cfg.device_index = local
+    net = network.Network.create_network(cfg, (84, 84, 4), A, num_replicas=world)
+    dp.setup_network(net, cfg, mode=args.dp)
+    side = torch.cuda.Stream(device=dev)
+    with torch.cuda.stream(side):
+        rm = _make_ring(args, torch, c, replay_memory, rank, local, dev)
+        gen = torch.Generator(device=dev).manual_seed(2 + rank)
+        states = torch.randint(0, 256, (per_gpu, 84, 84, 4), dtype=torch.uint8, device=dev, generator=gen)
+        random.seed(9 + rank)
+        tab = torch.tensor([random.sample(range(rm.size()), batch) for _ in range(64)], dtype=torch.int32, device=dev)
+        d_idx = torch.empty(batch, dtype=torch.int32, device=dev)
+        d_idx.copy_(tab[0])
+        dp.train_step(net, rm, batch, d_idx)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=side):
+            dp.train_step(net, rm, batch, d_idx)
+        n = args.steps or 100
+
+        def act(i):
+            net.predict(states, argmax=True)
+
+        def train(i):
+            d_idx.copy_(tab[i % 64], non_blocking=True)
+            g.replay()
+
+        def sync(i):
+            net.sync_target()
+
+        def cycle(i):
+            act(i); train(i); sync(i)
+        out = {}
+        for name, fn in (("act", act), ("train", train), ("target_sync", sync), ("cycle", cycle)):
+            if world > 1:
+                torch.cuda.synchronize(); dist.barrier()
+            ms = _event_time(torch, fn, n, warm=5)
+            t = torch.tensor([ms], device=dev)
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            out[name] = float(t.item()) * 1e3
+        del g
+    if rank != 0:
+        return None
+    return {
+        "metric": "act(1024 envs) + train step (B=512/GPU) + target sync cycles/sec", "value": 1e6 / out["cycle"],
+        "unit": "cycles/s", "n_gpus": world, "steps": n, "warmup": 5, "ms_per_step": out["cycle"] / 1e3,
+        "higher_is_better": True, "scaling": "strong for the act phase (1024 envs split over the GPUs), weak for the update",
+        "vs_baseline": None, "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
+        "config": {"workload": "Breakout shape (4 actions): batched greedy act for 1024 synthetic 84x84x4 uint8 env states "
+                               "(%d per GPU) + one minibatch-512/GPU update + target-network sync" % per_gpu,
+                   "parallelism": "dp%d" % world, "cache": "update gathers fresh random transitions from a 14.1 GB ring"},
+        "phases_us": out, "sum_of_phases_us": out["act"] + out["train"] + out["target_sync"],
+        "roofline": None, "cpu_baseline": None, "e2e": None, "dp_exchange": (args.dp if world > 1 else None),
+    }
 
 
 def peaks():
@@ -476,16 +830,20 @@ def peaks():
 
 
 def _traffic(name, batch):
-    """DRAM bytes per launch of `name` from the committed ncu --set full captures (taken at B=32 and B=512), else None."""
+    """DRAM bytes per launch of `name` from the committed ncu --set full captures, else None.  Not measured in this run
+    (that needs a profiler): the source file is named beside the value."""
     try:
         t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-        return t["dram_bytes_per_launch"].get(str(batch), {}).get(name)
+        v = t["dram_bytes_per_launch"].get(str(batch), {}).get(name)
+        return v, (t.get("source") if v is not None else None)
     except Exception:
-        return None
+        return None, None
 
 
-def roofline(kernels, arch, batch, nparams):
-    """Roofline of the dominant kernel of the step (largest average duration)."""
+def roofline(kernels, arch, batch, nparams, floor_us=0.0):
+    """Roofline of the dominant kernel of the step (largest average duration on the critical path).  Durations come
+    from CUDA-event brackets in an eager pass; `floor_us` (the same bracket around an empty launch, measured in the
+    same run) is subtracted."""
     if not kernels:
         return None
     hbm, burst, sustained, src = peaks()
@@ -494,20 +852,22 @@ def roofline(kernels, arch, batch, nparams):
     side = ("head_wgrad", "loss", "wgrad_fc", "wgrad_conv3", "wgrad_conv2")
     crit = {k: v for k, v in kernels.items() if k not in side} or kernels
     name = max(crit, key=lambda k: crit[k])
-    us = crit[name]
+    raw_us = crit[name]
+    us = max(raw_us - floor_us, 0.25 * raw_us)
     macs = MACS[arch]
     layer = {"conv1": 0, "conv2": 1, "conv3": 2, "fc": 3}
+    traffic, tsrc = _traffic(name, batch)
     if name.startswith(("fwd_", "wgrad_", "dgrad_")):
         l = layer[name.split("_", 1)[1]]
         passes = 2 if name.startswith("fwd_") else 1          # online + target forward share one launch
         flops = 2.0 * macs[l] * batch * passes
         ach = flops / (us * 1e-6) / 1e12
         return {"kernel": name, "bound": "tensor", "achieved": ach, "peak": sustained, "unit": "TFLOP/s",
-                "frac": ach / sustained, "traffic": _traffic(name, batch), "us_per_launch": us,
+                "frac": ach / sustained, "traffic": traffic, "traffic_source": tsrc, "us_per_launch": us,
+                "us_event_bracket": raw_us, "event_floor_us": floor_us, "minibatch": batch,
                 "peak_source": src + " bf16 sustained",
-                "note": "implicit GEMM measured against the bf16 tensor-pipe peak (fp32 mode runs on CUDA cores); durations "
-                        "come from an instrumented eager pass (CUDA events around every launch, no PDL overlap), which adds "
-                        "several microseconds per launch at batch 32 -- the fraction is meaningful at --batch 512"}
+                "note": "implicit GEMM against the measured bf16 tensor-pipe peak; at batch 32 every kernel is a few "
+                        "CTAs of latency-bound work and the fraction only says so -- see roofline_large_batch"}
     if name == "gather":
         byts = GATHER_BYTES * batch
     elif name in ("optimizer", "reduce_grad"):
@@ -516,40 +876,49 @@ def roofline(kernels, arch, batch, nparams):
         byts = 0.0
     ach = byts / (us * 1e-6) / 1e9
     return {"kernel": name, "bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm,
-            "traffic": None, "us_per_launch": us, "peak_source": src}
+            "traffic": traffic, "traffic_source": tsrc, "us_per_launch": us, "us_event_bracket": raw_us,
+            "event_floor_us": floor_us, "minibatch": batch, "peak_source": src}
 
 
-def gather_sweep(rm, dev, k=8192, iters=30):
-    """Replay gather GB/s at a large batch (config 4 of BASELINE.json), CUDA-event timed, fresh indices each launch."""
+def gather_sweep(rm, dev, ks=(8192,), iters=30):
+    """Replay gather GB/s (config 4 of BASELINE.json) per k, CUDA-event timed, fresh random indices each launch (the
+    frame ring is far larger than L2).  Returns the k = max(ks) entry with the others under "sweep"."""
     import torch
     import _cabi as c
     size = rm.size()
-    random.seed(77)
-    tables = torch.tensor([random.sample(range(size), k) for _ in range(iters + 3)], dtype=torch.int32, device=dev)
-    states = torch.empty((k, 84, 84, 4), dtype=torch.uint8, device=dev)
-    nexts = torch.empty_like(states)
-    acts = torch.empty(k, dtype=torch.int32, device=dev)
-    rews = torch.empty(k, dtype=torch.float64, device=dev)
-    terms = torch.empty(k, dtype=torch.uint8, device=dev)
-    st = c.current_stream()
-
-    def go(i):
-        c.check(c.lib.dqn_replay_gather(rm.handle, tables[i].data_ptr(), k, states.data_ptr(), nexts.data_ptr(),
-                                        acts.data_ptr(), rews.data_ptr(), terms.data_ptr(), st))
-    for i in range(3):
-        go(i)
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for i in range(3, 3 + iters):
-        go(i)
-    e1.record()
-    torch.cuda.synchronize()
-    us = e0.elapsed_time(e1) / iters * 1e3
     hbm, _, _, src = peaks()
-    gbs = GATHER_BYTES * k / (us * 1e-6) / 1e9
-    return {"k": k, "us_per_launch": us, "achieved_gbs": gbs, "frac_of_hbm_peak": gbs / hbm, "peak_gbs": hbm,
-            "bytes_per_transition": GATHER_BYTES, "peak_source": src}
+    st = c.current_stream()
+    out = []
+    for k in ks:
+        random.seed(77 + k)
+        n = iters if k >= 512 else 200
+        tables = torch.tensor([random.sample(range(size), k) for _ in range(n + 3)], dtype=torch.int32, device=dev)
+        states = torch.empty((k, 84, 84, 4), dtype=torch.uint8, device=dev)
+        nexts = torch.empty_like(states)
+        acts = torch.empty(k, dtype=torch.int32, device=dev)
+        rews = torch.empty(k, dtype=torch.float64, device=dev)
+        terms = torch.empty(k, dtype=torch.uint8, device=dev)
+
+        def go(i):
+            c.check(c.lib.dqn_replay_gather(rm.handle, tables[i].data_ptr(), k, states.data_ptr(), nexts.data_ptr(),
+                                            acts.data_ptr(), rews.data_ptr(), terms.data_ptr(), st))
+        for i in range(3):
+            go(i)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(3, 3 + n):
+            go(i)
+        e1.record()
+        torch.cuda.synchronize()
+        us = e0.elapsed_time(e1) / n * 1e3
+        gbs = GATHER_BYTES * k / (us * 1e-6) / 1e9
+        out.append({"k": k, "us_per_launch": us, "achieved_gbs": gbs, "frac_of_hbm_peak": gbs / hbm})
+        del tables, states, nexts
+    top = dict(max(out, key=lambda e: e["k"]))
+    top.update({"peak_gbs": hbm, "bytes_per_transition": GATHER_BYTES, "peak_source": src, "sweep": out,
+                "timing": "back-to-back launches between two CUDA events (launch overhead overlaps the previous kernel)"})
+    return top
 
 
 def run_e2e(args, cfg, net, rm, world, dev, DQNAgent, FrameBuffer, dist):

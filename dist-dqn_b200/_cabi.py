@@ -70,6 +70,9 @@ SIGNATURES = {
     "dqn_net_target_sync": (C.c_int, [c_vp, c_vp]),
     "dqn_net_dp_handle": (C.c_int, [c_vp, c_vp]),
     "dqn_net_dp_connect": (C.c_int, [c_vp, c_i32, c_i32, c_vp]),
+    "dqn_net_dp_set_timeout": (C.c_int, [c_vp, c_f64]),
+    "dqn_net_dp_status": (C.c_int, [c_vp, C.POINTER(c_i64), c_vp]),
+    "dqn_net_refresh_operands": (C.c_int, [c_vp, c_i32, c_vp]),
     "dqn_net_dp_step": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
     "dqn_train_step_dp": (C.c_int, [c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
     "dqn_train_step": (C.c_int, [c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
@@ -81,6 +84,7 @@ SIGNATURES = {
     "dqn_net_set_timing": (C.c_int, [c_vp, c_i32]),
     "dqn_net_timing_collect": (C.c_int, [c_vp]),
     "dqn_net_timing_read": (C.c_int, [c_vp, c_i32, C.POINTER(c_f64), C.POINTER(c_i32)]),
+    "dqn_net_timing_floor": (C.c_int, [c_vp, c_vp, C.POINTER(c_f64)]),
     "dqn_stage_name": (C.c_char_p, [c_i32]),
 }
 

@@ -191,6 +191,8 @@ struct OptArgs {
   long long P;
   int peer_mask;                         // bit s set: segment s is summed over the ranks here; clear: already summed locally
   int flag_slot;                         // which flag array guards the peer-summed segments
+  long long timeout_ns;                  // how long a rank waits for its peers' flags before it reports them missing
+  unsigned long long* err;               // device word: last step whose wait timed out (0 = none); read by dqn_net_dp_status
 };
 
 __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
@@ -202,6 +204,54 @@ __device__ __forceinline__ float ld_relaxed_sys(const float* p) {
   float v;
   asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
   return v;
+}
+__device__ __forceinline__ float4 ld_relaxed_sys_v4(const float* p) {
+  float4 v;
+  asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+// One thread waits until every rank has published its gradient of `step` (flags[r] >= step).  The wait is bounded by
+// a.timeout_ns of wall-clock time (dqn_net_dp_set_timeout; ranks are driven by independent host code, so seconds of skew
+// are normal): when it expires the step number is left in *a.err for the host (dqn_net_dp_status) and the kernel goes on
+// with whatever the exchange buffers hold, instead of trapping and taking the CUDA context down.
+__device__ __forceinline__ void wait_peer_flags(const OptArgs& a, unsigned long long step) {
+  const unsigned long long t0 = global_timer_ns();
+  for (int r = 0; r < a.world; ++r) {
+    unsigned spins = 0;
+    while (ld_acquire_sys(a.flags + 8 * a.flag_slot + r) < step) {
+      if ((++spins & 1023u) == 0 && (long long)(global_timer_ns() - t0) > a.timeout_ns) {
+        atomicMax(a.err, step);
+        return;
+      }
+    }
+  }
+}
+
+// Sum over the ranks of element gi of the exchange buffers.  All loads are issued before the first add (a loop with
+// a run-time trip count is a serial chain of NVLink round trips); the fixed tree is the same on every rank, so the
+// ranks end up with bit-identical sums.
+__device__ __forceinline__ float peer_sum1(const OptArgs& a, size_t gi) {
+  float v[8];
+#pragma unroll
+  for (int r = 0; r < 8; ++r) v[r] = r < a.world ? ld_relaxed_sys(a.peer_grad[r] + gi) : 0.f;
+  return ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
+}
+__device__ __forceinline__ float4 peer_sum4(const OptArgs& a, size_t gi) {      // gi % 4 == 0
+  float4 v[8];
+#pragma unroll
+  for (int r = 0; r < 8; ++r) v[r] = r < a.world ? ld_relaxed_sys_v4(a.peer_grad[r] + gi) : make_float4(0.f, 0.f, 0.f, 0.f);
+  float4 s;
+  s.x = ((v[0].x + v[1].x) + (v[2].x + v[3].x)) + ((v[4].x + v[5].x) + (v[6].x + v[7].x));
+  s.y = ((v[0].y + v[1].y) + (v[2].y + v[3].y)) + ((v[4].y + v[5].y) + (v[6].y + v[7].y));
+  s.z = ((v[0].z + v[1].z) + (v[2].z + v[3].z)) + ((v[4].z + v[5].z) + (v[6].z + v[7].z));
+  s.w = ((v[0].w + v[1].w) + (v[2].w + v[3].w)) + ((v[4].w + v[5].w) + (v[6].w + v[7].w));
+  return s;
 }
 
 // Sum of the weight-gradient partials of element i in a fixed order (deterministic).  Up to ~150 partials (one per CTA
@@ -255,15 +305,8 @@ __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs a) {
   }
   const long long step = *a.step;
   if (a.world > 1) {
-    // wait until every rank has published its gradient of this step (bounded: a dead peer traps instead of hanging)
-    if (threadIdx.x == 0) {
-      const long long t0 = clock64();
-      for (int r = 0; r < a.world; ++r) {
-        while (ld_acquire_sys(a.flags + 8 * a.flag_slot + r) < (unsigned long long)step) {
-          if (clock64() - t0 > 8000000000LL) __trap();
-        }
-      }
-    }
+    // wait until every rank has published its gradient of this step
+    if (threadIdx.x == 0) wait_peer_flags(a, (unsigned long long)step);
     __syncthreads();
   }
   if (i >= s.len) return;
@@ -272,9 +315,7 @@ __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs a) {
   float g;
   if (a.world > 1 && ((a.peer_mask >> blockIdx.y) & 1)) {
     const size_t gi = (size_t)(step & 1) * (size_t)a.P + p;
-    g = 0.f;
-    for (int r = 0; r < a.world; ++r) g += ld_relaxed_sys(a.peer_grad[r] + gi);     // rank order: identical on every rank
-    g *= a.gscale;
+    g = peer_sum1(a, gi) * a.gscale;
   } else {
     g = seg_grad(s, i) * a.gscale;
   }
@@ -396,23 +437,18 @@ __global__ void __launch_bounds__(256) reduce_grad_kernel(OptArgs a, float* __re
 __global__ void __launch_bounds__(256) peer_sum_kernel(OptArgs a, int seg_base, float* __restrict__ gsum) {
   pdl_wait();
   const Seg s = a.seg[blockIdx.y + seg_base];
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = (blockIdx.x * blockDim.x + threadIdx.x) * 4;            // 4 consecutive parameters per thread: 16-byte peer loads
   const long long step = *a.step;
-  if (threadIdx.x == 0) {
-    const long long t0 = clock64();
-    for (int r = 0; r < a.world; ++r) {
-      while (ld_acquire_sys(a.flags + 8 * a.flag_slot + r) < (unsigned long long)step) {
-        if (clock64() - t0 > 8000000000LL) __trap();
-      }
-    }
-  }
+  if (threadIdx.x == 0) wait_peer_flags(a, (unsigned long long)step);
   __syncthreads();
   if (i >= s.len) return;
-  const size_t p = (size_t)s.off + i;
-  const size_t gi = (size_t)(step & 1) * (size_t)a.P + p;
-  float g = 0.f;
-  for (int r = 0; r < a.world; ++r) g += ld_relaxed_sys(a.peer_grad[r] + gi);      // rank order: identical on every rank
-  gsum[p] = g;
+  const size_t p = (size_t)s.off + i;                                  // segments start at multiples of 4 floats
+  const size_t gi = (size_t)(step & 1) * (size_t)a.P + p;              // P is a multiple of 4 as well
+  if (i + 4 <= s.len) {
+    *reinterpret_cast<float4*>(gsum + p) = peer_sum4(a, gi);
+  } else {
+    for (int e = 0; i + e < s.len; ++e) gsum[p + e] = peer_sum1(a, gi + e);
+  }
 }
 
 // loss = mean_b se_b + reg * sum_{reg tensors} ||w||^2 / 2   (network.py:150-152); one CTA.
@@ -448,6 +484,11 @@ __global__ void dp_publish_kernel(unsigned long long* const* peer_flags, int ran
     const unsigned long long v = (unsigned long long)*step;
     asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(peer_flags[r] + rank), "l"(v) : "memory");
   }
+}
+
+__global__ void empty_kernel() {
+  pdl_trigger();
+  pdl_wait();
 }
 
 __global__ void fill_kernel(float* p, long long n, float v) {
@@ -652,6 +693,8 @@ struct dqn_net_s {
   void* dp_peer_block[8] = {};                 // mapped exchange blocks of all ranks (own = dp_block)
   unsigned long long** dp_peer_flags_dev = nullptr;   // device array of the peers' flag pointers
   unsigned int* dp_counter = nullptr;                 // finished-block counter of the publishing reduce kernel
+  unsigned long long* dp_err = nullptr;               // last step whose flag wait timed out (0 = none)
+  long long dp_timeout_ns = 120LL * 1000000000LL;     // dqn_net_dp_set_timeout
   // weight-gradient kernels run on a forked stream, concurrently with the data-gradient chain (captured into the
   // step's CUDA graph as a parallel branch)
   cudaStream_t side = nullptr, side2 = nullptr;     // side2: early half of the data-parallel exchange
@@ -941,6 +984,15 @@ extern "C" int dqn_net_set_global_step(dqn_net_t h, int64_t step) {
   long long v = step;
   DQN_CUDA(cudaDeviceSynchronize());
   DQN_CUDA(cudaMemcpy(h->step, &v, sizeof(v), cudaMemcpyHostToDevice));
+  if (h->dp_block) {
+    // the exchange flags count steps too ("rank r has published step s"): realign this rank's flag arrays, otherwise a
+    // smaller restored step would make every wait pass at once.  Every rank must do this at the same point, with no
+    // dqn_net_dp_step in flight on any rank (Network.load puts a barrier on both sides).
+    unsigned long long f[16];
+    for (int i = 0; i < 16; ++i) f[i] = (unsigned long long)step;
+    DQN_CUDA(cudaMemcpy(h->dp_block, f, sizeof(f), cudaMemcpyHostToDevice));
+    if (h->dp_err) DQN_CUDA(cudaMemset(h->dp_err, 0, 8));
+  }
   return 0;
 }
 
@@ -1288,6 +1340,18 @@ static void fill_segs(dqn_net_s* h, OptArgs* o, const int nsplit[4], bool from_f
   o->gscale = h->hyper.grad_scale; o->opt = h->hyper.optimizer;
 }
 
+// data-parallel fields of the optimizer / exchange kernels' arguments
+static void set_dp_args(dqn_net_s* h, OptArgs* o, int flag_slot) {
+  o->world = h->dp_world;
+  for (int r = 0; r < h->dp_world; ++r)
+    o->peer_grad[r] = reinterpret_cast<const float*>(static_cast<const char*>(h->dp_peer_block[r]) + 256);
+  o->flags = static_cast<const unsigned long long*>(h->dp_block);
+  o->flag_slot = flag_slot;
+  o->P = h->P;
+  o->timeout_ns = h->dp_timeout_ns;
+  o->err = h->dp_err;
+}
+
 static int max_seg_len(const OptArgs& o) {
   int m = 0;
   for (int i = 0; i < o.nseg; ++i) m = o.seg[i].len > m ? o.seg[i].len : m;
@@ -1439,17 +1503,14 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       DQN_CUDA(cudaStreamWaitEvent(s2, h->ev_head, 0));
       OptArgs ea;
       fill_segs(h, &ea, nsplit, false);
-      ea.world = h->dp_world;
-      for (int r = 0; r < h->dp_world; ++r)
-        ea.peer_grad[r] = reinterpret_cast<const float*>(static_cast<const char*>(h->dp_peer_block[r]) + 256);
-      ea.flags = static_cast<const unsigned long long*>(h->dp_block);
-      ea.flag_slot = 0;
+      set_dp_args(h, &ea, 0);
       dim3 g3((max_seg_len(ea) + 255) / 256, 3);
       dqn::count_launch();
       launch_pdl(reduce_grad_kernel, g3, dim3(256), 0, s2, 1, ea, h->dp_grad, 0.f, 1,
                  PublishArgs{h->dp_peer_flags_dev, h->dp_counter, h->dp_rank, h->dp_world, 0, 2});
       dqn::count_launch();
-      launch_pdl(peer_sum_kernel, g3, dim3(256), 0, s2, 1, ea, 2, h->grad);
+      dim3 g3v((max_seg_len(ea) / 4 + 256) / 256, 3);          // 4 parameters per thread
+      launch_pdl(peer_sum_kernel, g3v, dim3(256), 0, s2, 1, ea, 2, h->grad);
       DQN_CUDA(cudaEventRecord(h->ev_join2, s2));
       return 0;
     };
@@ -1512,10 +1573,7 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
     DQN_CUDA(cudaGetLastError());
     if (mode == 2) {
       // late half of the exchange: conv1 and conv2 (segments 0, 1) are published here and summed by the optimizer
-      oa.world = h->dp_world;
-      for (int r = 0; r < h->dp_world; ++r)
-        oa.peer_grad[r] = reinterpret_cast<const float*>(static_cast<const char*>(h->dp_peer_block[r]) + 256);
-      oa.flags = static_cast<const unsigned long long*>(h->dp_block);
+      set_dp_args(h, &oa, 1);
       dim3 g01((max_seg_len(oa) + 255) / 256, 2);
       {
         StageScope sc(h, DQN_STAGE_REDUCE_GRAD, st);
@@ -1543,12 +1601,7 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
     // (peer loads over NVLink)
     const int one[4] = {1, 1, 1, 1};
     fill_segs(h, &oa, one, true);
-    oa.world = h->dp_world;
-    for (int r = 0; r < h->dp_world; ++r)
-      oa.peer_grad[r] = reinterpret_cast<const float*>(static_cast<const char*>(h->dp_peer_block[r]) + 256);
-    oa.flags = static_cast<const unsigned long long*>(h->dp_block);
-    oa.P = h->P;
-    oa.flag_slot = 1;
+    set_dp_args(h, &oa, 1);
     // conv nets: only segments 0, 1 (conv1, conv2) are still to be summed over the ranks; the MLP exchanges everything here
     oa.peer_mask = h->arch == DQN_ARCH_SIMPLE ? 0x7 : 0x3;
     dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
@@ -1601,6 +1654,14 @@ extern "C" int dqn_net_target_sync(dqn_net_t h, dqn_stream_t stream) {
   return 0;
 }
 
+extern "C" int dqn_net_refresh_operands(dqn_net_t h, int32_t which, dqn_stream_t stream) {
+  DQN_REQUIRE(h, DQN_ERR_INVALID, "refresh_operands: NULL handle");
+  DQN_REQUIRE(which == DQN_BUF_ONLINE || which == DQN_BUF_TARGET, DQN_ERR_INVALID, "refresh_operands: which must be online or target");
+  if (h->precision != 1) return 0;                      // the fp32 kernels read the master weights themselves
+  DeviceGuard g(h->device);
+  return refresh_bf16_weights(h, which == DQN_BUF_ONLINE ? 0 : 1, static_cast<cudaStream_t>(stream));
+}
+
 extern "C" int dqn_train_step(dqn_net_t net, dqn_replay_t replay, const int32_t* d_logical_idx, int32_t k, float* d_loss,
                               dqn_stream_t stream) {
   DQN_REQUIRE(net && replay && d_logical_idx, DQN_ERR_INVALID, "dqn_train_step: NULL argument");
@@ -1632,9 +1693,11 @@ static int dp_alloc(dqn_net_s* h) {
   h->dp_grad = reinterpret_cast<float*>(static_cast<char*>(h->dp_block) + 256);
   DQN_CUDA(cudaMalloc(reinterpret_cast<void**>(&h->dp_peer_flags_dev), 8 * sizeof(void*)));
   h->allocs.push_back(h->dp_peer_flags_dev);
-  DQN_CUDA(cudaMalloc(reinterpret_cast<void**>(&h->dp_counter), 16));
-  DQN_CUDA(cudaMemset(h->dp_counter, 0, 16));
+  DQN_CUDA(cudaMalloc(reinterpret_cast<void**>(&h->dp_counter), 32));
+  DQN_CUDA(cudaMemset(h->dp_counter, 0, 32));
   h->allocs.push_back(h->dp_counter);
+  h->dp_err = reinterpret_cast<unsigned long long*>(h->dp_counter + 4);       // bytes 16..23 of the same allocation
+  { const char* to = getenv("DQN_DP_TIMEOUT_S"); if (to && atof(to) > 0) h->dp_timeout_ns = (long long)(atof(to) * 1e9); }
   return 0;
 }
 
@@ -1696,6 +1759,24 @@ extern "C" int dqn_train_step_dp(dqn_net_t net, dqn_replay_t replay, const int32
   if (rc) return rc;
   return run_step(net, net->st_states, net->st_next, net->st_actions, net->st_rewards, net->st_term, k, d_loss, nullptr, 2,
                   0, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int dqn_net_dp_set_timeout(dqn_net_t h, double seconds) {
+  DQN_REQUIRE(h && seconds > 0, DQN_ERR_INVALID, "dp_set_timeout: bad argument");
+  h->dp_timeout_ns = (long long)(seconds * 1e9);
+  return 0;
+}
+
+extern "C" int dqn_net_dp_status(dqn_net_t h, int64_t* timed_out_step, dqn_stream_t stream) {
+  DQN_REQUIRE(h && timed_out_step, DQN_ERR_INVALID, "dp_status: NULL argument");
+  *timed_out_step = 0;
+  if (!h->dp_err) return 0;
+  DeviceGuard g(h->device);
+  unsigned long long v = 0;
+  DQN_CUDA(cudaMemcpyAsync(&v, h->dp_err, sizeof(v), cudaMemcpyDeviceToHost, static_cast<cudaStream_t>(stream)));
+  DQN_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+  *timed_out_step = (int64_t)v;
+  return 0;
 }
 
 // ---------------------------------------------------------------------------------------------- precision mode
@@ -1766,6 +1847,32 @@ extern "C" int dqn_net_timing_collect(dqn_net_t h) {
   return 0;
 }
 
+// What the event bracket of the timing hooks measures around a kernel that does nothing: event record, launch of an
+// empty kernel the same way the step's kernels are launched, event record.  bench.py subtracts it from the brackets.
+extern "C" int dqn_net_timing_floor(dqn_net_t h, dqn_stream_t stream, double* us) {
+  DQN_REQUIRE(h && us, DQN_ERR_INVALID, "timing_floor: NULL argument");
+  DeviceGuard g(h->device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  cudaEvent_t e0, e1;
+  DQN_CUDA(cudaEventCreate(&e0));
+  DQN_CUDA(cudaEventCreate(&e1));
+  double total = 0.0;
+  const int n = 20;
+  for (int i = 0; i < n + 2; ++i) {
+    DQN_CUDA(cudaEventRecord(e0, st));
+    launch_pdl(empty_kernel, dim3(1), dim3(32), 0, st, 1);
+    DQN_CUDA(cudaEventRecord(e1, st));
+    DQN_CUDA(cudaEventSynchronize(e1));
+    float ms = 0.f;
+    DQN_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+    if (i >= 2) total += ms;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  *us = total / n * 1e3;
+  return 0;
+}
+
 extern "C" int dqn_net_timing_read(dqn_net_t h, int32_t stage, double* total_ms, int32_t* count) {
   DQN_REQUIRE(h && stage >= 0 && stage < DQN_NUM_STAGES, DQN_ERR_INVALID, "timing_read: bad argument");
   if (total_ms) *total_ms = h->stage_ms[stage];
@@ -1808,6 +1915,9 @@ extern "C" int dqn_cnn_forward_noalloc(const float* d_params, int32_t num_action
   DQN_REQUIRE(n <= kNoAllocMaxStates, DQN_ERR_INVALID,
               "dqn_cnn_forward_noalloc: n=%d exceeds the built-in scratch, which holds at most %d states per call; "
               "split the batch or use dqn_net_forward", n, kNoAllocMaxStates);
+  DQN_REQUIRE(((uintptr_t)d_params % 16) == 0 && ((uintptr_t)d_states % 4) == 0, DQN_ERR_INVALID,
+              "dqn_cnn_forward_noalloc: d_params must be 16-byte and d_states 4-byte aligned");
+  // every argument check is above this line: a refused call has touched nothing
   int dev = -1;
   DQN_CUDA(cudaGetDevice(&dev));
   DQN_REQUIRE(dev >= 0 && dev < kNoAllocMaxDevices, DQN_ERR_UNSUPPORTED, "device index %d not supported", dev);
@@ -1834,8 +1944,6 @@ extern "C" int dqn_cnn_forward_noalloc(const float* d_params, int32_t num_action
   const float* t[10];
   int64_t off = 0;
   for (int i = 0; i < 10; ++i) { t[i] = d_params + off; off += sizes[i]; }
-  DQN_REQUIRE(((uintptr_t)d_params % 16) == 0 && ((uintptr_t)d_states % 4) == 0, DQN_ERR_INVALID,
-              "dqn_cnn_forward_noalloc: d_params must be 16-byte and d_states 4-byte aligned");
   for (int l = 0; l < 4; ++l) {
     FwdArgs a;
     a.B = n;

@@ -18,8 +18,11 @@ import os
 import random
 from functools import partial
 
+import time
+
 import numpy as np
 
+import data_parallel
 import utils
 from frame_buffer import FrameBuffer
 from stats import Stats
@@ -90,7 +93,18 @@ class DQNAgent(object):
         self._pass_newest = (config.frames_per_state > 1 and getattr(replay_memory, '_trusted', False)
                              and type(replay_memory).__name__ == 'ReplayMemory' and hasattr(replay_memory, 'seal'))
 
-        self._prefill_replay_memory(config.replay_start_size)     # dqn_agent.py:47
+        # data parallel: the number of gradient exchanges must not depend on the rank.  The "replay memory still
+        # smaller than a minibatch" early-out of _train_minibatch would make it so, hence the prefill covers at least
+        # one minibatch; ranks whose episode loop ends early keep updating until every rank is done (StopAgreement).
+        prefill = config.replay_start_size
+        self._stop = None
+        if self._world > 1:
+            prefill = max(prefill, config.minibatch_size)
+            self._stop = data_parallel.StopAgreement(window=int(getattr(config, 'dp_stop_window', 64)))
+        self._rate_t0, self._rate_steps0 = time.perf_counter(), 0
+        self.updates_per_sec = 0.0
+
+        self._prefill_replay_memory(prefill)                      # dqn_agent.py:47
         self._update_target_network()                             # dqn_agent.py:50 (step 0 always syncs)
 
     # ------------------------------------------------------------------ training loop (dqn_agent.py:52-106)
@@ -100,10 +114,28 @@ class DQNAgent(object):
             self.stats.log_episode(reward, steps)
             logging.info('Episode = %d, steps = %d, reward = %d, training steps = %d, last-100 mean reward = %.2f'
                          % (episode, steps, reward, self.training_steps, self.stats.last_100_mean_reward()))
+            self._log_rate()
             if supervisor and supervisor.should_stop():
                 logging.warning('Received signal to stop. Exiting train loop.')
                 break
+        if self._stop is not None:
+            # this rank's loop is over; keep the exchange count equal on every rank until all of them are done
+            self._stop.finished = True
+            while not self._stop.all_finished:
+                self._train_minibatch(self.config.minibatch_size)
+            if getattr(self.network, 'peers_connected', False):
+                self.network.dp_status()
         self.flush_summaries()
+
+    def _log_rate(self):
+        """The reference's throughput signal is the Supervisor's 'global_step/sec' line (main.py:136-143); here the same
+        number is logged once per episode (updates since the previous line / wall-clock seconds)."""
+        now = time.perf_counter()
+        dt, dn = now - self._rate_t0, self.training_steps - self._rate_steps0
+        if dt > 0 and dn > 0:
+            self.updates_per_sec = dn / dt
+            logging.info('global_step/sec: %g' % self.updates_per_sec)
+        self._rate_t0, self._rate_steps0 = now, self.training_steps
 
     def train_episode(self, max_steps):
         state = self._reset_episode()
@@ -159,6 +191,8 @@ class DQNAgent(object):
             self.flush_summaries()
         self.training_steps += 1
         self._update_target_network()
+        if self._stop is not None:
+            self._stop.after_update(self.training_steps)
 
     def _read_loss_later(self, loss, step):
         import torch
@@ -195,20 +229,8 @@ class DQNAgent(object):
             self.summary_writer.flush()
 
     def _eager_step(self, k, d_idx, want_loss, loss_out=None):
-        net, rm = self.network, self.replay_memory
-        if self._world == 1:
-            return net.train_step(rm, k, d_indices=d_idx, want_loss=want_loss, loss_out=loss_out)
-        if getattr(net, 'peers_connected', False):     # gradient exchange fused into the optimizer (NVLink peer loads)
-            return net.dp_train_step(rm, k, d_indices=d_idx, want_loss=want_loss, loss_out=loss_out)
-        import torch.distributed as dist
-        batch = rm.gather(d_idx)
-        loss, _ = net.backward_on_batch(batch, want_loss=want_loss)
-        dist.all_reduce(net.flat_buffer('grad'))                  # sum; grad_scale = 1/world applied by the update
-        net.apply_gradients()
-        if want_loss and loss_out is not None:
-            loss_out.copy_(loss, non_blocking=True)
-            return loss_out
-        return loss
+        # single GPU, peer-memory exchange fused into the step's kernels, or NCCL all-reduce (data_parallel.py)
+        return data_parallel.train_step(self.network, self.replay_memory, k, d_idx, want_loss=want_loss, loss_out=loss_out)
 
     def _device_step(self, k, indices, want_loss):
         """One update for the given logical sample indices (host list).  The first call per (k, want_loss) runs eagerly;

@@ -2,10 +2,15 @@
 """Entry point with the reference's flags (reference src/main.py:12-98) driving the B200 path.
 
 The reference's parameter-server/gRPC cluster (main.py:100-193) is replaced by synchronous data
-parallelism: launch one process per GPU with torchrun and every rank trains on its own replay
-shard while gradients are averaged with an NCCL all-reduce (the reference's --sync semantics).
-The distribution flags are still accepted so the scripts keep working; --ps_hosts/--worker_hosts/
---job/--disable_* have no effect here.
+parallelism: launch one process per GPU with torchrun (scripts/dqn_multi_gpu.sh) and every rank trains
+on its own replay shard while the gradients are averaged -- by default inside the step's own kernels over
+NVLink peer memory (--dp peer), or with an NCCL all-reduce (--dp nccl); both have the reference's --sync
+semantics.  The distribution flags are still accepted so the scripts keep working; --ps_hosts/
+--worker_hosts/--job/--disable_* have no effect here.
+
+--precision picks the arithmetic of the conv nets: bf16 (tcgen05 tensor cores, fp32 accumulation and
+fp32 master weights; the default for cnn / nature on uint8 frames) or fp32 (CUDA cores, the 1e-4 parity
+mode; always used by the simple network).
 """
 import argparse
 import logging
@@ -62,7 +67,16 @@ def parse_args(argv=None):
     # Extras
     p.add_argument('--seed', default=None, type=int)
     p.add_argument('--no_cuda_graph', dest='cuda_graph', action='store_false')
-    return p.parse_args(argv)
+    p.add_argument('--precision', default=None, choices=['fp32', 'bf16'],
+                   help='conv-net arithmetic; default bf16 for cnn/nature, fp32 for simple')
+    p.add_argument('--dp', default='peer', choices=['peer', 'nccl'],
+                   help='gradient exchange with more than one GPU: fused over NVLink peer memory, or NCCL all-reduce')
+    args = p.parse_args(argv)
+    if args.network == 'simple':
+        args.precision = 'fp32'
+    elif args.precision is None:
+        args.precision = 'bf16'
+    return args
 
 
 class _Supervisor(object):
@@ -83,33 +97,34 @@ def run_worker(args):
     from dqn_agent import DQNAgent
     from network import Network, Session
     from replay_memory import ReplayMemory
-    world = int(os.environ.get('WORLD_SIZE', '1'))
-    rank = int(os.environ.get('RANK', '0'))
-    local = int(os.environ.get('LOCAL_RANK', str(args.gpu_id if world == 1 else 0)))
+    import data_parallel
+    rank, local, world = data_parallel.world_info()
+    if world == 1:
+        local = args.gpu_id
     torch.cuda.set_device(local)
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group('nccl')
-    env = envs.make(args.env, seed=None if args.seed is None else args.seed + rank)
-    network = Network.create_network(config=args, input_shape=DQNAgent.get_input_shape(env, args),
+    data_parallel.init(device=torch.device('cuda', local))
+    env = envs.make(args.env, seed=data_parallel.shard_seed(args.seed, rank))
+    input_shape = DQNAgent.get_input_shape(env, args)
+    if args.precision == 'bf16' and len(input_shape) != 3:
+        args.precision = 'fp32'                       # vector observations: nothing for the tensor cores to do
+    network = Network.create_network(config=args, input_shape=input_shape,
                                      num_actions=env.action_space.n, num_replicas=world)
-    if world > 1:
-        import torch.distributed as dist
-        flat = network.flat_buffer('online')
-        dist.broadcast(flat, 0)                       # chief initialises, the others copy (main.py:133-143)
-        network.sync_target()
-        network.set_hyper(args, grad_scale=1.0 / world)
+    # chief initialises, the others copy (main.py:133-143); mean-of-gradients scaling; exchange set-up
+    data_parallel.setup_network(network, args, mode=args.dp)
     replay_memory = ReplayMemory(args.replay_memory_capacity, trusted=True)
     agent = DQNAgent(env, network, Session(), replay_memory, args, enable_summary=(rank == 0))
     agent.train(args.num_episodes, args.max_steps_per_episode, _Supervisor())
     if world > 1:
         import torch.distributed as dist
+        agent._graphs.clear()                         # graphs that hold NCCL kernels go before the communicator
+        torch.cuda.synchronize()
+        dist.barrier()
         dist.destroy_process_group()
 
 
 if __name__ == '__main__':
     args = parse_args()
-    logging.getLogger().setLevel(args.log_level)
+    logging.basicConfig(level=args.log_level, format='%(asctime)s %(levelname)s %(message)s')
     if args.job == 'ps':
         logging.warning('parameter servers are not used by the B200 path (NCCL data parallelism); exiting')
         sys.exit(0)

@@ -284,8 +284,31 @@ class Network(object):
             raise RuntimeError('checkpoint is for %s with %d actions' % (z['arch'], int(z['num_actions'])))
         for which in ('online', 'target', 'slot0', 'slot1'):
             self.set_params([z['%s_%d' % (which, i)] for i in range(self.num_tensors)], which=which)
+        # a connected data-parallel net realigns its exchange flags with the restored step: every rank loads at the
+        # same point, with no update in flight anywhere
+        if self.peers_connected:
+            import torch
+            import torch.distributed as dist
+            torch.cuda.synchronize()
+            dist.barrier()
         _c.check(_c.lib.dqn_net_set_global_step(self._h, int(z['global_step'])), 'load')
+        if self.peers_connected:
+            dist.barrier()
         return {k[6:]: z[k].item() for k in z.files if k.startswith('extra_')}
+
+    def refresh_operands(self, which='online'):
+        """After an in-place write to ``flat_buffer('online'/'target')`` (e.g. a broadcast): rebuilds the bf16 operand
+        copies the tensor-core kernels read.  No-op in fp32 mode."""
+        _c.check(_c.lib.dqn_net_refresh_operands(self._h, _c.BUF[which], _c.current_stream()), 'refresh_operands')
+
+    def broadcast_parameters(self, src=0):
+        """Rank ``src`` initialises, everyone else copies (the reference's chief / non-chief start-up,
+        main.py:133-143); the target network starts as a copy of the online one (dqn_agent.py:50)."""
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            dist.broadcast(self.flat_buffer('online'), src)
+            self.refresh_operands('online')
+        self.sync_target()
 
     # ------------------------------------------------------------------ data parallel over NVLink peer memory
     def connect_peers(self):
@@ -303,7 +326,16 @@ class Network(object):
         _c.check(_c.lib.dqn_net_dp_connect(self._h, rank, world, blob), 'connect_peers')
         self.set_hyper(self.config, grad_scale=1.0 / world)
         self.peers_connected = True
+        torch.cuda.synchronize()
         dist.barrier()
+
+    def dp_status(self):
+        """Raises if a peer-exchange wait of this rank ever timed out (a peer stalled longer than the timeout set with
+        ``DQN_DP_TIMEOUT_S`` / dqn_net_dp_set_timeout, default 120 s): the weights are then no longer in sync."""
+        s = _c.c_i64()
+        _c.check(_c.lib.dqn_net_dp_status(self._h, _c.C.byref(s), _c.current_stream()), 'dp_status')
+        if s.value:
+            raise RuntimeError('data-parallel exchange timed out waiting for a peer at update %d' % s.value)
 
     def dp_train_on_batch(self, batch, want_loss=False):
         k = batch.actions.numel()

@@ -170,7 +170,9 @@ int dqn_net_download(dqn_net_t h, int32_t which, float* host, int64_t floats);
  * and resets the update counter (global_step, network.py:83). */
 int dqn_net_set_hyper(dqn_net_t h, const dqn_hyper_t* hyper, int32_t reset_slots);
 int dqn_net_global_step(dqn_net_t h, int64_t* step, dqn_stream_t stream); /* synchronises the stream */
-/* Restores the update counter when resuming from a checkpoint (the Supervisor restored global_step, main.py:136-143). */
+/* Restores the update counter when resuming from a checkpoint (the Supervisor restored global_step, main.py:136-143).
+ * On a connected data-parallel net it also realigns this rank's exchange flags to `step`: every rank must call it at
+ * the same point with no dqn_net_dp_step in flight anywhere (barrier before and after). */
 int dqn_net_set_global_step(dqn_net_t h, int64_t step);
 /* Arithmetic of the conv / fully-connected GEMMs (north_star's two modes; no reference counterpart, TF ran fp32):
  * 0 = fp32 on CUDA cores, the parity mode (<= 1e-4 vs the oracle);
@@ -206,13 +208,19 @@ int dqn_net_apply(dqn_net_t h, dqn_stream_t stream);
  * every rank publishes its local mean gradient in a double-buffered exchange block that all ranks of the NVLink
  * domain have mapped (CUDA IPC), raises a per-rank flag with a system-scope release store, and the optimizer kernel
  * of every rank waits for all flags and sums the N gradients with peer loads in rank order (bit-identical weights on
- * all ranks) -- no separate all-reduce launch.  A dead peer makes the waiting kernel trap after a few seconds
- * instead of hanging.  Set hyper.grad_scale = 1/world.  2 <= world <= 8, one process per GPU.
+ * all ranks) -- no separate all-reduce launch.  Set hyper.grad_scale = 1/world.  2 <= world <= 8, one process per GPU.
  *   dqn_net_dp_handle : 64-byte IPC handle of this rank's exchange block (all-gather it across ranks)
  *   dqn_net_dp_connect: maps the peers' blocks; handles = world x 64 bytes in rank order
- *   dqn_net_dp_step   : dqn_net_train_step across ranks; every rank must call it the same number of times */
+ *   dqn_net_dp_step   : dqn_net_train_step across ranks; every rank must call it the same number of times
+ * Skew between ranks: a rank's kernels wait for the peers' flags for at most the time set with
+ * dqn_net_dp_set_timeout (default 120 s, or the environment variable DQN_DP_TIMEOUT_S read by dqn_net_dp_handle /
+ * dqn_net_dp_connect).  When the wait expires nothing traps: the step number is recorded, the update goes on with
+ * whatever the exchange buffers hold, and dqn_net_dp_status returns that step (0 = every wait so far was answered) so
+ * that the host can stop or fall back to dqn_net_backward + all-reduce + dqn_net_apply. */
 int dqn_net_dp_handle(dqn_net_t h, void* out_handle64);
 int dqn_net_dp_connect(dqn_net_t h, int32_t rank, int32_t world, const void* handles);
+int dqn_net_dp_set_timeout(dqn_net_t h, double seconds);
+int dqn_net_dp_status(dqn_net_t h, int64_t* timed_out_step, dqn_stream_t stream); /* synchronises the stream */
 int dqn_net_dp_step(dqn_net_t h, const void* d_states, const void* d_next_states, const int32_t* d_actions,
                     const double* d_rewards, const uint8_t* d_terminals, int32_t k, float* d_loss, dqn_stream_t stream);
 /* dqn_train_step (gather + update) across ranks. */
@@ -221,6 +229,12 @@ int dqn_train_step_dp(dqn_net_t net, dqn_replay_t replay, const int32_t* d_logic
 
 /* DQNAgent._update_target_network's assigns (dqn_agent.py:215-222, network.py:251-252): one D2D copy. */
 int dqn_net_target_sync(dqn_net_t h, dqn_stream_t stream);
+/* bf16 mode keeps pre-swizzled bf16 operand copies of the weights beside the fp32 master buffers; dqn_net_upload, the
+ * optimizer and dqn_net_target_sync keep them current.  Anything else that writes a DQN_BUF_ONLINE / DQN_BUF_TARGET
+ * buffer in place through dqn_net_buffer -- the start-up broadcast of rank 0's parameters (the reference's chief
+ * initialises and the others wait, main.py:133-143) -- must call this afterwards (which = the buffer written).
+ * A no-op in fp32 mode. */
+int dqn_net_refresh_operands(dqn_net_t h, int32_t which, dqn_stream_t stream);
 
 /* Sample-to-update in one call: gather from the ring (d_logical_idx as in dqn_replay_gather) into the
  * net's own staging buffers, then dqn_net_train_step.  This is the unit bench.py times. */
@@ -254,7 +268,8 @@ int dqn_preproc_run(dqn_preproc_t h, const uint8_t* d_rgb, int32_t n, uint8_t* d
  *   - at most 64 states per call; a larger n is refused with DQN_ERR_INVALID and a message saying so.
  *   - the array occupies about 1.27 MB on every GPU that loads the library, until the process exits.
  *   - the first call on each device looks the array's address up (cudaGetSymbolAddress on the current
- *     device); make that first call outside of any stream capture.
+ *     device); make that first call outside of any stream capture, and from one host thread at a time
+ *     (two first calls on the same device must not race).
  *   - every call on a device uses the same array, and the array keeps whatever the previous call left
  *     in it (every element a call reads is written earlier in the same call, so nothing needs
  *     clearing).  Two calls whose kernels can overlap on the GPU -- different streams without an
@@ -275,6 +290,8 @@ int dqn_net_set_timing(dqn_net_t h, int32_t enable);
 /* Synchronises the device and adds the last step's per-kernel durations to the totals. */
 int dqn_net_timing_collect(dqn_net_t h);
 int dqn_net_timing_read(dqn_net_t h, int32_t stage, double* total_ms, int32_t* count);
+/* The same event bracket around an empty kernel (microseconds, mean of 20): the floor to subtract from the above. */
+int dqn_net_timing_floor(dqn_net_t h, dqn_stream_t stream, double* us);
 const char* dqn_stage_name(int32_t stage); /* "" beyond the last stage */
 
 #ifdef __cplusplus

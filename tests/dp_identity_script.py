@@ -1,4 +1,7 @@
-"""Run under torchrun (one rank per GPU): N-rank data-parallel step == 1-rank step on the concatenated batch."""
+"""Run under torchrun (one rank per GPU): an N-rank data-parallel update == a 1-rank update on the concatenated batch
+(reference semantics: mean of the N replica gradients, one apply -- src/network.py:187-192), in both arithmetic modes,
+through both exchanges (NCCL all-reduce; peer memory fused into the step's kernels, fed from each rank's own replay ring),
+starting from DIFFERENT per-rank initial weights that the start-up broadcast must overwrite."""
 import os
 import sys
 
@@ -10,75 +13,96 @@ for p in (ROOT, os.path.join(ROOT, "dist-dqn_b200"), os.path.join(ROOT, "tests")
         sys.path.insert(0, p)
 
 
+def _ring_from_batch(replay_memory, batch, local):
+    s, a, r, s2, t = batch
+    rm = replay_memory.ReplayMemory(4 * len(a), device=local)
+    for i in range(len(a)):
+        rm.add(s[i], int(a[i]), float(r[i]), s2[i], bool(t[i]))
+    return rm
+
+
+def check_mode(precision, torch, dist, dp, network, replay_memory, helpers, rank, local, world):
+    make_batch, make_config, oracle_params, rel_err, to_device_batch = helpers
+    arch, ishape, A, B, steps = "cnn", (84, 84, 4), 6, 8, 3
+    tol = 2e-5 if precision == "fp32" else 2e-3
+    cfg = make_config(network=arch, minibatch_size=B * world, max_batch=B * world, device_index=local, precision=precision,
+                      seed=100 + rank)                                 # every rank starts from different weights
+    params = oracle_params(arch, ishape, A, 31)
+    batches = [make_batch(ishape, A, B, 700 + 10 * i + rank) for i in range(steps)]
+    gathered = [None] * world
+    dist.all_gather_object(gathered, batches)
+
+    def fresh(mode):
+        net = network.Network.create_network(cfg, ishape, A, num_replicas=world)
+        if rank == 0:
+            net.set_params(params)
+        dp.setup_network(net, cfg, mode=mode)                          # broadcast (+ bf16 operand refresh), 1/world, peers
+        return net
+
+    # single-rank reference on the concatenated batches (rank 0 only)
+    ref_params = None
+    if rank == 0:
+        ref = network.Network.create_network(cfg, ishape, A)
+        ref.set_params(params)
+        ref.sync_target()
+        for i in range(steps):
+            cat = [np.concatenate([g[i][j] for g in gathered]) for j in range(5)]
+            ref.train_on_batch(to_device_batch(ref, *cat))
+        torch.cuda.synchronize()
+        ref_params = ref.get_params()
+
+    ok = True
+    flats = {}
+    for mode in ("nccl", "peer"):
+        net = fresh(mode)
+        rings = [_ring_from_batch(replay_memory, b, local) for b in batches]
+        idx = torch.arange(B, dtype=torch.int32, device=net.device)
+        for i in range(steps):
+            dp.train_step(net, rings[i], B, idx)                       # ring -> gather -> update (dqn_train_step_dp for 'peer')
+        torch.cuda.synchronize()
+        if mode == "peer":
+            net.dp_status()
+        flat = net.flat_buffer("online").clone()
+        flats[mode] = flat
+        ref0 = flat.clone()
+        dist.broadcast(ref0, 0)
+        same = bool(torch.equal(flat, ref0))                           # bit-identical weights on every rank
+        q = net.predict(batches[0][0])                                 # runs on the refreshed bf16 operand images
+        q0 = q.clone()
+        dist.broadcast(q0, 0)
+        same_q = bool(torch.equal(q, q0))
+        err = 0.0
+        if rank == 0:
+            err = max(rel_err(a, b) for a, b in zip(net.get_params(), ref_params))
+            print("%s %s: %d-rank x %d steps vs 1 rank on the concatenated batches: max rel err %.3g (tol %g); identical "
+                  "weights %s, identical Q %s" % (precision, mode, world, steps, err, tol, same, same_q))
+        ok = ok and same and same_q and err < tol
+    perr = float(((flats["peer"] - flats["nccl"]).abs().max() / flats["nccl"].abs().max()).item())
+    if rank == 0:
+        print("%s: peer exchange vs NCCL exchange, max rel err %.3g" % (precision, perr))
+    return ok and perr < tol
+
+
 def main():
     import torch
     import torch.distributed as dist
     import data_parallel as dp
     import network
+    import replay_memory
     from gpu_helpers import make_batch, make_config, oracle_params, rel_err, to_device_batch
     rank, local, world = dp.world_info()
     torch.cuda.set_device(local)
     dp.init(device=torch.device("cuda", local))
-    arch, ishape, A, B = "cnn", (84, 84, 4), 6, 8
-    cfg = make_config(network=arch, minibatch_size=B * world, max_batch=B * world, device_index=local)
-    net = network.Network.create_network(cfg, ishape, A, num_replicas=world)
-    params = oracle_params(arch, ishape, A, 31)
-    if rank == 0:
-        net.set_params(params)
-    dp.broadcast_parameters(net.flat_buffer("online"))
-    net.sync_target()
-    net.set_hyper(cfg, grad_scale=dp.grad_scale(world))
-    batch = make_batch(ishape, A, B, 700 + rank)
-    net.backward_on_batch(to_device_batch(net, *batch))
-    dp.sync_gradients(net.flat_buffer("grad"))
-    net.apply_gradients()
-    torch.cuda.synchronize()
-    got = net.get_params()
-    gathered = [None] * world
-    dist.all_gather_object(gathered, batch)
+    helpers = (make_batch, make_config, oracle_params, rel_err, to_device_batch)
     ok = True
-    if rank == 0:
-        ref = network.Network.create_network(cfg, ishape, A)
-        ref.set_params(params)
-        ref.sync_target()
-        cat = [np.concatenate([g[i] for g in gathered]) for i in range(5)]
-        ref.train_on_batch(to_device_batch(ref, *cat))
-        torch.cuda.synchronize()
-        errs = [rel_err(a, b) for a, b in zip(got, ref.get_params())]
-        print("dp identity max rel err", max(errs))
-        ok = max(errs) < 2e-5
-    # same step again through the peer-memory path (gradient exchange fused into the optimizer kernel)
-    pnet = network.Network.create_network(cfg, ishape, A, num_replicas=world)
-    if rank == 0:
-        pnet.set_params(params)
-    dp.broadcast_parameters(pnet.flat_buffer("online"))
-    pnet.sync_target()
-    pnet.connect_peers()
-    for _ in range(3):                                   # several steps: exercises the double buffering / flags
-        pnet.dp_train_on_batch(to_device_batch(pnet, *batch))
-    torch.cuda.synchronize()
-    for _ in range(2):
-        net.backward_on_batch(to_device_batch(net, *batch))
-        dp.sync_gradients(net.flat_buffer("grad"))
-        net.apply_gradients()
-    torch.cuda.synchronize()
-    perr = max(rel_err(a, b) for a, b in zip(pnet.get_params(), net.get_params()))
-    if rank == 0:
-        print("peer path vs NCCL path after 3 steps, max rel err", perr)
-    ok = ok and perr < 2e-5
-    pflat = pnet.flat_buffer("online").clone()
-    p0 = pflat.clone()
-    dist.broadcast(p0, 0)
-    ok = ok and bool(torch.equal(pflat, p0))
-    # all ranks must hold identical weights afterwards
-    flat = net.flat_buffer("online").clone()
-    ref0 = flat.clone()
-    dist.broadcast(ref0, 0)
-    same = bool(torch.equal(flat, ref0))
+    for precision in ("fp32", "bf16"):
+        ok = check_mode(precision, torch, dist, dp, network, replay_memory, helpers, rank, local, world) and ok
+    t = torch.tensor([0 if ok else 1], device="cuda")
+    dist.all_reduce(t)
     dist.barrier()
     dist.destroy_process_group()
-    if not (ok and same):
-        print("FAILED ok=%s same=%s" % (ok, same))
+    if t.item() != 0:
+        print("FAILED on some rank")
         sys.exit(1)
     if rank == 0:
         print("DP_IDENTITY_OK")

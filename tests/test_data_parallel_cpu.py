@@ -67,3 +67,85 @@ def test_shard_seed_and_scale():
     import data_parallel as dp
     assert dp.grad_scale(8) == 0.125 and dp.shard_seed(None, 3) is None
     assert len({dp.shard_seed(7, r) for r in range(8)}) == 8
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Agent loop under data parallelism: ranks whose episodes have different lengths must still make the SAME number of
+# gradient exchanges (a synchronous exchange hangs otherwise).  The network / replay memory are stand-ins; the exchange
+# is a gloo all-reduce, which blocks for ever if one rank makes fewer calls than the other.
+def _agent_worker(rank, world, port, out_q):
+    os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1",
+                      MASTER_PORT=str(port))
+    for p in (ROOT, PKG):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import argparse
+    import tempfile
+    import torch.distributed as dist
+    import data_parallel as dp
+    import envs
+    dp.init(backend="gloo")
+    from dqn_agent import DQNAgent
+
+    class FakeNet(object):
+        peers_connected = False
+
+        def sync_target(self):
+            pass
+
+        def predict(self, states, argmax=False):
+            return None, torch.zeros(1, dtype=torch.int32)
+
+    class FakeReplay(object):
+        def __init__(self):
+            self.n = 0
+
+        def add(self, *a, **k):
+            self.n += 1
+
+        def size(self):
+            return self.n
+
+        def sample_indices(self, k):
+            return list(range(k))
+
+    class Agent(DQNAgent):
+        exchanges = 0
+
+        def _device_step(self, k, indices, want_loss):
+            t = torch.ones(1)
+            dist.all_reduce(t)                         # the gradient exchange: needs every rank
+            assert t.item() == world
+            self.exchanges += 1
+            return t
+
+    cfg = argparse.Namespace(
+        minibatch_size=8, frames_per_state=1, resize_width=0, resize_height=0, update_freq=1, replay_start_size=0,
+        init_random_action_prob=0.5, min_random_action_prob=0.1, random_action_explore_steps=100, target_update_freq=7,
+        summary_freq=0, logdir=tempfile.mkdtemp(prefix="dqn_dp_agent_"), cuda_graph=False, dp_stop_window=5)
+    # rank 0: short episodes, rank 1: long ones -> very different update counts per episode loop
+    env = envs.CartPoleEnv(seed=rank, max_steps=6 if rank == 0 else 40)
+    agent = Agent(env, FakeNet(), None, FakeReplay(), cfg, enable_summary=False)
+    assert agent.replay_memory.size() >= cfg.minibatch_size          # the prefill covers one minibatch in data-parallel mode
+    agent.train(num_episodes=4, max_steps_per_episode=50)
+    counts = [None] * world
+    dist.all_gather_object(counts, (agent.exchanges, agent.training_steps))
+    if rank == 0:
+        out_q.put(counts)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_agent_loops_of_unequal_length_make_the_same_number_of_exchanges():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31500 + (os.getpid() % 2000)
+    procs = [ctx.Process(target=_agent_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    counts = q.get(timeout=180)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert counts[0] == counts[1] and counts[0][0] == counts[0][1] > 0, counts
+    assert counts[0][0] % 5 == 0                        # everyone left at a check-in (window of 5 updates)

@@ -33,7 +33,7 @@ def _cos(a, b):
     return float(a @ b / (np.linalg.norm(a) * np.linalg.norm(b) + 1e-300))
 
 
-@pytest.mark.parametrize("A,B", [(6, 5), (4, 37), (6, 130)])
+@pytest.mark.parametrize("A,B", [(6, 5), (4, 37), (6, 130), (6, 512)])     # 512: the large-batch template instances (fc NTILE=256)
 def test_bf16_forward(A, B):
     from oracle import net_ref as N
     net, cfg = _net(A, B)
@@ -50,7 +50,7 @@ def test_bf16_forward(A, B):
     assert rel_err(qt, N.forward(ARCH, [p * 0.5 for p in params], s, ISHAPE)) < TOL
 
 
-@pytest.mark.parametrize("A,B", [(6, 5), (6, 70)])
+@pytest.mark.parametrize("A,B", [(6, 5), (6, 70), (6, 512)])     # 512: fc dgrad NTILE=256, conv1 wgrad with several tiles per CTA
 def test_bf16_loss_and_gradients(A, B):
     from oracle import net_ref as N
     net, cfg = _net(A, B)
@@ -77,7 +77,40 @@ def test_bf16_loss_and_gradients(A, B):
     assert min(cos_x) > 0.99, cos_x
 
 
-@pytest.mark.parametrize("A,B", [(6, 5), (4, 32), (4, 70)])
+@pytest.mark.parametrize("A,B", [(6, 48), (4, 512)])
+def test_bf16_gradients_with_non_terminal_transitions(A, B):
+    """The TD path in bf16: ~70% of the transitions bootstrap from the target network (y = r + gamma * max_a Q_target(s')),
+    with a target network that differs from the online one.  Checked against the oracle that rounds where the kernels
+    round, with its own bf16-restated target Q-values."""
+    from oracle import net_ref as N
+    net, cfg = _net(A, B)
+    params = oracle_params(ARCH, ISHAPE, A, 41)
+    tparams = [p * 0.75 for p in oracle_params(ARCH, ISHAPE, A, 42)]
+    net.set_params(params)
+    net.set_params(tparams, which="target")
+    s, a, r, s2, t = make_batch(ISHAPE, A, B, 43)                       # default: 30% terminal, 70% non-terminal
+    assert 0 < t.sum() < B
+    # rewards well above the bf16 noise of a Q-value, so the TD error is not a difference of two noisy numbers
+    r = np.random.default_rng(44).uniform(-2000.0, 2000.0, B).astype(np.float32).astype(np.float64)
+
+    def targets(bf16):
+        qt = N.forward(ARCH, tparams, s2, ISHAPE, bf16=bf16)
+        y = r + cfg.reward_discount * qt.max(axis=1) * (1 - t)          # python float64, then the float32 placeholder
+        return y.astype(np.float32).astype(np.float64)
+    loss, q = net.backward_on_batch(to_device_batch(net, s, a, r, s2, t), want_loss=True, want_q=True, include_reg=True)
+    grads = net.get_grads()
+    loss_x, q_x, g_x = N.loss_and_grads(ARCH, params, s, targets(False), a, cfg.reg_param, ISHAPE)
+    loss_b, q_b, g_b = N.loss_and_grads(ARCH, params, s, targets(True), a, cfg.reg_param, ISHAPE, bf16=True)
+    assert rel_err(q.cpu().numpy(), q_x) < TOL and rel_err(q.cpu().numpy(), q_b) < 2e-3
+    assert abs(float(loss.item()) - loss_x) <= TOL * abs(loss_x)
+    errs_b = [rel_err(g, e) for g, e in zip(grads, g_b)]
+    cos_x = [_cos(g, e) for g, e in zip(grads, g_x)]
+    print("bf16 TD-path grads vs bf16-restated oracle:", ["%.5f" % e for e in errs_b])
+    assert max(errs_b) < TOL, errs_b
+    assert min(cos_x) > 0.99, cos_x
+
+
+@pytest.mark.parametrize("A,B", [(6, 5), (4, 32), (4, 70), (4, 512)])     # 512: fc forward NTILE=256
 def test_bf16_nature_architecture(A, B):
     """The Nature-paper variant (VALID convs, no pooling, fc 512; north_star's 'Nature-DQN convs and FC-512') on the same
     tensor-core kernels: forward, loss and every gradient tensor against both oracles."""
