@@ -15,6 +15,7 @@
 #include "gemm_core.cuh"
 #include "umma_core.cuh"
 #include "fc_fused.cuh"
+#include "conv1_s2d.cuh"
 
 #include <cmath>
 #include <cstdlib>
@@ -172,6 +173,7 @@ struct Seg {
   __nv_bfloat16* wt;      // [N][K]            (forward)
   __nv_bfloat16* wd;      // [CIN][taps][N]    (dgrad), may be null
   int K, N, CIN;
+  int kperm;              // conv1 in the space-to-depth formulation: the image's reduction index is s2d::kperm(k)
 };
 constexpr int MAX_SEGS = 6;
 struct OptArgs {
@@ -379,7 +381,8 @@ __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs a) {
       __align__(16) __nv_bfloat16 c8[8];
 #pragma unroll
       for (int e = 0; e < 8; ++e) c8[e] = wtile[e][threadIdx.x];
-      *reinterpret_cast<uint4*>(s.wt + umma::img_index(n, k, s.N)) = *reinterpret_cast<const uint4*>(c8);   // thread < 32: k = 8*kt
+      // thread < 32: k = 8*kt (kperm keeps runs of 8 consecutive reduction indices together)
+      *reinterpret_cast<uint4*>(s.wt + umma::img_index(n, s.kperm ? umma::s2d::kperm(k) : k, s.N)) = *reinterpret_cast<const uint4*>(c8);
     }
     if (s.wd) {
       const int t = k / s.CIN, c = k - t * s.CIN;
@@ -498,7 +501,7 @@ __global__ void fill_kernel(float* p, long long n, float v) {
 // bf16 copies of one layer's weights for the tensor-core path: wt[n][k] (forward: B operand, K-major) and
 // wd[c][(ky,kx,n)] (dgrad), both stored as swizzled stage images (umma::img_index) so that a stage's tile is one
 // contiguous bulk copy.  w is the fp32 master in TF layout [k=(ky,kx,c)][n].
-struct CvtLayer { const float* w; __nv_bfloat16* wt; __nv_bfloat16* wd; int K, N, CIN; };
+struct CvtLayer { const float* w; __nv_bfloat16* wt; __nv_bfloat16* wd; int K, N, CIN, kperm; };
 struct CvtArgs { CvtLayer l[4]; };
 __global__ void __launch_bounds__(256) weights_to_bf16_kernel(CvtArgs a) {
   const CvtLayer L = a.l[blockIdx.y];
@@ -506,7 +509,7 @@ __global__ void __launch_bounds__(256) weights_to_bf16_kernel(CvtArgs a) {
   if (i >= L.K * L.N) return;
   const int k = i / L.N, n = i - k * L.N;
   const __nv_bfloat16 v = __float2bfloat16_rn(L.w[i]);
-  L.wt[umma::img_index(n, k, L.N)] = v;
+  L.wt[umma::img_index(n, L.kperm ? umma::s2d::kperm(k) : k, L.N)] = v;
   if (L.wd) {
     const int t = k / L.CIN, c = k - t * L.CIN;
     L.wd[umma::img_index(c, t * L.N + n, L.CIN)] = v;
@@ -701,6 +704,8 @@ struct dqn_net_s {
   cudaStream_t side3 = nullptr;                     // head weight gradient + loss (fused fc/TD path)
   bool no_resident = false;                         // DQN_NO_RESIDENT=1: im2col gathers from L2 instead of a shared-memory resident input block
   bool no_fused_fc = true;                          // DQN_FUSED_FC=1: fc forward / TD head / fc dgrad as one launch (experimental)
+  bool conv1_s2d = false;                           // reference conv net, bf16: conv1 forward / weight gradient in the space-to-depth formulation
+  bool fuse_gather = true;                          // ... reading the frames straight from the replay ring in dqn_train_step (DQN_NO_FUSED_GATHER=1: off)
   cudaEvent_t ev_fork[3] = {}, ev_join = nullptr, ev_x = nullptr, ev_join2 = nullptr, ev_head = nullptr;
   // bf16 tensor-core mode (precision == 1; DQN_ARCH_CNN only)
   int precision = 0;
@@ -857,6 +862,7 @@ extern "C" int dqn_net_create(dqn_net_t* out, int32_t arch, const int32_t* in_sh
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->side3, cudaStreamNonBlocking);
     { const char* nr = getenv("DQN_NO_RESIDENT"); h->no_resident = nr && nr[0] == '1'; }
     { const char* nf = getenv("DQN_FUSED_FC"); h->no_fused_fc = !(nf && nf[0] == '1'); }
+    { const char* ng = getenv("DQN_NO_FUSED_GATHER"); h->fuse_gather = !(ng && ng[0] == '1'); }
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_head, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_x, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_join2, cudaEventDisableTiming);
@@ -1129,6 +1135,48 @@ static void launch_fwd_res_u8(umma::FwdArgsT a, int npass, int num_sms, cudaStre
   dim3 grid((unsigned)((total + per - 1) / per), 1, 1);
   launch_pdl(umma::umma_fwd_res_u8_kernel<G, NTILE>, grid, dim3(umma::TT), smem, st, 1, a);
 }
+// conv1 in the space-to-depth formulation (conv1_s2d.cuh): persistent, one CTA per SM
+static void launch_conv1_s2d_fwd(dqn_net_s* h, const umma::s2d::Src& src, const int pass_id[2], int npass, int B, cudaStream_t st) {
+  namespace S = umma::s2d;
+  static bool once = (set_smem(S::conv1_s2d_fwd_kernel<false>, S::FWD_SMEM), set_smem(S::conv1_s2d_fwd_kernel<true>, S::FWD_SMEM), true);
+  (void)once;
+  S::FwdArgs a;
+  a.src = src;
+  a.B = B;
+  a.npass = npass;
+  for (int p = 0; p < 2; ++p) {
+    const int id = pass_id[p < npass ? p : 0];
+    const float* params = id == 0 ? h->online : h->target;
+    a.wt[p] = h->wt_bf[id] + h->wt_off[0];
+    a.bias[p] = params + h->tensors[1].off;
+    a.out[p] = h->act_bf[id][0];
+    a.arg[p] = h->arg[id][0];
+  }
+  int grid = npass == 2 ? (h->num_sms & ~1) : h->num_sms;
+  if (grid > npass * B) grid = npass * B;
+  if (src.x[0]) launch_pdl(S::conv1_s2d_fwd_kernel<false>, dim3(grid), dim3(S::NWARPS * 32), S::FWD_SMEM, st, 1, a);
+  else launch_pdl(S::conv1_s2d_fwd_kernel<true>, dim3(grid), dim3(S::NWARPS * 32), S::FWD_SMEM, st, 1, a);
+}
+
+static void launch_conv1_s2d_wgrad(dqn_net_s* h, const umma::s2d::Src& src, int B, cudaStream_t st, int* nsplit_out) {
+  namespace S = umma::s2d;
+  static bool once = (set_smem(S::conv1_s2d_wgrad_kernel<false>, S::WG_SMEM), set_smem(S::conv1_s2d_wgrad_kernel<true>, S::WG_SMEM), true);
+  (void)once;
+  S::WgradArgs a;
+  a.src = src;
+  a.dactg = h->dact_bf[0];
+  a.arg = h->arg[0][0];
+  a.partial = h->L[0].partial;
+  a.B = B;
+  const int grid = B < h->num_sms ? B : h->num_sms;
+  {
+    StageScope sc(h, DQN_STAGE_WGRAD_CONV1, st);
+    if (src.x[0]) launch_pdl(S::conv1_s2d_wgrad_kernel<false>, dim3(grid), dim3(S::NWARPS * 32), S::WG_SMEM, st, 1, a);
+    else launch_pdl(S::conv1_s2d_wgrad_kernel<true>, dim3(grid), dim3(S::NWARPS * 32), S::WG_SMEM, st, 1, a);
+  }
+  *nsplit_out = grid;
+}
+
 // Ring depth: a grid of at most one CTA per SM is latency-bound (deep ring, loads far ahead of the MMAs); a grid of
 // several waves wants two CTAs resident per SM (small ring).  (Splitting the reduction of a tile over a cluster with a
 // DSMEM reduction was measured slower at B=32: the cluster launch and its two cluster barriers cost more than the
@@ -1238,6 +1286,7 @@ static int refresh_bf16_weights(dqn_net_s* h, int set, cudaStream_t st) {
     c.l[l].wd = (set == 0 && l >= 1) ? h->wd_bf + h->wd_off[l] : nullptr;
     c.l[l].K = L.K; c.l[l].N = L.N;
     c.l[l].CIN = l == 0 ? 4 : (l == 1 ? 32 : (l == 2 ? 64 : L.K));
+    c.l[l].kperm = (l == 0 && h->conv1_s2d) ? 1 : 0;
     maxn = L.K * L.N > maxn ? L.K * L.N : maxn;
   }
   dim3 grid((maxn + 255) / 256, 4);
@@ -1247,9 +1296,22 @@ static int refresh_bf16_weights(dqn_net_s* h, int set, cudaStream_t st) {
   return 0;
 }
 
+static umma::s2d::Src stack_src(const void* x0, const void* x1) {
+  umma::s2d::Src s;
+  memset(&s, 0, sizeof(s));
+  s.x[0] = static_cast<const uint8_t*>(x0);
+  s.x[1] = static_cast<const uint8_t*>(x1);
+  return s;
+}
+
 static int run_trunk_tc(dqn_net_s* h, int npass, const void* const x[2], const int pass_id[2], int B, cudaStream_t st,
-                        int nlayers = 4) {
+                        int nlayers = 4, const umma::s2d::Src* ring = nullptr) {
   for (int l = 0; l < nlayers; ++l) {
+    if (l == 0 && h->conv1_s2d) {
+      StageScope sc(h, DQN_STAGE_FWD_CONV1, st);
+      launch_conv1_s2d_fwd(h, ring ? *ring : stack_src(x[0], x[npass == 2 ? 1 : 0]), pass_id, npass, B, st);
+      continue;
+    }
     umma::FwdArgsT a;
     a.B = B;
     a.npass = npass;
@@ -1310,7 +1372,7 @@ static void fill_segs(dqn_net_s* h, OptArgs* o, const int nsplit[4], bool from_f
     for (int i = 0; i < 3; ++i) {
       const Tensor& w = h->tensors[2 * i];
       const Tensor& b = h->tensors[2 * i + 1];
-      o->seg[i] = Seg{(long long)w.off, (int)(w.numel + b.numel), (int)w.numel, h->grad + w.off, 1, 0, nullptr, nullptr, 0, 0, 0};
+      o->seg[i] = Seg{(long long)w.off, (int)(w.numel + b.numel), (int)w.numel, h->grad + w.off, 1, 0, nullptr, nullptr, 0, 0, 0, 0};
     }
   } else {
     o->nseg = 5;
@@ -1318,19 +1380,20 @@ static void fill_segs(dqn_net_s* h, OptArgs* o, const int nsplit[4], bool from_f
       const Tensor& w = h->tensors[2 * l];
       const GemmLayer& L = h->L[l];
       Seg s{(long long)w.off, L.K * L.N + L.N, l == 3 ? L.K * L.N : 0, L.partial, nsplit[l], (long long)(L.K + 1) * L.N,
-            nullptr, nullptr, 0, 0, 0};
+            nullptr, nullptr, 0, 0, 0, 0};
       if (from_flat_grad) { s.partial = h->grad + w.off; s.nsplit = 1; s.stride = 0; }
       if (h->precision == 1) {
         s.wt = h->wt_bf[0] + h->wt_off[l];
         s.wd = l >= 1 ? h->wd_bf + h->wd_off[l] : nullptr;
         s.K = L.K; s.N = L.N;
         s.CIN = l == 0 ? 4 : (l == 1 ? 32 : (l == 2 ? 64 : L.K));
+        s.kperm = (l == 0 && h->conv1_s2d) ? 1 : 0;
       }
       o->seg[l] = s;
     }
     const Tensor& w5 = h->tensors[8];
     Seg s{(long long)w5.off, (h->F + 1) * h->A, h->F * h->A, h->head_partial, h->head_nsplit,
-          (long long)(h->F + 1) * h->A, nullptr, nullptr, 0, 0, 0};
+          (long long)(h->F + 1) * h->A, nullptr, nullptr, 0, 0, 0, 0};
     if (from_flat_grad) { s.partial = h->grad + w5.off; s.nsplit = 1; s.stride = 0; }
     o->seg[4] = s;
   }
@@ -1390,10 +1453,12 @@ extern "C" int dqn_net_forward(dqn_net_t h, int32_t which, const void* d_x, int3
 }
 
 // Forward of both nets + TD + full backward.  mode 0: fused optimizer; 1: materialise flat gradient.
+// ring != null (conv1_s2d only): the conv1 kernels read the frames of the sampled transitions from the replay ring
+// themselves and the forward kernel writes actions / rewards / terminals (d_states / d_next are not used).
 static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, const int32_t* d_actions,
                     const double* d_rewards, const uint8_t* d_term, int k, float* d_loss, float* d_q, int mode,
-                    int include_reg, cudaStream_t st) {
-  DQN_REQUIRE(d_states && d_next && d_actions && d_rewards && d_term, DQN_ERR_INVALID, "train: NULL batch pointer");
+                    int include_reg, cudaStream_t st, const umma::s2d::Src* ring = nullptr) {
+  DQN_REQUIRE((ring || (d_states && d_next)) && d_actions && d_rewards && d_term, DQN_ERR_INVALID, "train: NULL batch pointer");
   DQN_REQUIRE(k >= 1 && k <= h->MB, DQN_ERR_INVALID, "train: minibatch %d outside [1, max_batch=%d]", k, h->MB);
   int nsplit[4] = {1, 1, 1, 1};
   OptArgs oa;
@@ -1436,7 +1501,7 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
     const int ids[2] = {0, 1};
     // reference architecture in tensor-core mode: fc forward (both nets) + head + TD + fc data gradient are one kernel
     const bool fused = h->precision == 1 && !nat && h->F == umma::FCF && h->A <= umma::FC_AP && !h->no_fused_fc;
-    int rc = h->precision == 1 ? run_trunk_tc(h, 2, xs, ids, k, st, fused ? 3 : 4) : run_trunk(h, 2, xs, ps, ids, k, st);
+    int rc = h->precision == 1 ? run_trunk_tc(h, 2, xs, ids, k, st, fused ? 3 : 4, ring) : run_trunk(h, 2, xs, ps, ids, k, st);
     if (rc) return rc;
     const float* w5 = h->online + h->tensors[8].off;
     cudaStream_t sd = h->side;
@@ -1542,7 +1607,8 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       if (early_exchange()) return DQN_ERR_CUDA;
       if (fork_after_dgrad(2)) return DQN_ERR_CUDA;
       launch_wgrad_tc<C2, __nv_bfloat16, 64>(h, 1, h->act_bf[0][0], k, sd, &nsplit[1]); if (h->no_resident) launch_dgrad_tc<C2, 32>(h, 1, k, st); else launch_dgrad_res<C2, 32, 4, 1>(h, 1, k, st);
-      if (h->no_resident) launch_wgrad_tc<C1, uint8_t, 32>(h, 0, d_states, k, st, &nsplit[0]);
+      if (h->conv1_s2d) launch_conv1_s2d_wgrad(h, ring ? *ring : stack_src(d_states, nullptr), k, st, &nsplit[0]);
+      else if (h->no_resident) launch_wgrad_tc<C1, uint8_t, 32>(h, 0, d_states, k, st, &nsplit[0]);
       else launch_wgrad_res_u8<C1>(h, d_states, k, st, &nsplit[0]);
     } else if (nat) {
       launch_wgrad<NF, float>(h, 3, h->act[0][2], k, sh, &nsplit[3]); launch_dgrad<NF>(h, 3, k, st);
@@ -1654,6 +1720,30 @@ extern "C" int dqn_net_target_sync(dqn_net_t h, dqn_stream_t stream) {
   return 0;
 }
 
+// Sample-to-update.  Reference conv net in bf16 mode: no gather launch -- the conv1 kernels fetch the frames of the
+// sampled transitions from the ring themselves (4 bulk copies per stack) and the forward kernel copies the scalars.
+// Everything else: gather into the net's staging buffers, then the step.
+static int step_from_ring(dqn_net_s* net, dqn_replay_t replay, const int32_t* d_idx, int k, float* d_loss, int mode, cudaStream_t st) {
+  RingView rv;
+  dqn_replay_view_(replay, &rv);
+  if (net->conv1_s2d && net->fuse_gather && rv.frames_per_state == 4 && rv.elem_bytes == 1 &&
+      rv.frame_bytes == (int)umma::s2d::FRAME_BYTES) {
+    int rc = dqn_replay_flush(replay, st);                  // frames / records staged on the host go to the ring first
+    if (rc) return rc;
+    umma::s2d::Src src;
+    memset(&src, 0, sizeof(src));
+    src.frames = rv.frames; src.meta = rv.meta; src.ring_state = rv.state; src.idx = d_idx;
+    src.capacity = rv.capacity; src.frame_capacity = rv.frame_capacity; src.pitch = rv.pitch;
+    src.actions = net->st_actions; src.rewards = net->st_rewards; src.terminals = net->st_term;
+    return run_step(net, nullptr, nullptr, net->st_actions, net->st_rewards, net->st_term, k, d_loss, nullptr, mode, 0, st, &src);
+  }
+  if (net->timing) cudaEventRecord(net->ev0[DQN_STAGE_GATHER], st);
+  int rc = dqn_replay_gather(replay, d_idx, k, net->st_states, net->st_next, net->st_actions, net->st_rewards, net->st_term, st);
+  if (net->timing) { cudaEventRecord(net->ev1[DQN_STAGE_GATHER], st); net->stage_used[DQN_STAGE_GATHER] = true; }
+  if (rc) return rc;
+  return run_step(net, net->st_states, net->st_next, net->st_actions, net->st_rewards, net->st_term, k, d_loss, nullptr, mode, 0, st);
+}
+
 extern "C" int dqn_net_refresh_operands(dqn_net_t h, int32_t which, dqn_stream_t stream) {
   DQN_REQUIRE(h, DQN_ERR_INVALID, "refresh_operands: NULL handle");
   DQN_REQUIRE(which == DQN_BUF_ONLINE || which == DQN_BUF_TARGET, DQN_ERR_INVALID, "refresh_operands: which must be online or target");
@@ -1672,16 +1762,7 @@ extern "C" int dqn_train_step(dqn_net_t net, dqn_replay_t replay, const int32_t*
   DQN_REQUIRE((size_t)rv.frame_bytes * rv.frames_per_state == net->state_bytes, DQN_ERR_INVALID,
               "replay stacks are %d bytes but the net expects %zu", rv.frame_bytes * rv.frames_per_state, net->state_bytes);
   DeviceGuard g(net->device);
-  int rc;
-  {
-    if (net->timing) cudaEventRecord(net->ev0[DQN_STAGE_GATHER], static_cast<cudaStream_t>(stream));
-    rc = dqn_replay_gather(replay, d_logical_idx, k, net->st_states, net->st_next, net->st_actions, net->st_rewards,
-                           net->st_term, stream);
-    if (net->timing) { cudaEventRecord(net->ev1[DQN_STAGE_GATHER], static_cast<cudaStream_t>(stream)); net->stage_used[DQN_STAGE_GATHER] = true; }
-  }
-  if (rc) return rc;
-  return run_step(net, net->st_states, net->st_next, net->st_actions, net->st_rewards, net->st_term, k, d_loss, nullptr, 0,
-                  0, static_cast<cudaStream_t>(stream));
+  return step_from_ring(net, replay, d_logical_idx, k, d_loss, 0, static_cast<cudaStream_t>(stream));
 }
 
 // ---------------------------------------------------------------------------------------------- peer-memory data parallelism
@@ -1754,11 +1835,7 @@ extern "C" int dqn_train_step_dp(dqn_net_t net, dqn_replay_t replay, const int32
   DQN_REQUIRE(net->dp_world >= 2 && net->dp_peer_flags_dev, DQN_ERR_STATE, "dqn_train_step_dp: call dqn_net_dp_connect first");
   DQN_REQUIRE(dqn_replay_device_(replay) == net->device, DQN_ERR_INVALID, "replay and net live on different devices");
   DeviceGuard g(net->device);
-  int rc = dqn_replay_gather(replay, d_logical_idx, k, net->st_states, net->st_next, net->st_actions, net->st_rewards,
-                             net->st_term, stream);
-  if (rc) return rc;
-  return run_step(net, net->st_states, net->st_next, net->st_actions, net->st_rewards, net->st_term, k, d_loss, nullptr, 2,
-                  0, static_cast<cudaStream_t>(stream));
+  return step_from_ring(net, replay, d_logical_idx, k, d_loss, 2, static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int dqn_net_dp_set_timeout(dqn_net_t h, double seconds) {
@@ -1800,12 +1877,14 @@ extern "C" int dqn_net_set_precision(dqn_net_t h, int32_t precision) {
       for (int l = 0; l < 4; ++l) NET_ALLOC(h->dact_bf[l], (size_t)h->MB * h->L[l].out_elems * 2);
     }
     h->precision = 1;
+    h->conv1_s2d = h->arch == DQN_ARCH_CNN && !h->no_resident;
     int rc = refresh_bf16_weights(h, 0, nullptr);
     if (!rc) rc = refresh_bf16_weights(h, 1, nullptr);
     if (rc) return rc;
     DQN_CUDA(cudaDeviceSynchronize());
   } else {
     h->precision = 0;
+    h->conv1_s2d = false;
   }
   return 0;
 }
