@@ -319,12 +319,31 @@ def _timed_steps(torch, dist, world, rank, local, dev, step, warmup, steps, afte
     return max(per_rank), per_rank, clocks
 
 
-def _kernel_times(torch, c, net, run_one, nprof=30):
-    """us per launch of every kernel of a step, from an instrumented eager pass (CUDA events around every launch)."""
+def _kernel_times(torch, c, net, run_one, nprof=30, stream=None, prepare=None):
+    """us per launch of every kernel of a step: the step is captured into a CUDA graph with a CUDA-event record node on
+    either side of every kernel, and the graph is replayed `nprof` times on fresh inputs (`prepare(i)`).  The events
+    stamp each kernel as it runs inside the graph, so a bracket holds neither host launch latency nor the neighbours'
+    overlap.  (stream=None: eager launches bracketed by ordinary event records -- several microseconds of launch
+    latency per bracket.)"""
     c.check(c.lib.dqn_net_set_timing(net.handle, 2))
-    for i in range(nprof):
-        run_one(i)
-        c.check(c.lib.dqn_net_timing_collect(net.handle))
+    if stream is not None:
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=stream):
+            run_one(0)
+            c.check(c.lib.dqn_net_timing_floor_enqueue(net.handle, c.current_stream()))
+        c.check(c.lib.dqn_net_set_timing(net.handle, 3))
+        for i in range(nprof):
+            if prepare is not None:
+                prepare(i)
+            g.replay()
+            c.check(c.lib.dqn_net_timing_collect(net.handle))
+        del g
+    else:
+        for i in range(nprof):
+            if prepare is not None:
+                prepare(i)
+            run_one(i)
+            c.check(c.lib.dqn_net_timing_collect(net.handle))
     c.check(c.lib.dqn_net_set_timing(net.handle, 0))
     kernels = {}
     tot, cnt = c.c_f64(), c.c_i32()
@@ -337,6 +356,8 @@ def _kernel_times(torch, c, net, run_one, nprof=30):
         if cnt.value:
             kernels[name.decode()] = tot.value / cnt.value * 1e3
         s += 1
+    if "launch_floor" in kernels:                     # in-graph brackets: the floor was measured inside the same graph
+        return kernels, kernels.pop("launch_floor")
     floor = c.c_f64()
     c.check(c.lib.dqn_net_timing_floor(net.handle, c.current_stream(), c.C.byref(floor)))
     return kernels, floor.value
@@ -466,10 +487,8 @@ def run_update_bench(args, torch, dist, dp, rank, local, world, dev):
         samples_per_s = world * batch * steps / (ms_total / 1e3)
 
         # ---- per-kernel durations (instrumented eager pass over fresh indices) -> roofline of the dominant kernel
-        def prof_one(i):
-            d_idx.copy_(idx_table[(warmup + i) % total_steps])
-            eager_step()
-        kernels, floor_us = _kernel_times(torch, c, net, prof_one)
+        kernels, floor_us = _kernel_times(torch, c, net, lambda i: eager_step(), stream=None if args.no_graph else side,
+                                          prepare=lambda i: d_idx.copy_(idx_table[(warmup + i) % total_steps]))
         roof = roofline(kernels, args.arch, batch, net.flat_size, floor_us)
 
         # ---- the same at the large batch (config 3's per-GPU batch), where the GEMM kernels are no longer latency-bound
@@ -565,15 +584,14 @@ def large_batch_block(args, torch, c, network, rm, dev, side, batch=512, steps=1
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / steps
 
-    def prof_one(i):
-        d_idx.copy_(tab[i % (steps + 13)])
-        net.train_step(rm, batch, d_indices=d_idx)
-    kernels, floor_us = _kernel_times(torch, c, net, prof_one, nprof=20)
+    kernels, floor_us = _kernel_times(torch, c, net, lambda i: net.train_step(rm, batch, d_indices=d_idx), nprof=20, stream=side,
+                                      prepare=lambda i: d_idx.copy_(tab[i % (steps + 13)]))
     roof = roofline(kernels, args.arch, batch, net.flat_size, floor_us)
     flops = 2.0 * batch * (4 * sum(MACS[args.arch]) - MACS[args.arch][0])    # fwd x2 + wgrad + dgrad (no conv1 dgrad)
     del g, net
     return roof, {"minibatch": batch, "value": 1e3 / ms, "unit": "updates/s", "ms_per_step": ms, "steps": steps,
-                  "samples_per_s": batch * 1e3 / ms, "step_tflops": flops / (ms * 1e-3) / 1e12, "kernels_us": kernels}
+                  "samples_per_s": batch * 1e3 / ms, "step_tflops": flops / (ms * 1e-3) / 1e12, "kernels_us": kernels,
+                  "event_floor_us": floor_us}
 
 
 # ----------------------------------------------------------------------------------------------- other configs
@@ -842,8 +860,8 @@ def _traffic(name, batch):
 
 def roofline(kernels, arch, batch, nparams, floor_us=0.0):
     """Roofline of the dominant kernel of the step (largest average duration on the critical path).  Durations come
-    from CUDA-event brackets in an eager pass; `floor_us` (the same bracket around an empty launch, measured in the
-    same run) is subtracted."""
+    from CUDA-event brackets (see _kernel_times); `floor_us` (the same bracket around an empty launch) is subtracted for
+    eager brackets and 0 for in-graph ones."""
     if not kernels:
         return None
     hbm, burst, sustained, src = peaks()

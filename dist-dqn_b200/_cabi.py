@@ -85,6 +85,7 @@ SIGNATURES = {
     "dqn_net_timing_collect": (C.c_int, [c_vp]),
     "dqn_net_timing_read": (C.c_int, [c_vp, c_i32, C.POINTER(c_f64), C.POINTER(c_i32)]),
     "dqn_net_timing_floor": (C.c_int, [c_vp, c_vp, C.POINTER(c_f64)]),
+    "dqn_net_timing_floor_enqueue": (C.c_int, [c_vp, c_vp]),
     "dqn_stage_name": (C.c_char_p, [c_i32]),
 }
 

@@ -109,7 +109,7 @@ enum {
   DQN_STAGE_TD_HEAD, DQN_STAGE_HEAD_WGRAD, DQN_STAGE_LOSS, DQN_STAGE_WGRAD_FC, DQN_STAGE_DGRAD_FC,
   DQN_STAGE_WGRAD_CONV3, DQN_STAGE_DGRAD_CONV3, DQN_STAGE_WGRAD_CONV2, DQN_STAGE_DGRAD_CONV2, DQN_STAGE_WGRAD_CONV1,
   DQN_STAGE_REDUCE_GRAD, DQN_STAGE_OPTIMIZER, DQN_STAGE_MLP_BACKWARD, DQN_STAGE_MLP_FORWARD, DQN_STAGE_HEAD_FORWARD,
-  DQN_STAGE_FC_TD_FUSED,
+  DQN_STAGE_FC_TD_FUSED, DQN_STAGE_LAUNCH_FLOOR,
   DQN_NUM_STAGES
 };
 

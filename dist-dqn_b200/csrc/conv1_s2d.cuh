@@ -26,6 +26,8 @@
 // Weight-gradient kernel: the same image read MN-major (the reduction runs over the pool windows), the routed output
 // gradient as B operand, accumulation in TMEM over all samples of the CTA, one partial per CTA.
 #pragma once
+#include <cuda_fp16.h>
+
 #include "umma_core.cuh"
 
 namespace dqn {
@@ -40,7 +42,7 @@ constexpr uint32_t STACK_BYTES = 4 * FRAME_BYTES;      // 28224
 constexpr uint32_t RAW_BYTES = 28 * 1024;              // raw ring slot
 constexpr int UNITS = 84 * 21;                         // 16-byte source units per stack (4 pixels x 4 frames)
 constexpr uint32_t W_BYTES = 256 * 32 * 2;             // conv1 weight image, 16 KB
-constexpr int NWARPS = 16;
+constexpr int NWARPS = 16;                           // weight-gradient kernel (the forward kernel has FWD_WARPS)
 
 __host__ __device__ constexpr int img_row(int Y, int X) { return (Y & 1) * PLANE_Y + (X & 1) * PLANE_X + (Y >> 1) * PW + (X >> 1); }
 // reduction index of the permuted conv1 weight image for the reference index k = (ky*8 + kx)*4 + f
@@ -69,27 +71,57 @@ struct Src {
 
 struct RingRec { int64_t state_pos, next_pos; double reward; int32_t action; uint8_t terminal; uint8_t pad[3]; };
 
-// one elected thread: start the copy of sample b's stack into `dst`; completion (STACK_BYTES) is counted on `bar`
-__device__ __forceinline__ void load_stack(const Src& s, int pass, int b, uint32_t dst, uint64_t* bar) {
+// Ring mode: where the 4 frames of sample b's stack (pass 0: state, pass 1: next state) start in the frame ring.  The
+// look-up is a chain of dependent global loads (index -> record -> positions), so a whole warp resolves up to 64 tiles
+// at once into a shared-memory table ahead of the copy loop.  Pass 0 also copies the transition's scalars.
+__device__ __forceinline__ void resolve_stack(const Src& s, int pass, int b, int64_t off[4]) {
+  int64_t slot = s.ring_state[0] + (int64_t)s.idx[b];
+  if (slot >= s.capacity) slot -= s.capacity;
+  const RingRec* r = static_cast<const RingRec*>(s.meta) + slot;
+  const int64_t pos = pass ? r->next_pos : r->state_pos;
+#pragma unroll
+  for (int f = 0; f < 4; ++f) off[f] = ((pos - 3 + f) % s.frame_capacity) * (int64_t)s.pitch;
+  if (pass == 0) {
+    if (s.actions) s.actions[b] = r->action;
+    if (s.rewards) s.rewards[b] = r->reward;
+    if (s.terminals) s.terminals[b] = r->terminal;
+  }
+}
+constexpr int TAB_TILES = 64;
+
+// one elected thread: start the copy of a stack into `dst`; completion (STACK_BYTES) is counted on `bar`
+__device__ __forceinline__ void load_stack(const Src& s, int pass, int b, const int64_t* tab_entry, uint32_t dst, uint64_t* bar) {
   mbar_expect_tx(bar, STACK_BYTES);
   const uint8_t* x = pass ? s.x[1] : s.x[0];
   if (x) {
     bulk_g2s(dst, x + (size_t)b * STACK_BYTES, STACK_BYTES, bar);
     return;
   }
-  int64_t slot = s.ring_state[0] + (int64_t)s.idx[b];
-  if (slot >= s.capacity) slot -= s.capacity;
-  const RingRec* r = static_cast<const RingRec*>(s.meta) + slot;
-  const int64_t pos = pass ? r->next_pos : r->state_pos;
 #pragma unroll
-  for (int f = 0; f < 4; ++f) {
-    const int64_t fs = (pos - 3 + f) % s.frame_capacity;
-    bulk_g2s(dst + f * FRAME_BYTES, s.frames + fs * (int64_t)s.pitch, FRAME_BYTES, bar);
-  }
-  if (pass == 0) {
-    if (s.actions) s.actions[b] = r->action;
-    if (s.rewards) s.rewards[b] = r->reward;
-    if (s.terminals) s.terminals[b] = r->terminal;
+  for (int f = 0; f < 4; ++f) bulk_g2s(dst + f * FRAME_BYTES, s.frames + tab_entry[f], FRAME_BYTES, bar);
+}
+
+// The producer warp's loop: every lane resolves tiles of the next table round, then one elected lane issues the copies.
+// slot_of(i) / wait_empty(i) are supplied by the kernel (raw ring slot and its "empty" wait of tile i).
+template <class FDst, class FWait, class FBar>
+__device__ __forceinline__ void producer_loop(const Src& s, int pass, int b0, int bstep, int ntiles, int64_t (*tab)[4], FDst dst_of,
+                                              FWait wait_empty, FBar bar_of) {
+  const int lane = threadIdx.x & 31;
+  const bool ring = (pass ? s.x[1] : s.x[0]) == nullptr;
+  for (int base = 0; base < ntiles; base += TAB_TILES) {
+    const int n = min(TAB_TILES, ntiles - base);
+    if (ring) {
+      for (int t = lane; t < n; t += 32) resolve_stack(s, pass, b0 + (base + t) * bstep, tab[t]);
+    }
+    __syncwarp();
+    if (elect_one()) {
+      for (int t = 0; t < n; ++t) {
+        const int i = base + t;
+        wait_empty(i);
+        load_stack(s, pass, b0 + i * bstep, tab[t], dst_of(i), bar_of(i));
+      }
+    }
+    __syncwarp();
   }
 }
 
@@ -101,50 +133,139 @@ __device__ __forceinline__ uint4 interleave4(uint32_t a, uint32_t b, uint32_t c,
                     __byte_perm(ab_hi, cd_hi, 0x7632));
 }
 
-// Builder threads (nb of them, this one is bt): widen the raw stack and scatter it into the image.  PLANAR: the raw
-// slot holds 4 frames back to back (ring mode) instead of the HWC stack.
-template <bool PLANAR>
-__device__ __forceinline__ void build_image(const uint8_t* raw, uint8_t* img, int bt, int nb) {
-#pragma unroll 2
-  for (int u = bt; u < UNITS; u += nb) {
-    uint4 v;
-    if constexpr (PLANAR) {
-      const uint32_t* p = reinterpret_cast<const uint32_t*>(raw) + u;
-      v = interleave4(p[0], p[FRAME_BYTES / 4], p[2 * (FRAME_BYTES / 4)], p[3 * (FRAME_BYTES / 4)]);
-    } else {
-      v = reinterpret_cast<const uint4*>(raw)[u];
+// uint8 -> f16 without the (slow) integer conversion instruction: byte n next to the byte 0x64 is the f16 number
+// 1024 + n (0x6400 is 1024.0 and its ulp is 1); one packed subtraction leaves n, exactly.  One byte permute and one
+// HSUB2 per PAIR of values.
+__device__ __forceinline__ uint32_t f16x2_from_bytes(uint32_t w, uint32_t sel) {
+  const uint32_t biased = __byte_perm(w, 0x64646464u, sel);
+  const __half2 d = __hsub2(*reinterpret_cast<const __half2*>(&biased), __half2half2(__ushort_as_half((unsigned short)0x6400)));
+  return *reinterpret_cast<const uint32_t*>(&d);
+}
+__device__ __forceinline__ uint4 f16x8_from_u8(uint32_t w0, uint32_t w1) {        // 2 pixels x 4 frames, HWC order
+  return make_uint4(f16x2_from_bytes(w0, 0x4140), f16x2_from_bytes(w0, 0x4342), f16x2_from_bytes(w1, 0x4140),
+                    f16x2_from_bytes(w1, 0x4342));
+}
+
+constexpr int BUILD_THREADS = 336;      // 21 source columns x 16 row phases
+
+// Builder thread bt (< BUILD_THREADS) owns source column j = bt % 21 (16 bytes: 4 pixels x 4 frames) of the rows
+// r0 + 16k: the position inside the super-pixel (yy, chunk) and the plane are then fixed per thread and the image row
+// advances by 22 per step, so the address arithmetic is a handful of instructions per 16 source bytes.  PLANAR: the raw
+// slot holds 4 frames back to back (ring mode) instead of the HWC stack.  F16: the image holds IEEE halves (forward:
+// f16 x f16 MMAs), else bf16 (weight gradient: the other operand is a bf16 gradient); exact either way.
+template <bool PLANAR, bool F16>
+__device__ __forceinline__ void build_image(const uint8_t* raw, uint8_t* img, int bt) {
+  if (bt >= BUILD_THREADS) return;
+  const int r0 = bt / 21, j = bt - r0 * 21;
+  const int yy = (r0 + 2) & 3, Y0 = (r0 + 2) >> 2;
+  const int rbase = (Y0 & 1) * PLANE_Y + (Y0 >> 1) * PW;
+  const int ra0 = rbase + (j & 1) * PLANE_X + (j >> 1);               // super-pixel X = j:   pixels xx = 2,3 -> chunk 2*yy+1
+  const int rb0 = rbase + ((j + 1) & 1) * PLANE_X + ((j + 1) >> 1);   // super-pixel X = j+1: pixels xx = 0,1 -> chunk 2*yy
+  const int u0 = r0 * 21 + j;
+  uint4 v[6];
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {
+    if (k < 5 || r0 < 4) {
+      if constexpr (PLANAR) {
+        const uint32_t* p = reinterpret_cast<const uint32_t*>(raw) + u0 + 336 * k;
+        v[k] = make_uint4(p[0], p[FRAME_BYTES / 4], p[2 * (FRAME_BYTES / 4)], p[3 * (FRAME_BYTES / 4)]);
+      } else {
+        v[k] = reinterpret_cast<const uint4*>(raw)[u0 + 336 * k];
+      }
     }
-    const int iy = u / 21, j = u - iy * 21;
-    const int Y = (iy + 2) >> 2, yy = (iy + 2) & 3;
-    const int rbase = (Y & 1) * PLANE_Y + (Y >> 1) * PW;
-    const int ra = rbase + (j & 1) * PLANE_X + (j >> 1);               // super-pixel X = j:   pixels xx = 2,3 -> chunk 2*yy+1
-    const int rb = rbase + ((j + 1) & 1) * PLANE_X + ((j + 1) >> 1);   // super-pixel X = j+1: pixels xx = 0,1 -> chunk 2*yy
-    *reinterpret_cast<uint4*>(img + ra * 128 + (((2 * yy + 1) ^ (ra & 7)) << 4)) = widen_u8x8(make_uint2(v.x, v.y));
-    *reinterpret_cast<uint4*>(img + rb * 128 + (((2 * yy) ^ (rb & 7)) << 4)) = widen_u8x8(make_uint2(v.z, v.w));
+  }
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {
+    if (k < 5 || r0 < 4) {
+      const int ra = ra0 + 22 * k, rb = rb0 + 22 * k;
+      uint4 lo, hi;
+      if constexpr (PLANAR && F16) {
+        // v = 4 pixels of frames a, b, c, d: pair the frames first, then convert each pair
+        const uint32_t ab01 = __byte_perm(v[k].x, v[k].y, 0x5140), ab23 = __byte_perm(v[k].x, v[k].y, 0x7362);
+        const uint32_t cd01 = __byte_perm(v[k].z, v[k].w, 0x5140), cd23 = __byte_perm(v[k].z, v[k].w, 0x7362);
+        lo = make_uint4(f16x2_from_bytes(ab01, 0x4140), f16x2_from_bytes(cd01, 0x4140), f16x2_from_bytes(ab01, 0x4342),
+                        f16x2_from_bytes(cd01, 0x4342));
+        hi = make_uint4(f16x2_from_bytes(ab23, 0x4140), f16x2_from_bytes(cd23, 0x4140), f16x2_from_bytes(ab23, 0x4342),
+                        f16x2_from_bytes(cd23, 0x4342));
+      } else {
+        const uint4 w = PLANAR ? interleave4(v[k].x, v[k].y, v[k].z, v[k].w) : v[k];
+        if constexpr (F16) {
+          lo = f16x8_from_u8(w.x, w.y);
+          hi = f16x8_from_u8(w.z, w.w);
+        } else {
+          lo = widen_u8x8(make_uint2(w.x, w.y));
+          hi = widen_u8x8(make_uint2(w.z, w.w));
+        }
+      }
+      *reinterpret_cast<uint4*>(img + ra * 128 + (((2 * yy + 1) ^ (ra & 7)) << 4)) = lo;
+      *reinterpret_cast<uint4*>(img + rb * 128 + (((2 * yy) ^ (rb & 7)) << 4)) = hi;
+    }
   }
 }
 
 // ------------------------------------------------------------------------------------------------ forward
 struct FwdArgs {
   Src src;
-  const __nv_bfloat16* wt[2];   // k-permuted weight images (kperm): 4 taps x [32 rows][64] SWIZZLE_128B
+  const __nv_bfloat16* wt[2];   // k-permuted F16 weight images (kperm): 4 taps x [32 rows][64] SWIZZLE_128B
   const float* bias[2];
   __nv_bfloat16* out[2];        // pooled activation [B][121][32]
   uint8_t* arg[2];              // pool arg-max [B][121][32] (may be null)
   int B, npass;
+  unsigned long long* trace;    // debugging (DQN_S2D_TRACE=1): CTA 0 stamps clock64() per tile and pipeline event; else null
 };
+__device__ __forceinline__ void trace_stamp(unsigned long long* trace, int tile, int ev) {
+  if (trace && blockIdx.x == 0 && tile < 60) trace[tile * 8 + ev] = (unsigned long long)clock64();
+}
+// per-CTA wall-clock stamps (ns): trace[480 + 4*cta + ev], ev 0 = entry, 1 = set-up done, 2 = past the PDL wait, 3 = exit
+__device__ __forceinline__ void trace_cta(unsigned long long* trace, int ev) {
+  if (trace && blockIdx.x < 160) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    trace[480 + 4 * blockIdx.x + ev] = t;
+  }
+}
 
 constexpr uint32_t FWD_OFF_IMG = 2 * RAW_BYTES, FWD_OFF_W = FWD_OFF_IMG + 2 * IMG_BYTES;
 constexpr uint32_t FWD_SMEM = SMEM_SLACK + FWD_OFF_W + W_BYTES;        // 205,824 bytes
-constexpr int FWD_BUILD_WARP0 = 6, FWD_BUILD_WARPS = NWARPS - FWD_BUILD_WARP0;
+constexpr int FWD_EPI_WARPS = 8;                       // two per TMEM lane quarter: 16 of the 32 channels each
+constexpr int FWD_BUILD_WARP0 = 2 + FWD_EPI_WARPS, FWD_BUILD_WARPS = 11, FWD_WARPS = FWD_BUILD_WARP0 + FWD_BUILD_WARPS;   // 21 warps
+static_assert(FWD_BUILD_WARPS * 32 >= BUILD_THREADS, "not enough builder threads");
+
+// instruction descriptor with the operand formats chosen separately (0 = f16, 1 = bf16), fp32 accumulation
+__host__ __device__ constexpr uint32_t make_idesc_ab(int M, int N, bool a_mn_major, bool b_mn_major, bool a_bf16, bool b_bf16) {
+  return (1u << 4) | ((a_bf16 ? 1u : 0u) << 7) | ((b_bf16 ? 1u : 0u) << 10) | ((a_mn_major ? 1u : 0u) << 15) |
+         ((b_mn_major ? 1u : 0u) << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+// 16 consecutive accumulator columns of this thread's TMEM lane; the caller issues tcgen05.wait::ld before using them
+__device__ __forceinline__ void tmem_ld16_nowait(uint32_t taddr, uint32_t r[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float v[16]) {
+  uint32_t r[16];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
 
 template <bool PLANAR>
-__global__ void __launch_bounds__(NWARPS * 32, 1) conv1_s2d_fwd_kernel(FwdArgs a) {
+__global__ void __launch_bounds__(FWD_WARPS * 32, 1) conv1_s2d_fwd_kernel(FwdArgs a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align_smem(smem_raw);
   __shared__ uint64_t raw_full[2], raw_empty[2], img_full[2], img_empty[2], acc_full[2], acc_empty[2], wbar;
   __shared__ uint32_t tmem_slot;
   __shared__ float bias_sm[32];
+  __shared__ int64_t tab[TAB_TILES][4];
   const int tid = threadIdx.x, lane = tid & 31;
   const int warp = warp_uniform_idx();
   // tile = (pass, sample); a CTA stays on one pass so that it needs one set of weights
@@ -152,6 +273,7 @@ __global__ void __launch_bounds__(NWARPS * 32, 1) conv1_s2d_fwd_kernel(FwdArgs a
   const int pass = a.npass == 2 ? (int)(blockIdx.x & 1) : 0;
   const int b0 = a.npass == 2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
   const int ntiles = b0 < a.B ? (a.B - b0 + nper - 1) / nper : 0;
+  if (tid == 0) trace_cta(a.trace, 0);
   if (tid == 0) {
 #pragma unroll
     for (int i = 0; i < 2; ++i) {
@@ -160,14 +282,14 @@ __global__ void __launch_bounds__(NWARPS * 32, 1) conv1_s2d_fwd_kernel(FwdArgs a
       mbar_init(&img_full[i], FWD_BUILD_WARPS);
       mbar_init(&img_empty[i], 1);
       mbar_init(&acc_full[i], 1);
-      mbar_init(&acc_empty[i], 4);
+      mbar_init(&acc_empty[i], FWD_EPI_WARPS);
     }
     mbar_init(&wbar, 1);
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc(&tmem_slot, 256);                 // two sets of four 128x32 fp32 accumulators
   // the padding of the images (border super-pixels, rows between the planes) is never written again: zero it once
-  for (int i = tid; i < (int)(2 * IMG_BYTES / 16); i += NWARPS * 32)
+  for (int i = tid; i < (int)(2 * IMG_BYTES / 16); i += FWD_WARPS * 32)
     reinterpret_cast<uint4*>(smem + FWD_OFF_IMG)[i] = make_uint4(0u, 0u, 0u, 0u);
   fence_async_proxy();
   tc_fence_before();
@@ -175,24 +297,27 @@ __global__ void __launch_bounds__(NWARPS * 32, 1) conv1_s2d_fwd_kernel(FwdArgs a
   tc_fence_after();
   const uint32_t tmem = tmem_slot;
   const uint32_t sbase = smem_u32(smem);
-  pdl_wait_then_trigger();                                    // everything above overlapped the previous kernel
-  if (tid < 32) bias_sm[tid] = __ldg((pass ? a.bias[1] : a.bias[0]) + tid);
-  __syncthreads();
+  if (tid == 0) trace_cta(a.trace, 1);
+  pdl_wait();                                                 // everything above overlapped the previous kernel
+  // the grid never exceeds one CTA per SM and a CTA owns its SM's shared memory, so the successor's CTAs can only
+  // start where one of ours has exited: let it launch now, its launch latency and set-up hide under our tail
+  pdl_trigger();
+  if (tid == 0) trace_cta(a.trace, 2);
   if (warp == 0) {
     // ---------------------------------------------------------------- producer
     if (elect_one()) {
       mbar_expect_tx(&wbar, W_BYTES);
       bulk_g2s(sbase + FWD_OFF_W, pass ? a.wt[1] : a.wt[0], W_BYTES, &wbar);
-      for (int i = 0; i < ntiles; ++i) {
-        const int rb = i & 1;
-        mbar_wait(&raw_empty[rb], ((i >> 1) & 1) ^ 1);
-        load_stack(a.src, pass, b0 + i * nper, sbase + rb * RAW_BYTES, &raw_full[rb]);
-      }
     }
     __syncwarp();
+    producer_loop(
+        a.src, pass, b0, nper, ntiles, tab, [&](int i) { return sbase + (i & 1) * RAW_BYTES; },
+        [&](int i) { mbar_wait(&raw_empty[i & 1], ((i >> 1) & 1) ^ 1); trace_stamp(a.trace, i, 0); },
+        [&](int i) { return &raw_full[i & 1]; });
   } else if (warp == 1) {
-    // ---------------------------------------------------------------- MMA issuer
-    constexpr uint32_t idesc = make_idesc(TM, 32, false, false);
+    // ---------------------------------------------------------------- MMA issuer (f16 image x f16 weights: the two
+    // operands of a kind::f16 MMA must share one format -- f16 x bf16 is an illegal instruction)
+    constexpr uint32_t idesc = make_idesc_ab(TM, 32, false, false, false, false);
     mbar_wait(&wbar, 0);
     for (int i = 0; i < ntiles; ++i) {
       const int ib = i & 1, ph = (i >> 1) & 1;
@@ -200,6 +325,7 @@ __global__ void __launch_bounds__(NWARPS * 32, 1) conv1_s2d_fwd_kernel(FwdArgs a
       mbar_wait(&acc_empty[ib], ph ^ 1);
       tc_fence_after();
       if (elect_one()) {
+        trace_stamp(a.trace, i, 4);
         const uint32_t img = sbase + FWD_OFF_IMG + ib * IMG_BYTES;
         const uint64_t bd0 = make_desc_sw128(sbase + FWD_OFF_W);
 #pragma unroll
@@ -216,14 +342,21 @@ __global__ void __launch_bounds__(NWARPS * 32, 1) conv1_s2d_fwd_kernel(FwdArgs a
         }
         mma_commit(&img_empty[ib]);
         mma_commit(&acc_full[ib]);
+        trace_stamp(a.trace, i, 5);
       }
       __syncwarp();
     }
   } else if (warp < FWD_BUILD_WARP0) {
-    // ---------------------------------------------------------------- epilogue (TMEM lane quarter = warp & 3)
-    const int q = warp & 3, m = 32 * q + lane;
+    // ---------------------------------------------------------------- epilogue: TMEM lane quarter = warp & 3, channel
+    // half h = (warp - 2) >> 2 (16 of the 32 output channels)
+    if (warp == 2) bias_sm[lane] = __ldg((pass ? a.bias[1] : a.bias[0]) + lane);
+    asm volatile("bar.sync 1, %0;" ::"n"(FWD_EPI_WARPS * 32) : "memory");            // the epilogue warps
+    const int q = warp & 3, h = (warp - 2) >> 2, m = 32 * q + lane;
     const int py = m / PW, px = m - py * PW;
     const bool valid = m < NWIN;
+    float bias[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) bias[j] = bias_sm[h * 16 + j];
     __nv_bfloat16* outp = pass ? a.out[1] : a.out[0];
     uint8_t* argp = pass ? a.arg[1] : a.arg[0];
     for (int i = 0; i < ntiles; ++i) {
@@ -231,45 +364,49 @@ __global__ void __launch_bounds__(NWARPS * 32, 1) conv1_s2d_fwd_kernel(FwdArgs a
       const int b = b0 + i * nper;
       mbar_wait(&acc_full[ib], ph);
       tc_fence_after();
-      uint32_t key[32];
+      if (tid == 64) trace_stamp(a.trace, i, 6);
+      // all four window positions' accumulators first (their TMEM latencies overlap), one wait, then the TMEM set goes back
+      uint32_t r[4][16];
 #pragma unroll
-      for (int j = 0; j < 32; ++j) key[j] = 0u;
-#pragma unroll
-      for (int w = 0; w < 4; ++w) {
-        float v[32];
-        tmem_ld32(tmem + ((uint32_t)(32 * q) << 16) + ib * 128 + w * 32, v);
-        // window position (wy, wx) lies inside the 21x21 conv output unless it is the pool's padding row / column
-        const bool in = valid && ((w >> 1) == 0 || py < PW - 1) && ((w & 1) == 0 || px < PW - 1);
-        // values are >= 0 after ReLU, so their float bits order like unsigned integers: (value with the 2 lowest
-        // mantissa bits replaced by 3-w) is a key whose maximum is the largest value, first window position on ties
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const uint32_t kj = in ? ((__float_as_uint(fmaxf(v[j] + bias_sm[j], 0.f)) & ~3u) | (3u - (uint32_t)w)) : 0u;
-          key[j] = max(key[j], kj);
-        }
-      }
-      // the accumulators are in registers: hand the TMEM set back before the global stores
+      for (int w = 0; w < 4; ++w) tmem_ld16_nowait(tmem + ((uint32_t)(32 * q) << 16) + ib * 128 + w * 32 + h * 16, r[w]);
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[ib]);
-      if (valid) {
-        const size_t off = ((size_t)b * NWIN + m) * 32;
-        uint32_t pk[16];
+      // A value's float bits, taken as a SIGNED integer, order like the value for values >= 0 and put every negative
+      // value below them; with the 2 lowest mantissa bits replaced by 3-w the maximum over the window positions is the
+      // largest value (first position on ties) whenever the pooled ReLU output is positive, and negative otherwise.
+      int key[16];
 #pragma unroll
-        for (int j = 0; j < 16; ++j) pk[j] = pack_bf16(__uint_as_float(key[2 * j] & ~3u), __uint_as_float(key[2 * j + 1] & ~3u));
+      for (int j = 0; j < 16; ++j) key[j] = (int)0x80000000;
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-          *reinterpret_cast<uint4*>(outp + off + 8 * j) = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
-        if (argp) {
-          uint32_t ak[8];
+      for (int w = 0; w < 4; ++w) {
+        // window position (wy, wx) lies inside the 21x21 conv output unless it is the pool's padding row / column
+        const bool in = ((w >> 1) == 0 || py < PW - 1) && ((w & 1) == 0 || px < PW - 1);
 #pragma unroll
-          for (int j = 0; j < 8; ++j)
-            ak[j] = (3u - (key[4 * j] & 3u)) | ((3u - (key[4 * j + 1] & 3u)) << 8) | ((3u - (key[4 * j + 2] & 3u)) << 16) |
-                    ((3u - (key[4 * j + 3] & 3u)) << 24);
-          *reinterpret_cast<uint4*>(argp + off) = make_uint4(ak[0], ak[1], ak[2], ak[3]);
-          *reinterpret_cast<uint4*>(argp + off + 16) = make_uint4(ak[4], ak[5], ak[6], ak[7]);
+        for (int j = 0; j < 16; ++j) {
+          const int kj = (__float_as_int(__uint_as_float(r[w][j]) + bias[j]) & ~3) | (3 - w);
+          key[j] = in ? max(key[j], kj) : key[j];
         }
       }
+      if (valid) {
+        const size_t off = ((size_t)b * NWIN + m) * 32 + h * 16;
+        uint32_t pk[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          pk[j] = pack_bf16(__int_as_float(max(key[2 * j], 0) & ~3), __int_as_float(max(key[2 * j + 1], 0) & ~3));
+        *reinterpret_cast<uint4*>(outp + off) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+        *reinterpret_cast<uint4*>(outp + off + 8) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+        if (argp) {
+          uint32_t ak[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            ak[j] = (3u - ((uint32_t)key[4 * j] & 3u)) | ((3u - ((uint32_t)key[4 * j + 1] & 3u)) << 8) |
+                    ((3u - ((uint32_t)key[4 * j + 2] & 3u)) << 16) | ((3u - ((uint32_t)key[4 * j + 3] & 3u)) << 24);
+          *reinterpret_cast<uint4*>(argp + off) = make_uint4(ak[0], ak[1], ak[2], ak[3]);
+        }
+      }
+      if (tid == 64) trace_stamp(a.trace, i, 7);
     }
   } else {
     // ---------------------------------------------------------------- builders
@@ -277,10 +414,13 @@ __global__ void __launch_bounds__(NWARPS * 32, 1) conv1_s2d_fwd_kernel(FwdArgs a
     for (int i = 0; i < ntiles; ++i) {
       const int rb = i & 1, ph = (i >> 1) & 1;
       mbar_wait(&raw_full[rb], ph);
+      if (bt == 0) trace_stamp(a.trace, i, 1);
       mbar_wait(&img_empty[rb], ph ^ 1);
-      build_image<PLANAR>(smem + rb * RAW_BYTES, smem + FWD_OFF_IMG + rb * IMG_BYTES, bt, FWD_BUILD_WARPS * 32);
+      if (bt == 0) trace_stamp(a.trace, i, 2);
+      build_image<PLANAR, true>(smem + rb * RAW_BYTES, smem + FWD_OFF_IMG + rb * IMG_BYTES, bt);       // exact f16 image
       fence_async_proxy();
       __syncwarp();
+      if (bt == 0) trace_stamp(a.trace, i, 3);
       if (lane == 0) {
         mbar_arrive(&img_full[rb]);
         mbar_arrive(&raw_empty[rb]);
@@ -290,6 +430,7 @@ __global__ void __launch_bounds__(NWARPS * 32, 1) conv1_s2d_fwd_kernel(FwdArgs a
   pdl_trigger();
   tc_fence_before();
   __syncthreads();
+  if (tid == 0) trace_cta(a.trace, 3);
   if (warp == 1) tmem_dealloc(tmem, 256);
 }
 
@@ -320,6 +461,7 @@ __global__ void __launch_bounds__(NWARPS * 32, 1) conv1_s2d_wgrad_kernel(WgradAr
   uint8_t* smem = align_smem(smem_raw);
   __shared__ uint64_t ld_full[2], ld_empty[2], op_full, op_empty;
   __shared__ uint32_t tmem_slot;
+  __shared__ int64_t tab[TAB_TILES][4];
   const int tid = threadIdx.x, lane = tid & 31;
   const int warp = warp_uniform_idx();
   const int G = gridDim.x, b0 = blockIdx.x;
@@ -341,7 +483,8 @@ __global__ void __launch_bounds__(NWARPS * 32, 1) conv1_s2d_wgrad_kernel(WgradAr
   tc_fence_after();
   const uint32_t tmem = tmem_slot;
   const uint32_t sbase = smem_u32(smem);
-  pdl_wait_then_trigger();
+  pdl_wait();
+  pdl_trigger();                                              // see the forward kernel
   float colsum[2][8];                                          // bias gradient: this thread's (m, channel chunk) items
 #pragma unroll
   for (int q = 0; q < 2; ++q)
@@ -349,17 +492,16 @@ __global__ void __launch_bounds__(NWARPS * 32, 1) conv1_s2d_wgrad_kernel(WgradAr
     for (int e = 0; e < 8; ++e) colsum[q][e] = 0.f;
   if (warp == 0) {
     // ---------------------------------------------------------------- producer: stack + gradient + arg-max of a sample
-    if (elect_one()) {
-      for (int i = 0; i < ntiles; ++i) {
-        const int rb = i & 1, b = b0 + i * G;
-        mbar_wait(&ld_empty[rb], ((i >> 1) & 1) ^ 1);
-        mbar_expect_tx(&ld_full[rb], WG_GRAD_BYTES + WG_ARG_BYTES);
-        bulk_g2s(sbase + WG_OFF_GA + rb * WG_GA_SLOT, a.dactg + (size_t)b * NWIN * 32, WG_GRAD_BYTES, &ld_full[rb]);
-        bulk_g2s(sbase + WG_OFF_GA + rb * WG_GA_SLOT + 8192, a.arg + (size_t)b * NWIN * 32, WG_ARG_BYTES, &ld_full[rb]);
-        load_stack(a.src, 0, b, sbase + rb * RAW_BYTES, &ld_full[rb]);
-      }
-    }
-    __syncwarp();
+    producer_loop(
+        a.src, 0, b0, G, ntiles, tab, [&](int i) { return sbase + (i & 1) * RAW_BYTES; },
+        [&](int i) {
+          const int rb = i & 1, b = b0 + i * G;
+          mbar_wait(&ld_empty[rb], ((i >> 1) & 1) ^ 1);
+          mbar_expect_tx(&ld_full[rb], WG_GRAD_BYTES + WG_ARG_BYTES);
+          bulk_g2s(sbase + WG_OFF_GA + rb * WG_GA_SLOT, a.dactg + (size_t)b * NWIN * 32, WG_GRAD_BYTES, &ld_full[rb]);
+          bulk_g2s(sbase + WG_OFF_GA + rb * WG_GA_SLOT + 8192, a.arg + (size_t)b * NWIN * 32, WG_ARG_BYTES, &ld_full[rb]);
+        },
+        [&](int i) { return &ld_full[i & 1]; });
   } else if (warp == 1) {
     // ---------------------------------------------------------------- MMA issuer
     constexpr uint32_t idesc = make_idesc(TM, 32, true, true);
@@ -398,7 +540,7 @@ __global__ void __launch_bounds__(NWARPS * 32, 1) conv1_s2d_wgrad_kernel(WgradAr
       const int rb = i & 1;
       mbar_wait(&ld_full[rb], (i >> 1) & 1);
       if (i > 0) mbar_wait(&op_empty, (i - 1) & 1);             // the previous sample's MMAs have read the operands
-      build_image<PLANAR>(smem + rb * RAW_BYTES, smem + WG_OFF_IMG, bt, WG_BUILDERS);
+      build_image<PLANAR, false>(smem + rb * RAW_BYTES, smem + WG_OFF_IMG, bt);
       const uint8_t* ga = smem + WG_OFF_GA + rb * WG_GA_SLOT;
 #pragma unroll
       for (int q = 0; q < 2; ++q) {

@@ -11,6 +11,8 @@
 //   conv_dgrad_kernel   gradient into the previous layer's activations
 //   optimizer_kernel    adds the partial sums up, L2 term, and applies one of TF's 7 update rules (network.py:169-202)
 //   mlp_*_kernel        the 4-20-20-A tanh net of SimpleNetwork as warp-level kernels (network.py:258-313)
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 #include "gemm_core.cuh"
 #include "umma_core.cuh"
@@ -173,7 +175,8 @@ struct Seg {
   __nv_bfloat16* wt;      // [N][K]            (forward)
   __nv_bfloat16* wd;      // [CIN][taps][N]    (dgrad), may be null
   int K, N, CIN;
-  int kperm;              // conv1 in the space-to-depth formulation: the image's reduction index is s2d::kperm(k)
+  int kperm;              // conv1 in the space-to-depth formulation: the image's reduction index is s2d::kperm(k) ...
+  int f16;                //   ... and its elements are IEEE halves (conv1's MMAs run f16 x f16, see conv1_s2d.cuh)
 };
 constexpr int MAX_SEGS = 6;
 struct OptArgs {
@@ -292,7 +295,7 @@ __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs a) {
   // of 256 consecutive elements (K*N is a multiple of 256, N of 32), so that the refreshed [n][k] stage image is
   // written as 16-byte chunks of 8 consecutive k (through shared memory) instead of 2-byte writes 128 bytes apart
   const bool tiled = s.wt != nullptr && (int)(blockIdx.x * blockDim.x) < s.K * s.N;
-  __shared__ __nv_bfloat16 wtile[8][32 + 2];
+  __shared__ uint16_t wtile[8][32 + 2];           // bf16 (or f16, s.f16) bit patterns
   if (tiled) {
     const int ntn = s.N >> 5, kt = blockIdx.x / ntn, nt = blockIdx.x - kt * ntn;
     i = (kt * 8 + (int)(threadIdx.x >> 5)) * s.N + nt * 32 + (int)(threadIdx.x & 31);
@@ -375,10 +378,10 @@ __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs a) {
   if (tiled) {
     const int k = i / s.N, n = i - k * s.N;
     const __nv_bfloat16 v = __float2bfloat16_rn(w);
-    wtile[threadIdx.x >> 5][threadIdx.x & 31] = v;
+    wtile[threadIdx.x >> 5][threadIdx.x & 31] = s.f16 ? __half_as_ushort(__float2half_rn(w)) : __bfloat16_as_ushort(v);
     __syncthreads();
     if (threadIdx.x < 32) {              // column n of the tile: its 8 consecutive k are one 16-byte chunk of the image
-      __align__(16) __nv_bfloat16 c8[8];
+      __align__(16) uint16_t c8[8];
 #pragma unroll
       for (int e = 0; e < 8; ++e) c8[e] = wtile[e][threadIdx.x];
       // thread < 32: k = 8*kt (kperm keeps runs of 8 consecutive reduction indices together)
@@ -501,7 +504,7 @@ __global__ void fill_kernel(float* p, long long n, float v) {
 // bf16 copies of one layer's weights for the tensor-core path: wt[n][k] (forward: B operand, K-major) and
 // wd[c][(ky,kx,n)] (dgrad), both stored as swizzled stage images (umma::img_index) so that a stage's tile is one
 // contiguous bulk copy.  w is the fp32 master in TF layout [k=(ky,kx,c)][n].
-struct CvtLayer { const float* w; __nv_bfloat16* wt; __nv_bfloat16* wd; int K, N, CIN, kperm; };
+struct CvtLayer { const float* w; __nv_bfloat16* wt; __nv_bfloat16* wd; int K, N, CIN, kperm, f16; };
 struct CvtArgs { CvtLayer l[4]; };
 __global__ void __launch_bounds__(256) weights_to_bf16_kernel(CvtArgs a) {
   const CvtLayer L = a.l[blockIdx.y];
@@ -509,7 +512,8 @@ __global__ void __launch_bounds__(256) weights_to_bf16_kernel(CvtArgs a) {
   if (i >= L.K * L.N) return;
   const int k = i / L.N, n = i - k * L.N;
   const __nv_bfloat16 v = __float2bfloat16_rn(L.w[i]);
-  L.wt[umma::img_index(n, L.kperm ? umma::s2d::kperm(k) : k, L.N)] = v;
+  reinterpret_cast<uint16_t*>(L.wt)[umma::img_index(n, L.kperm ? umma::s2d::kperm(k) : k, L.N)] =
+      L.f16 ? __half_as_ushort(__float2half_rn(L.w[i])) : __bfloat16_as_ushort(v);
   if (L.wd) {
     const int t = k / L.CIN, c = k - t * L.CIN;
     L.wd[umma::img_index(c, t * L.N + n, L.CIN)] = v;
@@ -716,6 +720,7 @@ struct dqn_net_s {
   size_t wt_off[4] = {}, wd_off[4] = {}, wt_total = 0, wd_total = 0;
   // optional per-kernel timing (bench.py's roofline figures): one event pair per stage
   bool timing = false;
+  bool timing_sticky = false;         // brackets captured into a graph: every replay refreshes the same stages
   cudaEvent_t ev0[DQN_NUM_STAGES] = {}, ev1[DQN_NUM_STAGES] = {};
   bool stage_used[DQN_NUM_STAGES] = {};
   double stage_ms[DQN_NUM_STAGES] = {};
@@ -723,15 +728,24 @@ struct dqn_net_s {
 };
 
 namespace {
-// Brackets one kernel launch: counts it and, in timing mode, records its event pair.
+// Brackets one kernel launch: counts it and, in timing mode, records its event pair.  While the stream is being
+// captured into a CUDA graph the records become external event-record NODES of the graph, so a replay of that graph
+// stamps every kernel as it runs inside the graph (no host launch latency inside the bracket; the nodes also cut the
+// programmatic-dependent-launch overlap between neighbours, so a bracket is one kernel's own duration).
+static void stage_record(cudaEvent_t ev, cudaStream_t st) {
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  cudaStreamIsCapturing(st, &cs);
+  if (cs == cudaStreamCaptureStatusActive) cudaEventRecordWithFlags(ev, st, cudaEventRecordExternal);
+  else cudaEventRecord(ev, st);
+}
 struct StageScope {
   dqn_net_s* h; int id; cudaStream_t st;
   StageScope(dqn_net_s* h_, int id_, cudaStream_t st_) : h(h_), id(id_), st(st_) {
     dqn::count_launch();
-    if (h->timing) cudaEventRecord(h->ev0[id], st);
+    if (h->timing) stage_record(h->ev0[id], st);
   }
   ~StageScope() {
-    if (h->timing) { cudaEventRecord(h->ev1[id], st); h->stage_used[id] = true; }
+    if (h->timing) { stage_record(h->ev1[id], st); h->stage_used[id] = true; }
   }
 };
 }  // namespace
@@ -739,7 +753,7 @@ struct StageScope {
 static const char* kStageNames[DQN_NUM_STAGES] = {
     "gather", "fwd_conv1", "fwd_conv2", "fwd_conv3", "fwd_fc", "td_head", "head_wgrad", "loss",
     "wgrad_fc", "dgrad_fc", "wgrad_conv3", "dgrad_conv3", "wgrad_conv2", "dgrad_conv2", "wgrad_conv1",
-    "reduce_grad", "optimizer", "mlp_backward", "mlp_forward", "head_forward", "fc_td_fused"};
+    "reduce_grad", "optimizer", "mlp_backward", "mlp_forward", "head_forward", "fc_td_fused", "launch_floor"};
 
 static int refresh_bf16_weights(dqn_net_s* h, int set, cudaStream_t st);
 
@@ -1135,6 +1149,25 @@ static void launch_fwd_res_u8(umma::FwdArgsT a, int npass, int num_sms, cudaStre
   dim3 grid((unsigned)((total + per - 1) / per), 1, 1);
   launch_pdl(umma::umma_fwd_res_u8_kernel<G, NTILE>, grid, dim3(umma::TT), smem, st, 1, a);
 }
+// DQN_S2D_TRACE=1: CTA 0 of the conv1 forward kernel stamps clock64() per (tile, pipeline event) here (dqn_debug_trace)
+static __device__ unsigned long long g_s2d_trace[60 * 8 + 160 * 4];
+static unsigned long long* s2d_trace_ptr() {
+  static unsigned long long* p = nullptr;
+  static bool init = false;
+  if (!init) {
+    init = true;
+    const char* e = getenv("DQN_S2D_TRACE");
+    if (e && e[0] == '1') cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_s2d_trace);
+  }
+  return p;
+}
+extern "C" int dqn_debug_trace(unsigned long long* host, int32_t n) {
+  DQN_REQUIRE(host && n > 0 && n <= 60 * 8 + 160 * 4, DQN_ERR_INVALID, "debug_trace: bad argument");
+  DQN_CUDA(cudaDeviceSynchronize());
+  DQN_CUDA(cudaMemcpyFromSymbol(host, g_s2d_trace, (size_t)n * 8));
+  return 0;
+}
+
 // conv1 in the space-to-depth formulation (conv1_s2d.cuh): persistent, one CTA per SM
 static void launch_conv1_s2d_fwd(dqn_net_s* h, const umma::s2d::Src& src, const int pass_id[2], int npass, int B, cudaStream_t st) {
   namespace S = umma::s2d;
@@ -1144,6 +1177,7 @@ static void launch_conv1_s2d_fwd(dqn_net_s* h, const umma::s2d::Src& src, const 
   a.src = src;
   a.B = B;
   a.npass = npass;
+  a.trace = s2d_trace_ptr();
   for (int p = 0; p < 2; ++p) {
     const int id = pass_id[p < npass ? p : 0];
     const float* params = id == 0 ? h->online : h->target;
@@ -1154,8 +1188,8 @@ static void launch_conv1_s2d_fwd(dqn_net_s* h, const umma::s2d::Src& src, const 
   }
   int grid = npass == 2 ? (h->num_sms & ~1) : h->num_sms;
   if (grid > npass * B) grid = npass * B;
-  if (src.x[0]) launch_pdl(S::conv1_s2d_fwd_kernel<false>, dim3(grid), dim3(S::NWARPS * 32), S::FWD_SMEM, st, 1, a);
-  else launch_pdl(S::conv1_s2d_fwd_kernel<true>, dim3(grid), dim3(S::NWARPS * 32), S::FWD_SMEM, st, 1, a);
+  if (src.x[0]) launch_pdl(S::conv1_s2d_fwd_kernel<false>, dim3(grid), dim3(S::FWD_WARPS * 32), S::FWD_SMEM, st, 1, a);
+  else launch_pdl(S::conv1_s2d_fwd_kernel<true>, dim3(grid), dim3(S::FWD_WARPS * 32), S::FWD_SMEM, st, 1, a);
 }
 
 static void launch_conv1_s2d_wgrad(dqn_net_s* h, const umma::s2d::Src& src, int B, cudaStream_t st, int* nsplit_out) {
@@ -1286,7 +1320,7 @@ static int refresh_bf16_weights(dqn_net_s* h, int set, cudaStream_t st) {
     c.l[l].wd = (set == 0 && l >= 1) ? h->wd_bf + h->wd_off[l] : nullptr;
     c.l[l].K = L.K; c.l[l].N = L.N;
     c.l[l].CIN = l == 0 ? 4 : (l == 1 ? 32 : (l == 2 ? 64 : L.K));
-    c.l[l].kperm = (l == 0 && h->conv1_s2d) ? 1 : 0;
+    c.l[l].kperm = c.l[l].f16 = (l == 0 && h->conv1_s2d) ? 1 : 0;
     maxn = L.K * L.N > maxn ? L.K * L.N : maxn;
   }
   dim3 grid((maxn + 255) / 256, 4);
@@ -1372,7 +1406,7 @@ static void fill_segs(dqn_net_s* h, OptArgs* o, const int nsplit[4], bool from_f
     for (int i = 0; i < 3; ++i) {
       const Tensor& w = h->tensors[2 * i];
       const Tensor& b = h->tensors[2 * i + 1];
-      o->seg[i] = Seg{(long long)w.off, (int)(w.numel + b.numel), (int)w.numel, h->grad + w.off, 1, 0, nullptr, nullptr, 0, 0, 0, 0};
+      o->seg[i] = Seg{(long long)w.off, (int)(w.numel + b.numel), (int)w.numel, h->grad + w.off, 1, 0, nullptr, nullptr, 0, 0, 0, 0, 0};
     }
   } else {
     o->nseg = 5;
@@ -1380,20 +1414,20 @@ static void fill_segs(dqn_net_s* h, OptArgs* o, const int nsplit[4], bool from_f
       const Tensor& w = h->tensors[2 * l];
       const GemmLayer& L = h->L[l];
       Seg s{(long long)w.off, L.K * L.N + L.N, l == 3 ? L.K * L.N : 0, L.partial, nsplit[l], (long long)(L.K + 1) * L.N,
-            nullptr, nullptr, 0, 0, 0, 0};
+            nullptr, nullptr, 0, 0, 0, 0, 0};
       if (from_flat_grad) { s.partial = h->grad + w.off; s.nsplit = 1; s.stride = 0; }
       if (h->precision == 1) {
         s.wt = h->wt_bf[0] + h->wt_off[l];
         s.wd = l >= 1 ? h->wd_bf + h->wd_off[l] : nullptr;
         s.K = L.K; s.N = L.N;
         s.CIN = l == 0 ? 4 : (l == 1 ? 32 : (l == 2 ? 64 : L.K));
-        s.kperm = (l == 0 && h->conv1_s2d) ? 1 : 0;
+        s.kperm = s.f16 = (l == 0 && h->conv1_s2d) ? 1 : 0;
       }
       o->seg[l] = s;
     }
     const Tensor& w5 = h->tensors[8];
     Seg s{(long long)w5.off, (h->F + 1) * h->A, h->F * h->A, h->head_partial, h->head_nsplit,
-          (long long)(h->F + 1) * h->A, nullptr, nullptr, 0, 0, 0, 0};
+          (long long)(h->F + 1) * h->A, nullptr, nullptr, 0, 0, 0, 0, 0};
     if (from_flat_grad) { s.partial = h->grad + w5.off; s.nsplit = 1; s.stride = 0; }
     o->seg[4] = s;
   }
@@ -1737,9 +1771,9 @@ static int step_from_ring(dqn_net_s* net, dqn_replay_t replay, const int32_t* d_
     src.actions = net->st_actions; src.rewards = net->st_rewards; src.terminals = net->st_term;
     return run_step(net, nullptr, nullptr, net->st_actions, net->st_rewards, net->st_term, k, d_loss, nullptr, mode, 0, st, &src);
   }
-  if (net->timing) cudaEventRecord(net->ev0[DQN_STAGE_GATHER], st);
+  if (net->timing) stage_record(net->ev0[DQN_STAGE_GATHER], st);
   int rc = dqn_replay_gather(replay, d_idx, k, net->st_states, net->st_next, net->st_actions, net->st_rewards, net->st_term, st);
-  if (net->timing) { cudaEventRecord(net->ev1[DQN_STAGE_GATHER], st); net->stage_used[DQN_STAGE_GATHER] = true; }
+  if (net->timing) { stage_record(net->ev1[DQN_STAGE_GATHER], st); net->stage_used[DQN_STAGE_GATHER] = true; }
   if (rc) return rc;
   return run_step(net, net->st_states, net->st_next, net->st_actions, net->st_rewards, net->st_term, k, d_loss, nullptr, mode, 0, st);
 }
@@ -1906,7 +1940,8 @@ extern "C" int dqn_net_set_timing(dqn_net_t h, int32_t enable) {
     }
   }
   h->timing = enable != 0;
-  for (int i = 0; i < DQN_NUM_STAGES; ++i) h->stage_used[i] = false;
+  h->timing_sticky = enable == 3;
+  if (enable != 3) for (int i = 0; i < DQN_NUM_STAGES; ++i) h->stage_used[i] = false;
   if (enable == 2) for (int i = 0; i < DQN_NUM_STAGES; ++i) { h->stage_ms[i] = 0.0; h->stage_count[i] = 0; }
   return 0;
 }
@@ -1921,8 +1956,22 @@ extern "C" int dqn_net_timing_collect(dqn_net_t h) {
     DQN_CUDA(cudaEventElapsedTime(&ms, h->ev0[i], h->ev1[i]));
     h->stage_ms[i] += ms;
     h->stage_count[i] += 1;
-    h->stage_used[i] = false;
+    if (!h->timing_sticky) h->stage_used[i] = false;
   }
+  return 0;
+}
+
+// Enqueues the timing bracket around an EMPTY kernel as the pseudo-stage "launch_floor" (works eagerly and under stream
+// capture, like the real brackets): what a bracket costs by itself, in the same mode as the step's brackets.
+extern "C" int dqn_net_timing_floor_enqueue(dqn_net_t h, dqn_stream_t stream) {
+  DQN_REQUIRE(h && h->timing, DQN_ERR_STATE, "timing_floor_enqueue: timing is not enabled");
+  DeviceGuard g(h->device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  {
+    StageScope sc(h, DQN_STAGE_LAUNCH_FLOOR, st);
+    launch_pdl(empty_kernel, dim3(1), dim3(32), 0, st, 1);
+  }
+  DQN_CUDA(cudaGetLastError());
   return 0;
 }
 

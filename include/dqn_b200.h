@@ -285,13 +285,20 @@ int dqn_cnn_forward_noalloc(const float* d_params, int32_t num_actions, const ui
  * launches the kernels that were counted when it was captured). */
 int64_t dqn_launch_count(void);
 /* enable=1: every kernel of the following eager steps is bracketed by a CUDA event pair on the
- * caller's stream; enable=2 additionally zeroes the accumulated totals; 0 switches it off. */
+ * caller's stream; enable=2 additionally zeroes the accumulated totals; 0 switches it off.
+ * If a step is CAPTURED into a CUDA graph while timing is on, the brackets become event-record nodes of that graph
+ * and every replay stamps the kernels as they run inside the graph; enable=3 (set after the capture, before the
+ * replays) keeps the set of bracketed stages from the capture so that dqn_net_timing_collect can be called after
+ * every replay. */
 int dqn_net_set_timing(dqn_net_t h, int32_t enable);
 /* Synchronises the device and adds the last step's per-kernel durations to the totals. */
 int dqn_net_timing_collect(dqn_net_t h);
 int dqn_net_timing_read(dqn_net_t h, int32_t stage, double* total_ms, int32_t* count);
 /* The same event bracket around an empty kernel (microseconds, mean of 20): the floor to subtract from the above. */
 int dqn_net_timing_floor(dqn_net_t h, dqn_stream_t stream, double* us);
+/* The same bracket as a pseudo-stage "launch_floor" of the step being timed (eager or captured): enqueue it after the
+ * step and read it back with dqn_net_timing_read like any other stage. */
+int dqn_net_timing_floor_enqueue(dqn_net_t h, dqn_stream_t stream);
 const char* dqn_stage_name(int32_t stage); /* "" beyond the last stage */
 
 #ifdef __cplusplus

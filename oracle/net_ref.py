@@ -191,8 +191,19 @@ def bf16_round(a):
     return u.astype(np.uint32).view(np.float32).astype(a.dtype if a.dtype.kind == "f" else np.float64)
 
 
+def f16_round(a):
+    """Round to the nearest IEEE half (ties to even), returned in the input's float type."""
+    a = np.asarray(a)
+    return a.astype(np.float16).astype(a.dtype if a.dtype.kind == "f" else np.float64)
+
+
 def _ident(a):
     return a
+
+
+# conv1 of the reference net ("cnn") in the CUDA path's 16-bit mode: f16 operands (the default kernels) or bf16 (the
+# DQN_NO_RESIDENT=1 kernels).  Tests that exercise the latter set this to False.
+CONV1_F16 = True
 
 
 # ----------------------------------------------------------------------------- forward / backward
@@ -216,6 +227,10 @@ def forward(arch, params, x, input_shape=None, keep=False, bf16=False):
     per = []
     for i, L in enumerate(layers):
         w, b = Q(params[2 * i]), params[2 * i + 1]
+        if bf16 and arch == "cnn" and i == 0 and CONV1_F16:
+            # conv1 of the reference net runs with f16 operands in the CUDA path's 16-bit mode (the uint8 frames enter the
+            # tensor core as f16 without a conversion instruction, and both operands of an MMA share one format)
+            w = f16_round(params[0])
         z, cols = conv_fwd(a, w, L)
         r = np.maximum(z + b, 0.0)
         if L["pool"]:
