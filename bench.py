@@ -379,7 +379,9 @@ def _dp_check(torch, dist, dp, network, cfg, rm, batch, d_idx, precision):
     ref = wa.clone()
     dist.broadcast(ref, 0)
     same = bool(torch.equal(ref, wa))
-    q = a.predict(rm.gather(d_idx).states[:8])            # through the refreshed bf16 operand images
+    probe = rm.gather(d_idx).states[:8].clone()           # the same 8 states on every rank (each rank's ring differs)
+    dist.broadcast(probe, 0)
+    q = a.predict(probe)                                  # through the refreshed bf16 operand images
     qr = q.clone()
     dist.broadcast(qr, 0)
     t = torch.tensor([rel, 0.0 if same else 1.0, 0.0 if torch.equal(q, qr) else 1.0], device=wa.device)
@@ -940,9 +942,11 @@ def gather_sweep(rm, dev, ks=(8192,), iters=30):
 
 
 def run_e2e(args, cfg, net, rm, world, dev, DQNAgent, FrameBuffer, dist):
-    """updates/s through the public API with HOST inputs: per step update_freq x (FrameBuffer.append/get_state +
-    ReplayMemory.add of a host frame) and DQNAgent._train_minibatch (host random.sample -> H2D indices -> CUDA graph
-    -> loss read back to the host)."""
+    """updates/s through the public API with HOST inputs, the same loop the reference arm times on the CPU: per step
+    update_freq x ReplayMemory.add(state, action, reward, next_state, terminal) with host uint8 stacks (the reference's
+    five-argument signature) and one DQNAgent._train_minibatch (host random.sample -> H2D indices -> CUDA graph -> loss
+    read back to the host).  Also reported: the same with the actor-side FrameBuffer.append/get_state in the loop (the
+    agent's own episode loop, which hands add() the newest frame as a contiguous array)."""
     import torch
 
     class _Env(object):            # DQNAgent only needs these at construction when replay_start_size == 0
@@ -959,38 +963,58 @@ def run_e2e(args, cfg, net, rm, world, dev, DQNAgent, FrameBuffer, dist):
     agent = DQNAgent(_Env(), net, None, rm, cfg, enable_summary=True)
     batch = cfg.minibatch_size
     rng = np.random.default_rng(5)
-    pool = rng.integers(0, 256, (256, 84, 84), dtype=np.uint8)
-    fb = FrameBuffer(4)
-    fb.append(pool[0])
-    state = fb.get_state()
+    NP = 256
+    pool = rng.integers(0, 256, (NP, 84, 84), dtype=np.uint8)
+    # host stacks as an actor would hold them: stack i = frames i-3..i (HWC, channel = time), so that stack i+1 is stack i
+    # shifted by one frame -- what ReplayMemory.add receives from the reference's episode loop (dqn_agent.py:96-100)
+    stacks = [np.ascontiguousarray(np.stack([pool[(i - 3 + c) % NP] for c in range(4)], axis=-1)) for i in range(NP)]
     n = args.e2e_steps
     warm = 10
-    fi = 1
+    fi = 0
 
     def one():
-        nonlocal state, fi
+        nonlocal fi
         for _ in range(cfg.update_freq):
-            fb.append(pool[fi % 256]); fi += 1
-            nxt = fb.get_state()
-            rm.add(state, fi % A_PONG, float(fi % 3 - 1), nxt, False, newest=fb.frames[-1])     # as DQNAgent._record does
-            state = nxt
+            rm.add(stacks[fi % NP], fi % A_PONG, float(fi % 3 - 1), stacks[(fi + 1) % NP], False)
+            fi += 1
         agent._train_minibatch(batch)          # summary_freq=1 -> the loss of every update is read back to the host
         return agent.last_loss                 # (asynchronously: it is picked up while the next update is prepared)
 
-    for _ in range(warm):
-        one()
-    torch.cuda.synchronize()
-    if dist is not None:
-        dist.barrier()
-    t0 = time.perf_counter()
-    for _ in range(n):
-        loss = one()
-    torch.cuda.synchronize()
-    dt = time.perf_counter() - t0
-    if dist is not None:
-        t = torch.tensor([dt], device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dt = float(t.item())
+    fb = FrameBuffer(4)
+    fb.append(pool[0])
+    fstate = [fb.get_state()]
+
+    def one_fb():
+        nonlocal fi
+        state = fstate[0]
+        for _ in range(cfg.update_freq):
+            fb.append(pool[fi % NP]); fi += 1
+            nxt = fb.get_state()
+            rm.add(state, fi % A_PONG, float(fi % 3 - 1), nxt, False, newest=fb.frames[-1])     # as DQNAgent._record does
+            state = nxt
+        fstate[0] = state
+        agent._train_minibatch(batch)
+        return agent.last_loss
+
+    def timed(fn, count):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        t0 = time.perf_counter()
+        for _ in range(count):
+            fn()
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        if dist is not None:
+            t = torch.tensor([dt], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+        return dt
+
+    dt = timed(one, n)
+    dt_fb = timed(one_fb, max(n // 4, 50))
     agent.flush_summaries()
     loss = agent.last_loss
     assert loss is not None and np.isfinite(loss)
@@ -1000,10 +1024,13 @@ def run_e2e(args, cfg, net, rm, world, dev, DQNAgent, FrameBuffer, dist):
     h2d = gi * FRAME + 64 + gi * 32 + batch * 4
     return {"value": world * n / dt, "unit": "updates/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
             "steps": n, "ms_per_step": dt / n * 1e3,
-            "path": "FrameBuffer.append/get_state + ReplayMemory.add x%d (host uint8 frames) + DQNAgent._train_minibatch "
+            "with_framebuffer": {"value": world * max(n // 4, 50) / dt_fb, "unit": "updates/s",
+                                 "path": "FrameBuffer.append/get_state + ReplayMemory.add(..., newest=frame) x%d + "
+                                         "_train_minibatch" % cfg.update_freq},
+            "path": "ReplayMemory.add x%d (host uint8 stacks, reference signature) + DQNAgent._train_minibatch "
                     "(random.sample on host; one CUDA-graph launch per update moves the staged frames into the ring, "
-                    "gathers, updates and copies the loss to pinned host memory, where it is collected one update later)"
-                    % cfg.update_freq}
+                    "updates straight from the ring and copies the loss to pinned host memory, where it is collected one "
+                    "update later)" % cfg.update_freq}
 
 
 _REAL_STDOUT = None

@@ -48,6 +48,9 @@ SIGNATURES = {
     "dqn_replay_flush": (C.c_int, [c_vp, c_vp]),
     "dqn_replay_seal": (C.c_int, [c_vp, C.POINTER(c_i32), c_vp]),
     "dqn_replay_ingest_staged": (C.c_int, [c_vp, c_i32, c_vp, c_vp, c_i32, c_vp]),
+    "dqn_replay_set_lanes": (C.c_int, [c_vp, c_i32]),
+    "dqn_replay_add_batch": (C.c_int, [c_vp, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "dqn_replay_current_states": (C.c_int, [c_vp, c_vp, c_vp]),
     "dqn_replay_size": (C.c_int, [c_vp, C.POINTER(c_i64), C.POINTER(c_i64)]),
     "dqn_replay_next_frame_pos": (C.c_int, [c_vp, C.POINTER(c_i64)]),
     "dqn_replay_gather": (C.c_int, [c_vp, c_vp, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),

@@ -203,6 +203,35 @@ ingest_kernel(const uint8_t* __restrict__ meta_blk, const uint8_t* __restrict__ 
   }
 }
 
+// Lock-step actors (dqn_replay_add_batch): copy op list -> frame ring.  src >= 0: frame index in the caller's batch;
+// src < 0: ring slot -src-1 (re-storing the tail of a stack at the start of an environment's lane).
+struct LaneOp { int64_t src, dst; };
+__global__ void __launch_bounds__(256)
+lane_scatter_kernel(const LaneOp* __restrict__ ops, const uint8_t* __restrict__ batch, int64_t batch_pitch,
+                    uint8_t* __restrict__ frames, int32_t pitch) {
+  const LaneOp op = ops[blockIdx.y];
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= pitch / 16) return;
+  const uint8_t* src = op.src >= 0 ? batch + op.src * batch_pitch : frames + (-op.src - 1) * (int64_t)pitch;
+  // a batch frame has frame_bytes valid bytes; the ring's pitch rounds that up to 16: the tail chunk may read a few
+  // bytes past the frame inside the caller's (larger) allocation only when batch_pitch == pitch, which the host enforces
+  reinterpret_cast<uint4*>(frames + op.dst * (int64_t)pitch)[i] = reinterpret_cast<const uint4*>(src)[i];
+}
+
+// Stacks ending at explicit ring positions (the actors' current states): out[n][elems][S], same layout as the gather.
+__global__ void __launch_bounds__(256)
+stack_at_positions_kernel(RingView rv, const int64_t* __restrict__ pos, int32_t n, int32_t elems, uint8_t* __restrict__ out) {
+  const int S = rv.frames_per_state;
+  const int64_t total = (int64_t)n * elems;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    const int32_t e = (int32_t)(t / elems), i = (int32_t)(t - (int64_t)e * elems);
+    for (int c = 0; c < S; ++c) {
+      const int64_t fs = (pos[e] - (S - 1) + c) % rv.frame_capacity;
+      out[((int64_t)e * elems + i) * S + c] = rv.frames[fs * (int64_t)rv.pitch + i];
+    }
+  }
+}
+
 }  // namespace dqn
 
 // ---------------------------------------------------------------------------------------------
@@ -247,6 +276,19 @@ struct dqn_replay_s {
   cudaStream_t last_stream = nullptr;
   int sticky = 0;
   int num_sms = 148;
+  // lock-step actor lanes (dqn_replay_set_lanes / dqn_replay_add_batch): environment e owns the frame slots
+  // [base, base + cap) and writes them in order, so the frames of its stacks stay consecutive although E environments
+  // append in turn.  `written` counts the slots consumed so far (virtual, never wraps), `tail` the oldest still needed.
+  struct Lane { int64_t base, cap, written, tail, last_pos, state_vlo; bool has_state; };   // state_vlo: virtual index of the oldest frame of the current state stack
+  std::vector<Lane> lanes;
+  std::vector<int32_t> rec_lane;     // per record slot: lane of the transition ...
+  std::vector<int64_t> rec_vlo;      // ... and the virtual index of the oldest frame it references
+  dqn::LaneOp* ops_host[2] = {nullptr, nullptr};   // pinned
+  dqn::LaneOp* ops_dev[2] = {nullptr, nullptr};
+  int64_t* pos_host = nullptr;       // pinned: current-state positions for dqn_replay_current_states
+  int64_t* pos_dev = nullptr;
+  cudaEvent_t ops_done[2] = {nullptr, nullptr};
+  int ops_turn = 0, ops_cap = 0;
 };
 
 static int64_t live_size(const dqn_replay_s* h) { return h->total_adds < h->cap ? h->total_adds : h->cap; }
@@ -357,6 +399,13 @@ extern "C" int dqn_replay_destroy(dqn_replay_t h) {
   cudaDeviceSynchronize();
   cudaFree(h->d_frames); cudaFree(h->d_meta); cudaFree(h->d_state);
 
+  for (int i = 0; i < 2; ++i) {
+    if (h->ops_host[i]) cudaFreeHost(h->ops_host[i]);
+    if (h->ops_dev[i]) cudaFree(h->ops_dev[i]);
+    if (h->ops_done[i]) cudaEventDestroy(h->ops_done[i]);
+  }
+  if (h->pos_host) cudaFreeHost(h->pos_host);
+  if (h->pos_dev) cudaFree(h->pos_dev);
   for (int i = 0; i < kStages; ++i) {
     if (h->stage[i].frames) cudaFreeHost(h->stage[i].frames);
     if (h->stage[i].recs) cudaFreeHost(h->stage[i].recs);
@@ -370,6 +419,7 @@ extern "C" int dqn_replay_destroy(dqn_replay_t h) {
 
 static int reserve_frames(dqn_replay_s* h, int32_t n) {
   DQN_REQUIRE(n > 0, DQN_ERR_INVALID, "append_frames: n must be positive");
+  DQN_REQUIRE(h->lanes.empty(), DQN_ERR_STATE, "append_frames: this replay memory is in lock-step actor mode (dqn_replay_set_lanes)");
   int64_t need = oldest_needed(h);
   DQN_REQUIRE(h->total_frames + n - need <= h->fcap, DQN_ERR_OVERFLOW,
               "frame ring overflow: %lld frames would be live but frame_capacity is %lld; create the replay "
@@ -436,6 +486,7 @@ extern "C" int dqn_replay_append_frames_device(dqn_replay_t h, const void* d_fra
 extern "C" int dqn_replay_add(dqn_replay_t h, int64_t state_pos, int64_t next_pos, int32_t action, double reward,
                               uint8_t terminal) {
   DQN_REQUIRE(h, DQN_ERR_INVALID, "add: NULL handle");
+  DQN_REQUIRE(h->lanes.empty(), DQN_ERR_STATE, "add: this replay memory is in lock-step actor mode (dqn_replay_set_lanes); use dqn_replay_add_batch");
   const int64_t S = h->S;
   int64_t lo = (state_pos < next_pos ? state_pos : next_pos) - (S - 1);
   int64_t hi = state_pos > next_pos ? state_pos : next_pos;
@@ -459,6 +510,154 @@ extern "C" int dqn_replay_add(dqn_replay_t h, int64_t state_pos, int64_t next_po
   h->need[(size_t)(h->total_adds % h->cap)] = lo;
   h->last_need = lo;
   h->total_adds++;
+  return 0;
+}
+
+// Stages one transition record (the part of dqn_replay_add after its position checks).
+static int stage_record(dqn_replay_s* h, int64_t state_pos, int64_t next_pos, int32_t action, double reward, uint8_t terminal) {
+  Stage* s = &h->stage[h->cur];
+  if (s->nrecs == kStageRecs) {
+    int rc = flush_impl(h, h->last_stream);
+    if (rc) return rc;
+    s = &h->stage[h->cur];
+  }
+  if (s->nrecs == 0) s->first_rec = h->total_adds;
+  TransitionRec& r = s->recs[s->nrecs++];
+  r.state_pos = state_pos; r.next_pos = next_pos; r.reward = reward; r.action = action; r.terminal = terminal ? 1 : 0;
+  r.pad[0] = r.pad[1] = r.pad[2] = 0;
+  return 0;
+}
+
+extern "C" int dqn_replay_set_lanes(dqn_replay_t h, int32_t num_envs) {
+  DQN_REQUIRE(h, DQN_ERR_INVALID, "set_lanes: NULL handle");
+  DQN_REQUIRE(num_envs >= 1, DQN_ERR_INVALID, "set_lanes: num_envs must be positive");
+  DQN_REQUIRE(h->total_adds == 0 && h->total_frames == 0, DQN_ERR_STATE, "set_lanes: the replay memory must be empty");
+  DQN_REQUIRE(h->pitch == h->frame_bytes, DQN_ERR_UNSUPPORTED, "set_lanes: frame_bytes must be a multiple of 16");
+  const int64_t cap = h->fcap / num_envs;
+  DQN_REQUIRE(cap >= 3 * (int64_t)h->S + 2, DQN_ERR_INVALID,
+              "set_lanes: %d environments leave %lld frame slots each; need at least %d (raise frame_capacity)", num_envs,
+              (long long)cap, 3 * h->S + 2);
+  DeviceGuard g(h->device);
+  h->lanes.assign((size_t)num_envs, dqn_replay_s::Lane{0, cap, 0, 0, -1, 0, false});
+  for (int e = 0; e < num_envs; ++e) h->lanes[(size_t)e].base = (int64_t)e * cap;
+  h->rec_lane.assign((size_t)h->cap, -1);
+  h->rec_vlo.assign((size_t)h->cap, 0);
+  h->ops_cap = num_envs * (2 * h->S);
+  for (int i = 0; i < 2; ++i) {
+    DQN_CUDA(cudaMallocHost(&h->ops_host[i], (size_t)h->ops_cap * sizeof(LaneOp)));
+    DQN_CUDA(cudaMalloc(&h->ops_dev[i], (size_t)h->ops_cap * sizeof(LaneOp)));
+    DQN_CUDA(cudaEventCreateWithFlags(&h->ops_done[i], cudaEventDisableTiming));
+  }
+  DQN_CUDA(cudaMallocHost(&h->pos_host, (size_t)num_envs * sizeof(int64_t)));
+  DQN_CUDA(cudaMalloc(&h->pos_dev, (size_t)num_envs * sizeof(int64_t)));
+  return 0;
+}
+
+// Reserves n consecutive slots in a lane (never straddling the lane's end) and returns the slot of the first one.
+static int lane_reserve(dqn_replay_s* h, dqn_replay_s::Lane& L, int n, int64_t* first_slot) {
+  int64_t off = L.written % L.cap;
+  int64_t skip = off + n > L.cap ? L.cap - off : 0;          // not enough room before the end: start over at the lane's base
+  DQN_REQUIRE(L.written + skip + n - L.tail <= L.cap, DQN_ERR_OVERFLOW,
+              "frame ring overflow in an actor lane: %lld frames would be live but the lane holds %lld; create the replay "
+              "with a larger frame_capacity", (long long)(L.written + skip + n - L.tail), (long long)L.cap);
+  L.written += skip;
+  *first_slot = L.base + L.written % L.cap;
+  L.written += n;
+  return 0;
+}
+
+extern "C" int dqn_replay_add_batch(dqn_replay_t h, int32_t num_envs, const void* d_frames, const int32_t* actions,
+                                    const double* rewards, const uint8_t* terminals, const uint8_t* episode_start,
+                                    dqn_stream_t stream) {
+  DQN_REQUIRE(h && d_frames && episode_start, DQN_ERR_INVALID, "add_batch: NULL argument");
+  DQN_REQUIRE(!h->lanes.empty() && num_envs == (int)h->lanes.size(), DQN_ERR_STATE,
+              "add_batch: call dqn_replay_set_lanes(h, %d) on the empty replay memory first", num_envs);
+  DeviceGuard g(h->device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int S = h->S;
+  const int turn = h->ops_turn;
+  DQN_CUDA(cudaEventSynchronize(h->ops_done[turn]));          // the op list about to be overwritten has been consumed
+  LaneOp* ops = h->ops_host[turn];
+  int nops = 0;
+  for (int e = 0; e < num_envs; ++e) {
+    dqn_replay_s::Lane& L = h->lanes[(size_t)e];
+    int64_t slot = 0;
+    if (episode_start[e]) {
+      // FrameBuffer.clear() + append(env.reset()): the window is the first frame S times (frame_buffer.py:35-36); no transition yet
+      int rc = lane_reserve(h, L, S, &slot);
+      if (rc) return rc;
+      for (int c = 0; c < S; ++c) ops[nops++] = LaneOp{e, slot + c};
+      L.last_pos = slot + S - 1;
+      L.state_vlo = L.written - S;
+      L.has_state = true;
+      continue;
+    }
+    DQN_REQUIRE(L.has_state, DQN_ERR_STATE, "add_batch: environment %d has no current state; its first frame must come with episode_start", e);
+    DQN_REQUIRE(actions && rewards && terminals, DQN_ERR_INVALID, "add_batch: NULL actions / rewards / terminals");
+    const int64_t spos = L.last_pos, svlo = L.state_vlo;
+    int64_t npos;
+    if ((L.written % L.cap) != 0 && L.base + L.written % L.cap == spos + 1) {
+      int rc = lane_reserve(h, L, 1, &slot);                  // the usual case: one new frame right behind the stack
+      if (rc) return rc;
+      ops[nops++] = LaneOp{e, slot};
+      npos = slot;
+      L.state_vlo = svlo + 1;
+    } else {
+      // the lane wrapped: the next-state stack is re-stored in full at its start (S-1 old frames + the new one)
+      int rc = lane_reserve(h, L, S, &slot);
+      if (rc) return rc;
+      for (int c = 0; c < S - 1; ++c) ops[nops++] = LaneOp{-(spos - (S - 2) + c) - 1, slot + c};
+      ops[nops++] = LaneOp{e, slot + S - 1};
+      npos = slot + S - 1;
+      L.state_vlo = L.written - S;
+    }
+    // record; the record slot being overwritten frees its lane's frames up to its own oldest one
+    const size_t rslot = (size_t)(h->total_adds % h->cap);
+    if (h->total_adds >= h->cap && h->rec_lane[rslot] >= 0) {
+      dqn_replay_s::Lane& old = h->lanes[(size_t)h->rec_lane[rslot]];
+      if (h->rec_vlo[rslot] > old.tail) old.tail = h->rec_vlo[rslot];
+    }
+    int rc = stage_record(h, spos, npos, actions[e], rewards[e], terminals[e]);
+    if (rc) return rc;
+    h->rec_lane[rslot] = e;
+    h->rec_vlo[rslot] = svlo;                                  // oldest frame this transition references
+    h->total_adds++;
+    L.last_pos = npos;
+  }
+  DQN_CUDA(cudaMemcpyAsync(h->ops_dev[turn], ops, (size_t)nops * sizeof(LaneOp), cudaMemcpyHostToDevice, st));
+  if (nops > 0) {
+    count_launch();
+    lane_scatter_kernel<<<dim3((h->pitch / 16 + 255) / 256, nops), 256, 0, st>>>(h->ops_dev[turn], static_cast<const uint8_t*>(d_frames),
+                                                                               h->frame_bytes, h->d_frames, h->pitch);
+    DQN_CUDA(cudaGetLastError());
+  }
+  DQN_CUDA(cudaEventRecord(h->ops_done[turn], st));
+  h->ops_turn ^= 1;
+  h->last_stream = st;
+  return 0;
+}
+
+extern "C" int dqn_replay_current_states(dqn_replay_t h, void* d_states, dqn_stream_t stream) {
+  DQN_REQUIRE(h && d_states, DQN_ERR_INVALID, "current_states: NULL argument");
+  DQN_REQUIRE(!h->lanes.empty(), DQN_ERR_STATE, "current_states: no actor lanes (dqn_replay_set_lanes)");
+  DeviceGuard g(h->device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int E = (int)h->lanes.size();
+  DQN_CUDA(cudaStreamSynchronize(st));                        // pos_host is reused by every call
+  for (int e = 0; e < E; ++e) {
+    DQN_REQUIRE(h->lanes[(size_t)e].has_state, DQN_ERR_STATE, "current_states: environment %d has no current state", e);
+    h->pos_host[e] = h->lanes[(size_t)e].last_pos;
+  }
+  DQN_CUDA(cudaMemcpyAsync(h->pos_dev, h->pos_host, (size_t)E * sizeof(int64_t), cudaMemcpyHostToDevice, st));
+  RingView rv;
+  dqn_replay_view_(h, &rv);
+  const int elems = h->frame_bytes;
+  DQN_REQUIRE(h->elem_bytes == 1, DQN_ERR_UNSUPPORTED, "current_states: uint8 frames only");
+  int64_t blocks = ((int64_t)E * elems + 255) / 256;
+  if (blocks > (int64_t)h->num_sms * 32) blocks = (int64_t)h->num_sms * 32;
+  count_launch();
+  stack_at_positions_kernel<<<(unsigned)blocks, 256, 0, st>>>(rv, h->pos_dev, E, elems, static_cast<uint8_t*>(d_states));
+  DQN_CUDA(cudaGetLastError());
   return 0;
 }
 

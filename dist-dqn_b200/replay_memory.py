@@ -261,6 +261,45 @@ class ReplayMemory(object):
             indices = self.sample_indices(k)
         return self.gather(self.upload_indices(indices))
 
+    # ------------------------------------------------------------------ lock-step actors on the device
+    def set_lanes(self, num_envs, frame_shape=(84, 84), frames_per_state=4, dtype=np.uint8):
+        """Switches the (empty) memory to lock-step actor mode: ``num_envs`` environments add one frame each per call of
+        ``add_batch`` and no frame passes through the host.  Creates the ring if it does not exist yet."""
+        if self._h is None:
+            probe = np.zeros(tuple(frame_shape) + ((frames_per_state,) if frames_per_state > 1 else ()), dtype)
+            self._ensure(probe)
+        _c.check(_c.lib.dqn_replay_set_lanes(self._h, int(num_envs)), "ReplayMemory.set_lanes")
+        self._lanes = int(num_envs)
+
+    def add_batch(self, frames, actions, rewards, terminals, episode_start):
+        """One preprocessed frame per environment (CUDA uint8 tensor [E, H, W], environment order) plus host sequences of E
+        actions / rewards / terminals / episode-start flags: what E calls of ``FrameBuffer.append`` + ``ReplayMemory.add``
+        do in the reference (dqn_agent.py:96-100), in one call.  A frame flagged ``episode_start`` is ``env.reset()``'s
+        observation: it starts a new window (the frame repeated frames_per_state times) and records no transition."""
+        E = self._lanes
+        frames = frames.contiguous()
+        if int(frames.shape[0]) != E:
+            raise RuntimeError("add_batch: expected %d frames, got %d" % (E, int(frames.shape[0])))
+        a = np.ascontiguousarray(actions, np.int32)
+        r = np.ascontiguousarray(rewards, np.float64)
+        t = np.ascontiguousarray(terminals, np.uint8)
+        s = np.ascontiguousarray(episode_start, np.uint8)
+        _c.check(_c.lib.dqn_replay_add_batch(self._h, E, frames.data_ptr(), a.ctypes.data, r.ctypes.data, t.ctypes.data,
+                                             s.ctypes.data, _c.current_stream()), "ReplayMemory.add_batch")
+        self._size = min(self._capacity, self._size + int(E - int(s.astype(bool).sum())))
+        self._last_next, self._last_next_pos = None, -1
+
+    def current_states(self, out=None):
+        """The E environments' current windows as a CUDA tensor [E, H, W, frames_per_state] (``FrameBuffer.get_state()``
+        of every environment), ready for ``Network.predict``."""
+        import torch
+        S, fshape, dt = self._stack
+        if out is None:
+            out = torch.empty((self._lanes,) + fshape + ((S,) if S > 1 else ()), dtype=torch.uint8,
+                              device=torch.device("cuda", self._device))
+        _c.check(_c.lib.dqn_replay_current_states(self._h, out.data_ptr(), _c.current_stream()), "ReplayMemory.current_states")
+        return out
+
     def flush(self):
         if self._h is not None:
             _c.check(_c.lib.dqn_replay_flush(self._h, _c.current_stream()), "ReplayMemory.flush")

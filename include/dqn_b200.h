@@ -128,6 +128,27 @@ int dqn_replay_flush(dqn_replay_t h, dqn_stream_t stream);
 int dqn_replay_seal(dqn_replay_t h, int32_t* stage, dqn_stream_t stream);
 int dqn_replay_ingest_staged(dqn_replay_t h, int32_t stage, const int32_t* pinned_idx, int32_t* d_idx, int32_t k,
                              dqn_stream_t stream);
+/* Lock-step actors on the device: the per-step actor work of the reference -- FrameBuffer.append +
+ * get_state + ReplayMemory.add for every environment (dqn_agent.py:96-100, frame_buffer.py:27-51) -- for E environments
+ * that step together, with no per-transition host call and no frame passing through the host.
+ *   dqn_replay_set_lanes(h, E): once, on the empty ring.  Environment e gets its own run of frame slots, so that the
+ *     frames of its stacks stay consecutive although the E environments append in turn.  Afterwards the ring only takes
+ *     dqn_replay_add_batch (dqn_replay_add / append_frames / push are refused).
+ *   dqn_replay_add_batch: one preprocessed frame per environment, d_frames = device [E][frame_bytes], in environment order.
+ *     episode_start[e] != 0: the frame is env.reset()'s observation -- FrameBuffer.clear() + append, i.e. the window becomes
+ *       that frame frames_per_state times (frame_buffer.py:35-36); no transition is recorded (actions/rewards/terminals[e]
+ *       are ignored).
+ *     otherwise: the frame is env.step(action[e])'s observation: it shifts environment e's window and the transition
+ *       (previous window, action, reward, new window, terminal) is recorded exactly as ReplayMemory.add would, in
+ *       environment order (logical indices and eviction follow deque(maxlen) over that order).
+ *     actions / rewards / terminals / episode_start are HOST arrays of E entries.
+ *   dqn_replay_current_states: the E current windows as stacks [E][frame elems][frames_per_state] (what
+ *     FrameBuffer.get_state() returns per environment), e.g. as the input of dqn_net_forward for batched acting. */
+int dqn_replay_set_lanes(dqn_replay_t h, int32_t num_envs);
+int dqn_replay_add_batch(dqn_replay_t h, int32_t num_envs, const void* d_frames, const int32_t* actions,
+                         const double* rewards, const uint8_t* terminals, const uint8_t* episode_start,
+                         dqn_stream_t stream);
+int dqn_replay_current_states(dqn_replay_t h, void* d_states, dqn_stream_t stream);
 /* ReplayMemory.size / capacity (replay_memory.py:25-29); host-side counters, no sync. */
 int dqn_replay_size(dqn_replay_t h, int64_t* size, int64_t* capacity);
 /* Frame-ring position that the next appended frame will get. */

@@ -67,7 +67,7 @@ def check_mode(precision, torch, dist, dp, network, replay_memory, helpers, rank
         ref0 = flat.clone()
         dist.broadcast(ref0, 0)
         same = bool(torch.equal(flat, ref0))                           # bit-identical weights on every rank
-        q = net.predict(batches[0][0])                                 # runs on the refreshed bf16 operand images
+        q = net.predict(gathered[0][0][0])                             # same probe states on every rank; runs on the refreshed bf16 operand images
         q0 = q.clone()
         dist.broadcast(q0, 0)
         same_q = bool(torch.equal(q, q0))

@@ -169,3 +169,88 @@ def test_frame_ring_overflow_and_bad_arguments_fail_loudly():
     rm = rm_mod.ReplayMemory(8)
     with pytest.raises(RuntimeError):
         rm.sample(3)
+
+
+def test_lock_step_actor_batch_add_equals_per_env_framebuffers_and_adds():
+    """E interleaved environments through ReplayMemory.add_batch (one device frame per environment per
+    call) against E FrameBuffers + one reference-semantics replay memory fed in environment order -- bit-exact, through
+    episode starts (dup-filled windows), terminals, eviction and wrap-around of the environments' frame lanes."""
+    _mods()
+    import torch
+    from frame_buffer import FrameBuffer
+    from oracle.replay_ref import ReplayRef
+    from replay_memory import ReplayMemory
+    E, S, cap, steps = 5, 4, 64, 60
+    rng = np.random.default_rng(11)
+    rm = ReplayMemory(cap, frame_capacity=E * 64)          # 64 slots per lane: every lane wraps during the run (~110 frames each)
+    rm.set_lanes(E)
+    ref = ReplayRef(cap)
+    fbs = [FrameBuffer(S) for _ in range(E)]
+    states = [None] * E
+    left = [0] * E                                          # steps until the environment's episode ends
+    for step in range(steps):
+        frames = rng.integers(0, 256, (E, 84, 84), dtype=np.uint8)
+        a = rng.integers(0, 6, E).astype(np.int32)
+        r = rng.integers(-1, 2, E).astype(np.float64)
+        t = np.zeros(E, np.uint8)
+        s = np.zeros(E, np.uint8)
+        for e in range(E):
+            if left[e] == 0:                                # env.reset(): FrameBuffer.clear + append, no transition
+                fbs[e].clear()
+                fbs[e].append(frames[e])
+                states[e] = fbs[e].get_state()
+                left[e] = int(rng.integers(1, 9))
+                s[e] = 1
+            else:
+                left[e] -= 1
+                t[e] = 1 if left[e] == 0 else 0
+                fbs[e].append(frames[e])
+                nxt = fbs[e].get_state()
+                ref.add(states[e], int(a[e]), float(r[e]), nxt, bool(t[e]))
+                states[e] = nxt
+        rm.add_batch(torch.from_numpy(frames).cuda(), a, r, t, s)
+        cur = rm.current_states().cpu().numpy()
+        for e in range(E):
+            assert np.array_equal(cur[e], states[e]), (step, e)
+    assert rm.size() == ref.size() == cap                  # the oldest transitions were evicted like deque(maxlen)
+    b = rm.sample(cap, indices=list(range(cap)))
+    st, nx = b.states.cpu().numpy(), b.next_states.cpu().numpy()
+    ac, rw, tm = b.actions.cpu().numpy(), b.rewards.cpu().numpy(), b.terminals.cpu().numpy()
+    for i, (s0, a0, r0, s1, t0) in enumerate(ref.memory):
+        assert np.array_equal(st[i], s0) and np.array_equal(nx[i], s1), i
+        assert ac[i] == a0 and rw[i] == r0 and bool(tm[i]) == t0, i
+
+
+def test_batched_actor_epsilon_greedy_matches_the_reference_rule():
+    """BatchedActor: epsilon decays before every roll, one roll per environment in environment order on Python's global
+    generator, greedy actions from ONE batched forward; an agent-style loop over 6 environments stays consistent with the
+    ring (sizes, finite Q-values)."""
+    _mods()
+    import envs
+    import network
+    from preprocess import BatchedActor
+    from replay_memory import ReplayMemory
+    from gpu_helpers import make_config
+    E = 6
+    cfg = make_config(network='cnn', minibatch_size=8, max_batch=8, init_random_action_prob=0.9, min_random_action_prob=0.1,
+                      random_action_explore_steps=50)
+    net = network.Network.create_network(cfg, (84, 84, 4), 6)
+    rm = ReplayMemory(500)
+    rm.set_lanes(E)
+    es = [envs.SyntheticAtariEnv('SyntheticPong-v0', num_actions=6, seed=e, frame_shape=(84, 84), min_len=5, max_len=12) for e in range(E)]
+    actor = BatchedActor(es, net, rm, cfg)
+    random.seed(4)
+    mirror = random.Random(4)
+    eps = cfg.init_random_action_prob
+    for _ in range(30):
+        nstep = sum(1 for x in actor._needs_reset if not x)
+        actor.step()
+        for e in range(nstep):                               # one decay, then one roll, per stepping environment
+            if eps > cfg.min_random_action_prob:
+                eps -= (cfg.init_random_action_prob - cfg.min_random_action_prob) / cfg.random_action_explore_steps
+            mirror.random()
+        assert abs(actor.random_action_prob - eps) < 1e-12
+        assert random.getstate() == mirror.getstate()
+    assert 0 < rm.size() <= 30 * E and actor.random_action_prob <= cfg.min_random_action_prob + 1e-9
+    q = net.predict(rm.current_states())
+    assert q.shape == (E, 6) and bool(q.isfinite().all())
