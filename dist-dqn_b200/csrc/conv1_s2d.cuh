@@ -103,9 +103,9 @@ __device__ __forceinline__ void load_stack(const Src& s, int pass, int b, const 
 
 // The producer warp's loop: every lane resolves tiles of the next table round, then one elected lane issues the copies.
 // slot_of(i) / wait_empty(i) are supplied by the kernel (raw ring slot and its "empty" wait of tile i).
-template <class FDst, class FWait, class FBar>
+template <class FDst, class FWait, class FBar, class FPost>
 __device__ __forceinline__ void producer_loop(const Src& s, int pass, int b0, int bstep, int ntiles, int64_t (*tab)[4], FDst dst_of,
-                                              FWait wait_empty, FBar bar_of) {
+                                              FWait wait_empty, FBar bar_of, FPost after_issue) {
   const int lane = threadIdx.x & 31;
   const bool ring = (pass ? s.x[1] : s.x[0]) == nullptr;
   for (int base = 0; base < ntiles; base += TAB_TILES) {
@@ -119,6 +119,7 @@ __device__ __forceinline__ void producer_loop(const Src& s, int pass, int b0, in
         const int i = base + t;
         wait_empty(i);
         load_stack(s, pass, b0 + i * bstep, tab[t], dst_of(i), bar_of(i));
+        after_issue(i);
       }
     }
     __syncwarp();
@@ -236,28 +237,6 @@ __host__ __device__ constexpr uint32_t make_idesc_ab(int M, int N, bool a_mn_maj
   return (1u << 4) | ((a_bf16 ? 1u : 0u) << 7) | ((b_bf16 ? 1u : 0u) << 10) | ((a_mn_major ? 1u : 0u) << 15) |
          ((b_mn_major ? 1u : 0u) << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
-// 16 consecutive accumulator columns of this thread's TMEM lane; the caller issues tcgen05.wait::ld before using them
-__device__ __forceinline__ void tmem_ld16_nowait(uint32_t taddr, uint32_t r[16]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-      : "r"(taddr)
-      : "memory");
-}
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float v[16]) {
-  uint32_t r[16];
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-      : "r"(taddr)
-      : "memory");
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
-}
-
 template <bool PLANAR>
 __global__ void __launch_bounds__(FWD_WARPS * 32, 1) conv1_s2d_fwd_kernel(FwdArgs a) {
   extern __shared__ uint8_t smem_raw[];
@@ -313,7 +292,7 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, 1) conv1_s2d_fwd_kernel(FwdArg
     producer_loop(
         a.src, pass, b0, nper, ntiles, tab, [&](int i) { return sbase + (i & 1) * RAW_BYTES; },
         [&](int i) { mbar_wait(&raw_empty[i & 1], ((i >> 1) & 1) ^ 1); trace_stamp(a.trace, i, 0); },
-        [&](int i) { return &raw_full[i & 1]; });
+        [&](int i) { return &raw_full[i & 1]; }, [](int) {});
   } else if (warp == 1) {
     // ---------------------------------------------------------------- MMA issuer (f16 image x f16 weights: the two
     // operands of a kind::f16 MMA must share one format -- f16 x bf16 is an illegal instruction)
@@ -459,7 +438,7 @@ template <bool PLANAR>
 __global__ void __launch_bounds__(NWARPS * 32, 1) conv1_s2d_wgrad_kernel(WgradArgs a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align_smem(smem_raw);
-  __shared__ uint64_t ld_full[2], ld_empty[2], op_full, op_empty;
+  __shared__ uint64_t stk_full[2], ga_full[2], ld_empty[2], op_full, op_empty;   // stack landed / gradient + arg-max landed / both consumed
   __shared__ uint32_t tmem_slot;
   __shared__ int64_t tab[TAB_TILES][4];
   const int tid = threadIdx.x, lane = tid & 31;
@@ -468,7 +447,7 @@ __global__ void __launch_bounds__(NWARPS * 32, 1) conv1_s2d_wgrad_kernel(WgradAr
   const int ntiles = b0 < a.B ? (a.B - b0 + G - 1) / G : 0;
   if (tid == 0) {
 #pragma unroll
-    for (int i = 0; i < 2; ++i) { mbar_init(&ld_full[i], 2); mbar_init(&ld_empty[i], WG_BUILD_WARPS); }   // ld_full: two expect_tx arrivals (gradient + arg-max, stack)
+    for (int i = 0; i < 2; ++i) { mbar_init(&stk_full[i], 1); mbar_init(&ga_full[i], 1); mbar_init(&ld_empty[i], WG_BUILD_WARPS); }
     mbar_init(&op_full, WG_BUILD_WARPS);
     mbar_init(&op_empty, 1);
     fence_mbar_init();
@@ -483,7 +462,10 @@ __global__ void __launch_bounds__(NWARPS * 32, 1) conv1_s2d_wgrad_kernel(WgradAr
   tc_fence_after();
   const uint32_t tmem = tmem_slot;
   const uint32_t sbase = smem_u32(smem);
-  pdl_wait();
+  // Only the output gradient and the arg-max bytes come from the predecessor in the stream (conv2's data gradient); the
+  // frames were in place before the step's first kernel finished (every kernel of the chain waits for its predecessor
+  // before it lets its successor launch).  So the stack of the first sample is fetched and its image built BEFORE the
+  // PDL wait, in the shadow of the predecessor; only the producer thread waits, right before it touches dactg / arg.
   pdl_trigger();                                              // see the forward kernel
   float colsum[2][8];                                          // bias gradient: this thread's (m, channel chunk) items
 #pragma unroll
@@ -494,14 +476,15 @@ __global__ void __launch_bounds__(NWARPS * 32, 1) conv1_s2d_wgrad_kernel(WgradAr
     // ---------------------------------------------------------------- producer: stack + gradient + arg-max of a sample
     producer_loop(
         a.src, 0, b0, G, ntiles, tab, [&](int i) { return sbase + (i & 1) * RAW_BYTES; },
+        [&](int i) { mbar_wait(&ld_empty[i & 1], ((i >> 1) & 1) ^ 1); },
+        [&](int i) { return &stk_full[i & 1]; },
         [&](int i) {
           const int rb = i & 1, b = b0 + i * G;
-          mbar_wait(&ld_empty[rb], ((i >> 1) & 1) ^ 1);
-          mbar_expect_tx(&ld_full[rb], WG_GRAD_BYTES + WG_ARG_BYTES);
-          bulk_g2s(sbase + WG_OFF_GA + rb * WG_GA_SLOT, a.dactg + (size_t)b * NWIN * 32, WG_GRAD_BYTES, &ld_full[rb]);
-          bulk_g2s(sbase + WG_OFF_GA + rb * WG_GA_SLOT + 8192, a.arg + (size_t)b * NWIN * 32, WG_ARG_BYTES, &ld_full[rb]);
-        },
-        [&](int i) { return &ld_full[i & 1]; });
+          if (i == 0) pdl_wait();
+          mbar_expect_tx(&ga_full[rb], WG_GRAD_BYTES + WG_ARG_BYTES);
+          bulk_g2s(sbase + WG_OFF_GA + rb * WG_GA_SLOT, a.dactg + (size_t)b * NWIN * 32, WG_GRAD_BYTES, &ga_full[rb]);
+          bulk_g2s(sbase + WG_OFF_GA + rb * WG_GA_SLOT + 8192, a.arg + (size_t)b * NWIN * 32, WG_ARG_BYTES, &ga_full[rb]);
+        });
   } else if (warp == 1) {
     // ---------------------------------------------------------------- MMA issuer
     constexpr uint32_t idesc = make_idesc(TM, 32, true, true);
@@ -538,9 +521,10 @@ __global__ void __launch_bounds__(NWARPS * 32, 1) conv1_s2d_wgrad_kernel(WgradAr
     const int bt = tid - WG_BUILD_WARP0 * 32;
     for (int i = 0; i < ntiles; ++i) {
       const int rb = i & 1;
-      mbar_wait(&ld_full[rb], (i >> 1) & 1);
+      mbar_wait(&stk_full[rb], (i >> 1) & 1);
       if (i > 0) mbar_wait(&op_empty, (i - 1) & 1);             // the previous sample's MMAs have read the operands
       build_image<PLANAR, false>(smem + rb * RAW_BYTES, smem + WG_OFF_IMG, bt);
+      mbar_wait(&ga_full[rb], (i >> 1) & 1);
       const uint8_t* ga = smem + WG_OFF_GA + rb * WG_GA_SLOT;
 #pragma unroll
       for (int q = 0; q < 2; ++q) {

@@ -58,6 +58,7 @@ struct FcFusedArgs {
   long long* step;
   double gamma;
   int B, A, loss_kind;
+  unsigned long long* trace;      // debugging (DQN_S2D_TRACE=1): CTA 0 of fc_td_cluster_kernel stamps clock64() per phase at trace[1080 + i]
 };
 
 __global__ void __launch_bounds__(TT) fc_td_fused_kernel(FcFusedArgs a) {

@@ -18,6 +18,7 @@
 #include "umma_core.cuh"
 #include "fc_fused.cuh"
 #include "conv1_s2d.cuh"
+#include "fc_cluster.cuh"
 
 #include <cmath>
 #include <cstdlib>
@@ -708,6 +709,7 @@ struct dqn_net_s {
   cudaStream_t side3 = nullptr;                     // head weight gradient + loss (fused fc/TD path)
   bool no_resident = false;                         // DQN_NO_RESIDENT=1: im2col gathers from L2 instead of a shared-memory resident input block
   bool no_fused_fc = true;                          // DQN_FUSED_FC=1: fc forward / TD head / fc dgrad as one launch (experimental)
+  bool fc_cluster = true;                           // B <= 32: fc forward / TD head / fc dgrad as one 8-CTA cluster launch (DQN_NO_FC_CLUSTER=1: off)
   bool conv1_s2d = false;                           // reference conv net, bf16: conv1 forward / weight gradient in the space-to-depth formulation
   bool fuse_gather = true;                          // ... reading the frames straight from the replay ring in dqn_train_step (DQN_NO_FUSED_GATHER=1: off)
   cudaEvent_t ev_fork[3] = {}, ev_join = nullptr, ev_x = nullptr, ev_join2 = nullptr, ev_head = nullptr;
@@ -877,6 +879,7 @@ extern "C" int dqn_net_create(dqn_net_t* out, int32_t arch, const int32_t* in_sh
     { const char* nr = getenv("DQN_NO_RESIDENT"); h->no_resident = nr && nr[0] == '1'; }
     { const char* nf = getenv("DQN_FUSED_FC"); h->no_fused_fc = !(nf && nf[0] == '1'); }
     { const char* ng = getenv("DQN_NO_FUSED_GATHER"); h->fuse_gather = !(ng && ng[0] == '1'); }
+    { const char* nc = getenv("DQN_NO_FC_CLUSTER"); h->fc_cluster = !(nc && nc[0] == '1'); }
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_head, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_x, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_join2, cudaEventDisableTiming);
@@ -1150,7 +1153,7 @@ static void launch_fwd_res_u8(umma::FwdArgsT a, int npass, int num_sms, cudaStre
   launch_pdl(umma::umma_fwd_res_u8_kernel<G, NTILE>, grid, dim3(umma::TT), smem, st, 1, a);
 }
 // DQN_S2D_TRACE=1: CTA 0 of the conv1 forward kernel stamps clock64() per (tile, pipeline event) here (dqn_debug_trace)
-static __device__ unsigned long long g_s2d_trace[60 * 8 + 160 * 4];
+static __device__ unsigned long long g_s2d_trace[60 * 8 + 160 * 4 + 16];
 static unsigned long long* s2d_trace_ptr() {
   static unsigned long long* p = nullptr;
   static bool init = false;
@@ -1162,7 +1165,7 @@ static unsigned long long* s2d_trace_ptr() {
   return p;
 }
 extern "C" int dqn_debug_trace(unsigned long long* host, int32_t n) {
-  DQN_REQUIRE(host && n > 0 && n <= 60 * 8 + 160 * 4, DQN_ERR_INVALID, "debug_trace: bad argument");
+  DQN_REQUIRE(host && n > 0 && n <= 60 * 8 + 160 * 4 + 16, DQN_ERR_INVALID, "debug_trace: bad argument");
   DQN_CUDA(cudaDeviceSynchronize());
   DQN_CUDA(cudaMemcpyFromSymbol(host, g_s2d_trace, (size_t)n * 8));
   return 0;
@@ -1534,7 +1537,9 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
     const float* ps[2] = {h->online, h->target};
     const int ids[2] = {0, 1};
     // reference architecture in tensor-core mode: fc forward (both nets) + head + TD + fc data gradient are one kernel
-    const bool fused = h->precision == 1 && !nat && h->F == umma::FCF && h->A <= umma::FC_AP && !h->no_fused_fc;
+    const bool fc_ok = h->precision == 1 && !nat && h->F == umma::FCF && h->A <= umma::FC_AP;
+    const bool fused_cl = fc_ok && h->fc_cluster && h->no_fused_fc && k <= umma::fcc::MAXB;      // one cluster launch (small minibatches)
+    const bool fused = fused_cl || (fc_ok && !h->no_fused_fc);
     int rc = h->precision == 1 ? run_trunk_tc(h, 2, xs, ids, k, st, fused ? 3 : 4, ring) : run_trunk(h, 2, xs, ps, ids, k, st);
     if (rc) return rc;
     const float* w5 = h->online + h->tensors[8].off;
@@ -1554,8 +1559,15 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       fa.a4 = h->act[0][3]; fa.qout = d_q; fa.se = h->se; fa.g = h->g;
       fa.dh_bf = h->dact_bf[3]; fa.dx = h->dact_bf[2];
       fa.step = h->step; fa.gamma = h->hyper.gamma; fa.B = k; fa.A = h->A; fa.loss_kind = h->hyper.loss;
+      fa.trace = s2d_trace_ptr();
       StageScope sc(h, DQN_STAGE_FC_TD_FUSED, st);
-      launch_pdl(umma::fc_td_fused_kernel, dim3((k + umma::TM - 1) / umma::TM), dim3(umma::TT), umma::FC_SMEM, st, 1, fa);
+      if (fused_cl) {
+        static bool once_cl = (set_smem(umma::fcc::fc_td_cluster_kernel, umma::fcc::SMEM), true);
+        (void)once_cl;
+        launch_pdl(umma::fcc::fc_td_cluster_kernel, dim3(1, 1, umma::fcc::CL), dim3(umma::fcc::THREADS), umma::fcc::SMEM, st, umma::fcc::CL, fa);
+      } else {
+        launch_pdl(umma::fc_td_fused_kernel, dim3((k + umma::TM - 1) / umma::TM), dim3(umma::TT), umma::FC_SMEM, st, 1, fa);
+      }
     } else {
     StageScope sc(h, DQN_STAGE_TD_HEAD, st);
     if (h->F == 256)

@@ -1,0 +1,61 @@
+"""Device timeline of one graph-replayed update (kernel start / duration from CUPTI through torch.profiler).
+    python tools/timeline.py [--batch 32]"""
+import argparse
+import os
+import random
+import sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "dist-dqn_b200"))
+ap = argparse.ArgumentParser(); ap.add_argument("--batch", type=int, default=32); ap.add_argument("--eager", action="store_true")
+a = ap.parse_args()
+import torch
+import __graft_entry__ as ge
+ge.build()
+import bench, _cabi as c, network, replay_memory
+from torch.profiler import profile, ProfilerActivity
+dev = torch.device("cuda", 0); torch.cuda.set_device(0)
+cfg = bench.atari_config(a.batch, "cnn", "bf16"); cfg.device_index = 0
+net = network.Network.create_network(cfg, (84, 84, 4), 6)
+a.capacity = 100000
+rm = bench._make_ring(a, torch, c, replay_memory, 0, 0, dev)
+tab = torch.tensor([random.sample(range(rm.size()), a.batch) for _ in range(64)], dtype=torch.int32, device=dev)
+d_idx = torch.empty(a.batch, dtype=torch.int32, device=dev)
+d_idx.copy_(tab[0])
+side = torch.cuda.Stream()
+with torch.cuda.stream(side):
+    for _ in range(3):
+        net.train_step(rm, a.batch, d_indices=d_idx)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=side):
+        net.train_step(rm, a.batch, d_indices=d_idx)
+
+    def step(i):
+        d_idx.copy_(tab[i % 64], non_blocking=True)
+        if a.eager:
+            net.train_step(rm, a.batch, d_indices=d_idx)
+        else:
+            g.replay()
+    for i in range(20):
+        step(i)
+    torch.cuda.synchronize()
+    with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+        for i in range(6):
+            step(i)
+        torch.cuda.synchronize()
+evs = [e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA]
+evs.sort(key=lambda e: e.time_range.start)
+# split into steps at the index copy (memcpy DtoD) that precedes every update
+steps, cur = [], []
+for e in evs:
+    if "Memcpy" in e.name or "memcpy" in e.name:
+        if cur:
+            steps.append(cur)
+        cur = []
+    cur.append(e)
+steps.append(cur)
+st = steps[-2]
+t0 = st[0].time_range.start
+print("kernels of one update (us from the index copy): start, duration, name")
+for e in st:
+    print("%8.2f %7.2f  %s" % (e.time_range.start - t0, e.time_range.end - e.time_range.start, e.name[:90]))
+print("update period: %.2f us" % (steps[-1][0].time_range.start - t0))
