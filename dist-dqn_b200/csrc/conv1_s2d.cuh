@@ -407,9 +407,15 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, 1) conv1_s2d_fwd_kernel(FwdArg
     }
   }
   pdl_trigger();
+  // exit stamp: the latest warp's arrival (a stamp taken right AFTER a __syncthreads records the barrier's issue, not
+  // its release: BAR.SYNC.DEFER_BLOCKING lets the warp run on until it touches barrier-protected state)
+  if (a.trace && lane == 0 && blockIdx.x < 160) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    atomicMax(a.trace + 480 + 4 * blockIdx.x + 3, t);
+  }
   tc_fence_before();
   __syncthreads();
-  if (tid == 0) trace_cta(a.trace, 3);
   if (warp == 1) tmem_dealloc(tmem, 256);
 }
 
