@@ -129,6 +129,18 @@ head_wgrad_kernel(const float* __restrict__ h_on, const float* __restrict__ g, c
   int b = blockIdx.y * per_split;
   const int B = min(Btot, b + per_split);
   out += (size_t)blockIdx.y * (size_t)((F + 1) * A);
+  for (; b + 16 <= B; b += 16) {            // 16 samples' loads in flight at once (the kernel is a chain of L2 latencies)
+    float hv[16], gv[16];
+    int av[16];
+#pragma unroll
+    for (int u = 0; u < 16; ++u) {
+      hv[u] = j < F ? h_on[(size_t)(b + u) * F + jj] : 1.f;
+      gv[u] = g[b + u];
+      av[u] = actions[b + u];
+    }
+#pragma unroll
+    for (int u = 0; u < 16; ++u) acc[u & 3] += (av[u] == a) ? hv[u] * gv[u] : 0.f;
+  }
   for (; b + 4 <= B; b += 4) {
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
@@ -458,29 +470,43 @@ __global__ void __launch_bounds__(256) peer_sum_kernel(OptArgs a, int seg_base, 
   }
 }
 
-// loss = mean_b se_b + reg * sum_{reg tensors} ||w||^2 / 2   (network.py:150-152); one CTA.
-__global__ void __launch_bounds__(256) loss_kernel(OptArgs a, const float* __restrict__ se, int B, float* __restrict__ out) {
-  __shared__ float red[256];
+// loss = mean_b se_b + reg * sum_{reg tensors} ||w||^2 / 2   (network.py:150-152); one CTA.  The weights are not written by
+// any kernel of the step before the optimizer, so the regularisation sum runs BEFORE the PDL wait, in the shadow of the
+// kernels that produce the squared errors.
+constexpr int LOSS_THREADS = 1024;
+__global__ void __launch_bounds__(LOSS_THREADS) loss_kernel(OptArgs a, const float* __restrict__ se, int B, float* __restrict__ out) {
+  __shared__ float red[LOSS_THREADS / 32];
   pdl_trigger();
-  pdl_wait();
-  float s = 0.f;
-  for (int b = threadIdx.x; b < B; b += 256) s += se[b];
-  s /= (float)B;
   float r = 0.f;
   for (int k = 0; k < a.nseg; ++k) {
     const Seg sg = a.seg[k];
-    for (int i = threadIdx.x; i < sg.reg_len; i += 256) {
-      const float w = a.w[(size_t)sg.off + i];
-      r = fmaf(w, w, r);
+    const float* w = a.w + (size_t)sg.off;
+    int i0 = 0;
+    if ((sg.off & 3) == 0) {                       // 16-byte aligned: four weights per load
+      const int n4 = sg.reg_len >> 2;
+      for (int i = threadIdx.x; i < n4; i += LOSS_THREADS) {
+        const float4 v = __ldg(reinterpret_cast<const float4*>(w) + i);
+        r = fmaf(v.x, v.x, r); r = fmaf(v.y, v.y, r); r = fmaf(v.z, v.z, r); r = fmaf(v.w, v.w, r);
+      }
+      i0 = n4 << 2;
     }
+    for (int i = i0 + threadIdx.x; i < sg.reg_len; i += LOSS_THREADS) r = fmaf(w[i], w[i], r);
   }
-  red[threadIdx.x] = s + 0.5f * a.reg * r;
+  r *= 0.5f * a.reg;
+  pdl_wait();
+  float s = 0.f;
+  for (int b = threadIdx.x; b < B; b += LOSS_THREADS) s += se[b];
+  s = s / (float)B + r;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
   __syncthreads();
-  for (int o = 128; o > 0; o >>= 1) {
-    if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
-    __syncthreads();
+  if (threadIdx.x < 32) {
+    s = red[threadIdx.x];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (threadIdx.x == 0) *out = s;
   }
-  if (threadIdx.x == 0) *out = red[0];
 }
 
 // Publishes "my gradient of step *step is complete" to every rank's flag array (including my own).
@@ -705,14 +731,14 @@ struct dqn_net_s {
   long long dp_timeout_ns = 120LL * 1000000000LL;     // dqn_net_dp_set_timeout
   // weight-gradient kernels run on a forked stream, concurrently with the data-gradient chain (captured into the
   // step's CUDA graph as a parallel branch)
-  cudaStream_t side = nullptr, side2 = nullptr;     // side2: early half of the data-parallel exchange
-  cudaStream_t side3 = nullptr;                     // head weight gradient + loss (fused fc/TD path)
+  cudaStream_t side = nullptr, side2 = nullptr;     // side2: head weight gradient, early half of the data-parallel exchange
+  cudaStream_t side3 = nullptr;                     // fc weight gradient + loss
   bool no_resident = false;                         // DQN_NO_RESIDENT=1: im2col gathers from L2 instead of a shared-memory resident input block
   bool no_fused_fc = true;                          // DQN_FUSED_FC=1: fc forward / TD head / fc dgrad as one launch (experimental)
   bool fc_cluster = true;                           // B <= 32: fc forward / TD head / fc dgrad as one 8-CTA cluster launch (DQN_NO_FC_CLUSTER=1: off)
   bool conv1_s2d = false;                           // reference conv net, bf16: conv1 forward / weight gradient in the space-to-depth formulation
   bool fuse_gather = true;                          // ... reading the frames straight from the replay ring in dqn_train_step (DQN_NO_FUSED_GATHER=1: off)
-  cudaEvent_t ev_fork[3] = {}, ev_join = nullptr, ev_x = nullptr, ev_join2 = nullptr, ev_head = nullptr;
+  cudaEvent_t ev_fork[3] = {}, ev_join = nullptr, ev_x = nullptr, ev_join2 = nullptr, ev_head = nullptr, ev_loss = nullptr;
   // bf16 tensor-core mode (precision == 1; DQN_ARCH_CNN only)
   int precision = 0;
   __nv_bfloat16* act_bf[2][4] = {};
@@ -881,6 +907,7 @@ extern "C" int dqn_net_create(dqn_net_t* out, int32_t arch, const int32_t* in_sh
     { const char* ng = getenv("DQN_NO_FUSED_GATHER"); h->fuse_gather = !(ng && ng[0] == '1'); }
     { const char* nc = getenv("DQN_NO_FC_CLUSTER"); h->fc_cluster = !(nc && nc[0] == '1'); }
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_head, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_loss, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_x, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_join2, cudaEventDisableTiming);
     for (int i = 0; i < 3 && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&h->ev_fork[i], cudaEventDisableTiming);
@@ -907,6 +934,7 @@ extern "C" int dqn_net_destroy(dqn_net_t h) {
   if (h->side2) cudaStreamDestroy(h->side2);
   if (h->side3) cudaStreamDestroy(h->side3);
   if (h->ev_head) cudaEventDestroy(h->ev_head);
+  if (h->ev_loss) cudaEventDestroy(h->ev_loss);
   if (h->ev_x) cudaEventDestroy(h->ev_x);
   if (h->ev_join2) cudaEventDestroy(h->ev_join2);
   for (int i = 0; i < 3; ++i) if (h->ev_fork[i]) cudaEventDestroy(h->ev_fork[i]);
@@ -1516,7 +1544,7 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
     fill_segs(h, &oa, nsplit, true);
     if (d_loss) {
       StageScope sc(h, DQN_STAGE_LOSS, st);
-      loss_kernel<<<1, 256, 0, st>>>(oa, h->se, k, d_loss);
+      loss_kernel<<<1, LOSS_THREADS, 0, st>>>(oa, h->se, k, d_loss);
     }
     if (mode == 1 && include_reg) {
       // grad already holds the data term; add reg*w in place through the reduce kernel (partial == grad)
@@ -1544,7 +1572,7 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
     if (rc) return rc;
     const float* w5 = h->online + h->tensors[8].off;
     cudaStream_t sd = h->side;
-    cudaStream_t sh = h->side3;                        // head weight gradient, loss, fc weight gradient
+    cudaStream_t sh = h->side3;                        // fc weight gradient, loss
     if (fused) {
       static bool once = (set_smem(umma::fc_td_fused_kernel, umma::FC_SMEM), true);
       (void)once;
@@ -1590,19 +1618,17 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
     DQN_CUDA(cudaEventRecord(h->ev_fork[0], st));
     DQN_CUDA(cudaStreamWaitEvent(sd, h->ev_fork[0], 0));
     DQN_CUDA(cudaStreamWaitEvent(sh, h->ev_fork[0], 0));
+    DQN_CUDA(cudaStreamWaitEvent(h->side2, h->ev_fork[0], 0));
     {
-    StageScope sc(h, DQN_STAGE_HEAD_WGRAD, sh);
+    // the head weight gradient gets a branch of its own (in data-parallel mode the early exchange follows it there)
+    StageScope sc(h, DQN_STAGE_HEAD_WGRAD, h->side2);
     h->head_nsplit = (k + 31) / 32 > 16 ? 16 : (k + 31) / 32;
     const int head_per = (k + h->head_nsplit - 1) / h->head_nsplit;
     h->head_nsplit = (k + head_per - 1) / head_per;
-    launch_pdl(head_wgrad_kernel, dim3(((h->F + 1) * h->A + 255) / 256, h->head_nsplit), dim3(256), 0, sh, 1, h->act[0][3],
+    launch_pdl(head_wgrad_kernel, dim3(((h->F + 1) * h->A + 255) / 256, h->head_nsplit), dim3(256), 0, h->side2, 1, h->act[0][3],
                h->g, d_actions, k, head_per, h->F, h->A, h->head_partial);
     }
-    if (d_loss) {
-      fill_segs(h, &oa, nsplit, false);
-      StageScope sc(h, DQN_STAGE_LOSS, sh);
-      launch_pdl(loss_kernel, dim3(1), dim3(256), 0, sh, 1, oa, h->se, k, d_loss);
-    }
+    if (mode != 2) DQN_CUDA(cudaEventRecord(h->ev_join2, h->side2));
     // data-parallel: as soon as the gradients of conv3, fc and the head (segments 2..4, 72% of the parameters) exist,
     // a third stream publishes them and sums them over the ranks into the local flat gradient buffer, in the shadow
     // of the rest of the backward pass
@@ -1678,6 +1704,16 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       else launch_wgrad<C1, float>(h, 0, d_states, k, st, &nsplit[0]);
     }
     fill_segs(h, &oa, nsplit, false);
+    if (d_loss) {
+      // last on its stream, so that no weight-gradient kernel queues behind it; the optimizer must not overwrite the
+      // weights before it has read them (ev_loss)
+      {
+        StageScope sc(h, DQN_STAGE_LOSS, sh);
+        launch_pdl(loss_kernel, dim3(1), dim3(LOSS_THREADS), 0, sh, 1, oa, h->se, k, d_loss);
+      }
+      DQN_CUDA(cudaEventRecord(h->ev_loss, sh));
+      DQN_CUDA(cudaStreamWaitEvent(st, h->ev_loss, 0));
+    }
     // join
     DQN_CUDA(cudaEventRecord(h->ev_join, sd));
     DQN_CUDA(cudaStreamWaitEvent(st, h->ev_join, 0));
@@ -1692,8 +1728,8 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
         launch_pdl(reduce_grad_kernel, g01, dim3(256), 0, st, 1, oa, h->dp_grad, 0.f, 1,
                    PublishArgs{h->dp_peer_flags_dev, h->dp_counter + 1, h->dp_rank, h->dp_world, 1, 0});
       }
-      DQN_CUDA(cudaStreamWaitEvent(st, h->ev_join2, 0));
     }
+    DQN_CUDA(cudaStreamWaitEvent(st, h->ev_join2, 0));
     if (mode == 1) {
       dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
       StageScope sc(h, DQN_STAGE_REDUCE_GRAD, st);

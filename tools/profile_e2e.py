@@ -71,3 +71,18 @@ for _ in range(3000):
 pr.disable()
 torch.cuda.synchronize()
 pstats.Stats(pr).sort_stats("tottime").print_stats(14)
+# device timeline of three consecutive end-to-end updates (CUPTI through torch.profiler)
+from torch.profiler import profile, ProfilerActivity
+with profile(activities=[ProfilerActivity.CUDA]) as prof:
+    for _ in range(8):
+        one()
+    torch.cuda.synchronize()
+evs = [e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA]
+evs.sort(key=lambda e: e.time_range.start)
+ing = [i for i, e in enumerate(evs) if "ingest" in e.name]
+if len(ing) >= 5:
+    t0 = evs[ing[3]].time_range.start
+    print("device timeline of one end-to-end update (us from its ingest kernel): start, duration, name")
+    for e in evs[ing[3]:ing[4] + 1]:
+        print("%8.2f %7.2f  %s" % (e.time_range.start - t0, e.time_range.end - e.time_range.start, e.name[:80]))
+    print("period: %s" % ["%.1f" % (evs[ing[i + 1]].time_range.start - evs[ing[i]].time_range.start) for i in range(len(ing) - 1)])
