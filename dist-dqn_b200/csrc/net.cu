@@ -211,7 +211,15 @@ struct OptArgs {
   int flag_slot;                         // which flag array guards the peer-summed segments
   long long timeout_ns;                  // how long a rank waits for its peers' flags before it reports them missing
   unsigned long long* err;               // device word: last step whose wait timed out (0 = none); read by dqn_net_dp_status
+  unsigned long long* trace;             // DQN_S2D_TRACE=1: globaltimer stamps of the exchange (tools/trace_dp.py), else null
 };
+__device__ __forceinline__ void dp_stamp(unsigned long long* trace, int slot, bool max_of_all = false) {
+  if (!trace) return;
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  if (max_of_all) atomicMax(trace + 1136 + slot, t);
+  else trace[1136 + slot] = t;
+}
 
 __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
   unsigned long long v;
@@ -324,7 +332,10 @@ __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs a) {
   const long long step = *a.step;
   if (a.world > 1) {
     // wait until every rank has published its gradient of this step
+    const bool tr0 = threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0;
+    if (tr0) dp_stamp(a.trace, 24);
     if (threadIdx.x == 0) wait_peer_flags(a, (unsigned long long)step);
+    if (tr0) dp_stamp(a.trace, 25);
     __syncthreads();
   }
   if (i >= s.len) return;
@@ -388,6 +399,7 @@ __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs a) {
     } break;
   }
   a.w[p] = w;
+  if (threadIdx.x == 0) dp_stamp(a.trace, 26, true);
   if (tiled) {
     const int k = i / s.N, n = i - k * s.N;
     const __nv_bfloat16 v = __float2bfloat16_rn(w);
@@ -414,11 +426,17 @@ struct PublishArgs {
   int rank, world;
   int flag_slot;                           // flag array to raise: 0 = early segments, 1 = final segment(s)
   int seg_base;                            // first segment this launch covers (gridDim.y segments)
+  int sys_release;                         // 1: raise the flags with a system-scope release store (see reduce_grad_kernel)
 };
+static int dp_sys_release() {
+  static const int v = [] { const char* e = getenv("DQN_DP_SYS_RELEASE"); return e && e[0] == '1' ? 1 : 0; }();
+  return v;
+}
 
 __global__ void __launch_bounds__(256) reduce_grad_kernel(OptArgs a, float* __restrict__ grad, float reg, int by_parity,
                                                           PublishArgs pub) {
   pdl_wait();
+  if (pub.peer_flags && threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0) dp_stamp(a.trace, 8 * pub.flag_slot);
   const Seg s = a.seg[blockIdx.y + pub.seg_base];
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (by_parity) grad += (size_t)(*a.step & 1) * (size_t)a.P;     // exchange block: buffer of this step's parity
@@ -438,13 +456,22 @@ __global__ void __launch_bounds__(256) reduce_grad_kernel(OptArgs a, float* __re
     }
     __syncthreads();
     if (last) {
-      if (threadIdx.x == 0) *pub.done_counter = 0;
+      if (threadIdx.x == 0) { *pub.done_counter = 0; dp_stamp(a.trace, 8 * pub.flag_slot + 1); }
       if ((int)threadIdx.x < pub.world) {
-        __threadfence();                  // acquire side of the counter: every block's stores are visible here
-        const unsigned long long v = (unsigned long long)*a.step;   // the release store below is the system-scope fence
-        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(pub.peer_flags[threadIdx.x] + 8 * pub.flag_slot + pub.rank),
+        // The gradient lives in THIS GPU's memory and the peers read it through this GPU's L2, so a gpu-scope fence
+        // (acquire side of the counter + every block's stores ordered before the flag) is what the flag store needs;
+        // a system-scope release here cost 2.5 us per publish (tools/trace_dp.py).  DQN_DP_SYS_RELEASE=1 restores it.
+        __threadfence();
+        const unsigned long long v = (unsigned long long)*a.step;
+        if (pub.sys_release)
+          asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(pub.peer_flags[threadIdx.x] + 8 * pub.flag_slot + pub.rank),
+                       "l"(v)
+                       : "memory");
+        else
+          asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(pub.peer_flags[threadIdx.x] + 8 * pub.flag_slot + pub.rank),
                      "l"(v)
                      : "memory");
+        if (threadIdx.x == 0) dp_stamp(a.trace, 8 * pub.flag_slot + 2);
       }
     }
   }
@@ -458,7 +485,10 @@ __global__ void __launch_bounds__(256) peer_sum_kernel(OptArgs a, int seg_base, 
   const Seg s = a.seg[blockIdx.y + seg_base];
   const int i = (blockIdx.x * blockDim.x + threadIdx.x) * 4;            // 4 consecutive parameters per thread: 16-byte peer loads
   const long long step = *a.step;
+  const bool tr0 = threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0;
+  if (tr0) dp_stamp(a.trace, 16);
   if (threadIdx.x == 0) wait_peer_flags(a, (unsigned long long)step);
+  if (tr0) dp_stamp(a.trace, 17);
   __syncthreads();
   if (i >= s.len) return;
   const size_t p = (size_t)s.off + i;                                  // segments start at multiples of 4 floats
@@ -468,6 +498,7 @@ __global__ void __launch_bounds__(256) peer_sum_kernel(OptArgs a, int seg_base, 
   } else {
     for (int e = 0; i + e < s.len; ++e) gsum[p + e] = peer_sum1(a, gi + e);
   }
+  if (threadIdx.x == 0) dp_stamp(a.trace, 18, true);
 }
 
 // loss = mean_b se_b + reg * sum_{reg tensors} ||w||^2 / 2   (network.py:150-152); one CTA.  The weights are not written by
@@ -1181,7 +1212,7 @@ static void launch_fwd_res_u8(umma::FwdArgsT a, int npass, int num_sms, cudaStre
   launch_pdl(umma::umma_fwd_res_u8_kernel<G, NTILE>, grid, dim3(umma::TT), smem, st, 1, a);
 }
 // DQN_S2D_TRACE=1: CTA 0 of the conv1 forward kernel stamps clock64() per (tile, pipeline event) here (dqn_debug_trace)
-static __device__ unsigned long long g_s2d_trace[60 * 8 + 160 * 4 + 16];
+static __device__ unsigned long long g_s2d_trace[60 * 8 + 160 * 4 + 16 + 64];     // + 64 data-parallel exchange stamps
 static unsigned long long* s2d_trace_ptr() {
   static unsigned long long* p = nullptr;
   static bool init = false;
@@ -1193,7 +1224,7 @@ static unsigned long long* s2d_trace_ptr() {
   return p;
 }
 extern "C" int dqn_debug_trace(unsigned long long* host, int32_t n) {
-  DQN_REQUIRE(host && n > 0 && n <= 60 * 8 + 160 * 4 + 16, DQN_ERR_INVALID, "debug_trace: bad argument");
+  DQN_REQUIRE(host && n > 0 && n <= 60 * 8 + 160 * 4 + 16 + 64, DQN_ERR_INVALID, "debug_trace: bad argument");
   DQN_CUDA(cudaDeviceSynchronize());
   DQN_CUDA(cudaMemcpyFromSymbol(host, g_s2d_trace, (size_t)n * 8));
   return 0;
@@ -1478,6 +1509,7 @@ static void set_dp_args(dqn_net_s* h, OptArgs* o, int flag_slot) {
   o->P = h->P;
   o->timeout_ns = h->dp_timeout_ns;
   o->err = h->dp_err;
+  o->trace = s2d_trace_ptr();
 }
 
 static int max_seg_len(const OptArgs& o) {
@@ -1550,13 +1582,13 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       // grad already holds the data term; add reg*w in place through the reduce kernel (partial == grad)
       dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
       StageScope sc(h, DQN_STAGE_REDUCE_GRAD, st);
-      reduce_grad_kernel<<<grid, 256, 0, st>>>(oa, h->grad, h->hyper.reg_param, 0, PublishArgs{nullptr, nullptr, 0, 1, 0, 0});
+      reduce_grad_kernel<<<grid, 256, 0, st>>>(oa, h->grad, h->hyper.reg_param, 0, PublishArgs{nullptr, nullptr, 0, 1, 0, 0, 0});
     }
     if (mode == 2) {
       dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
       StageScope sc(h, DQN_STAGE_REDUCE_GRAD, st);
       reduce_grad_kernel<<<grid, 256, 0, st>>>(oa, h->dp_grad, 0.f, 1,      // copy into this step's exchange buffer + publish
-                                               PublishArgs{h->dp_peer_flags_dev, h->dp_counter + 1, h->dp_rank, h->dp_world, 1, 0});
+                                               PublishArgs{h->dp_peer_flags_dev, h->dp_counter + 1, h->dp_rank, h->dp_world, 1, 0, dp_sys_release()});
     }
   } else {
     const bool nat = h->arch == DQN_ARCH_NATURE;
@@ -1644,7 +1676,7 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       dim3 g3((max_seg_len(ea) + 255) / 256, 3);
       dqn::count_launch();
       launch_pdl(reduce_grad_kernel, g3, dim3(256), 0, s2, 1, ea, h->dp_grad, 0.f, 1,
-                 PublishArgs{h->dp_peer_flags_dev, h->dp_counter, h->dp_rank, h->dp_world, 0, 2});
+                 PublishArgs{h->dp_peer_flags_dev, h->dp_counter, h->dp_rank, h->dp_world, 0, 2, dp_sys_release()});
       dqn::count_launch();
       dim3 g3v((max_seg_len(ea) / 4 + 256) / 256, 3);          // 4 parameters per thread
       launch_pdl(peer_sum_kernel, g3v, dim3(256), 0, s2, 1, ea, 2, h->grad);
@@ -1726,7 +1758,7 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       {
         StageScope sc(h, DQN_STAGE_REDUCE_GRAD, st);
         launch_pdl(reduce_grad_kernel, g01, dim3(256), 0, st, 1, oa, h->dp_grad, 0.f, 1,
-                   PublishArgs{h->dp_peer_flags_dev, h->dp_counter + 1, h->dp_rank, h->dp_world, 1, 0});
+                   PublishArgs{h->dp_peer_flags_dev, h->dp_counter + 1, h->dp_rank, h->dp_world, 1, 0, dp_sys_release()});
       }
     }
     DQN_CUDA(cudaStreamWaitEvent(st, h->ev_join2, 0));
@@ -1734,7 +1766,7 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
       StageScope sc(h, DQN_STAGE_REDUCE_GRAD, st);
       launch_pdl(reduce_grad_kernel, grid, dim3(256), 0, st, 1, oa, h->grad, include_reg ? h->hyper.reg_param : 0.f, 0,
-                 PublishArgs{nullptr, nullptr, 0, 1, 0, 0});
+                 PublishArgs{nullptr, nullptr, 0, 1, 0, 0, 0});
     }
   }
   if (mode == 0) {

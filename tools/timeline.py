@@ -1,5 +1,7 @@
 """Device timeline of one graph-replayed update (kernel start / duration from CUPTI through torch.profiler).
-    python tools/timeline.py [--batch 32]"""
+    python tools/timeline.py [--batch 32]
+    python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tools/timeline.py
+        (data-parallel step with the peer-memory exchange; rank 0 prints its timeline)"""
 import argparse
 import os
 import random
@@ -12,27 +14,32 @@ import torch
 import __graft_entry__ as ge
 ge.build()
 import bench, _cabi as c, network, replay_memory
+import data_parallel as dp
 from torch.profiler import profile, ProfilerActivity
-dev = torch.device("cuda", 0); torch.cuda.set_device(0)
-cfg = bench.atari_config(a.batch, "cnn", "bf16"); cfg.device_index = 0
+rank, local, world = dp.world_info()
+dev = torch.device("cuda", local); torch.cuda.set_device(local)
+dp.init(device=dev)
+cfg = bench.atari_config(a.batch, "cnn", "bf16"); cfg.device_index = local
 net = network.Network.create_network(cfg, (84, 84, 4), 6)
+dp.setup_network(net, cfg, "peer")
 a.capacity = 100000
-rm = bench._make_ring(a, torch, c, replay_memory, 0, 0, dev)
+rm = bench._make_ring(a, torch, c, replay_memory, rank, local, dev)
+random.seed(100 + rank)
 tab = torch.tensor([random.sample(range(rm.size()), a.batch) for _ in range(64)], dtype=torch.int32, device=dev)
 d_idx = torch.empty(a.batch, dtype=torch.int32, device=dev)
 d_idx.copy_(tab[0])
 side = torch.cuda.Stream()
 with torch.cuda.stream(side):
     for _ in range(3):
-        net.train_step(rm, a.batch, d_indices=d_idx)
+        dp.train_step(net, rm, a.batch, d_idx)
     g = torch.cuda.CUDAGraph()
     with torch.cuda.graph(g, stream=side):
-        net.train_step(rm, a.batch, d_indices=d_idx)
+        dp.train_step(net, rm, a.batch, d_idx)
 
     def step(i):
         d_idx.copy_(tab[i % 64], non_blocking=True)
         if a.eager:
-            net.train_step(rm, a.batch, d_indices=d_idx)
+            dp.train_step(net, rm, a.batch, d_idx)
         else:
             g.replay()
     for i in range(20):
@@ -53,9 +60,17 @@ for e in evs:
         cur = []
     cur.append(e)
 steps.append(cur)
+if world > 1:
+    import torch.distributed as dist
+    dist.barrier()
+if rank != 0:
+    dist.destroy_process_group()
+    sys.exit(0)
 st = steps[-2]
 t0 = st[0].time_range.start
 print("kernels of one update (us from the index copy): start, duration, name")
 for e in st:
     print("%8.2f %7.2f  %s" % (e.time_range.start - t0, e.time_range.end - e.time_range.start, e.name[:90]))
 print("update period: %.2f us" % (steps[-1][0].time_range.start - t0))
+if world > 1:
+    dist.destroy_process_group()
