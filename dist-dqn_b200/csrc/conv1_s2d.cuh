@@ -227,7 +227,8 @@ __device__ __forceinline__ void trace_cta(unsigned long long* trace, int ev) {
 }
 
 constexpr uint32_t FWD_OFF_IMG = 2 * RAW_BYTES, FWD_OFF_W = FWD_OFF_IMG + 2 * IMG_BYTES;
-constexpr uint32_t FWD_SMEM = SMEM_SLACK + FWD_OFF_W + W_BYTES;        // 205,824 bytes
+constexpr int FWD_W_BLOCKS = 8;                        // the four 4 KB tap blocks of the weight image, staged in two orders
+constexpr uint32_t FWD_SMEM = SMEM_SLACK + FWD_OFF_W + FWD_W_BLOCKS * 4096;        // 222,208 bytes
 constexpr int FWD_EPI_WARPS = 8;                       // two per TMEM lane quarter: 16 of the 32 channels each
 constexpr int FWD_BUILD_WARP0 = 2 + FWD_EPI_WARPS, FWD_BUILD_WARPS = 11, FWD_WARPS = FWD_BUILD_WARP0 + FWD_BUILD_WARPS;   // 21 warps
 static_assert(FWD_BUILD_WARPS * 32 >= BUILD_THREADS, "not enough builder threads");
@@ -285,8 +286,12 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, 1) conv1_s2d_fwd_kernel(FwdArg
   if (warp == 0) {
     // ---------------------------------------------------------------- producer
     if (elect_one()) {
-      mbar_expect_tx(&wbar, W_BYTES);
-      bulk_g2s(sbase + FWD_OFF_W, pass ? a.wt[1] : a.wt[0], W_BYTES, &wbar);
+      // tap blocks (4 KB each, tap d = 2*dy + dx in the global image) in the orders of the merged B operands, see the MMA issuer
+      const __nv_bfloat16* wsrc = pass ? a.wt[1] : a.wt[0];
+      constexpr int order[FWD_W_BLOCKS] = {3, 2, 0, 1, 2, 3, 1, 0};
+      mbar_expect_tx(&wbar, FWD_W_BLOCKS * 4096);
+#pragma unroll
+      for (int k = 0; k < FWD_W_BLOCKS; ++k) bulk_g2s(sbase + FWD_OFF_W + k * 4096, wsrc + order[k] * 2048, 4096, &wbar);
     }
     __syncwarp();
     producer_loop(
@@ -296,7 +301,17 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, 1) conv1_s2d_fwd_kernel(FwdArg
   } else if (warp == 1) {
     // ---------------------------------------------------------------- MMA issuer (f16 image x f16 weights: the two
     // operands of a kind::f16 MMA must share one format -- f16 x bf16 is an illegal instruction)
-    constexpr uint32_t idesc = make_idesc_ab(TM, 32, false, false, false, false);
+    // An MMA of this shape is bound by its shared-memory operand reads (4 KB image slice + 1 KB weights per 128x32x16 at
+    // 128 B/clk = 40 cycles for 16 cycles of math), so MMAs that read the SAME image slice are merged into wider ones.  The
+    // slice at super-pixel offset (Y, X) = (wy+dy, wx+dx) serves every (window position, tap) pair with that sum: the
+    // centre (1,1) all four positions, an edge two, a corner one.  With the accumulators in the column order
+    // [w00, w01, w11, w10] the centre is ONE N=128 MMA per k-step and three of the four edges are N=64 (the positions of
+    // edge (1,0), w00 and w10, are not neighbours): 40 MMAs instead of 64, 224 KB instead of 320 KB of operand reads per
+    // sample.  The weights are staged twice (FWD_W_BLOCKS), tap blocks in the orders the merged B operands need:
+    //   blocks 0..3 = taps [11, 10, 00, 01] (centre; single taps), blocks 4..7 = taps [10, 11, 01, 00] (edge pairs).
+    constexpr uint32_t idesc32 = make_idesc_ab(TM, 32, false, false, false, false);
+    constexpr uint32_t idesc64 = make_idesc_ab(TM, 64, false, false, false, false);
+    constexpr uint32_t idesc128 = make_idesc_ab(TM, 128, false, false, false, false);
     mbar_wait(&wbar, 0);
     for (int i = 0; i < ntiles; ++i) {
       const int ib = i & 1, ph = (i >> 1) & 1;
@@ -307,18 +322,24 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, 1) conv1_s2d_fwd_kernel(FwdArg
         trace_stamp(a.trace, i, 4);
         const uint32_t img = sbase + FWD_OFF_IMG + ib * IMG_BYTES;
         const uint64_t bd0 = make_desc_sw128(sbase + FWD_OFF_W);
+        const uint32_t acc = tmem + ib * 128;
+        // (image slice Y, X; first weight block; first accumulator column; N)
+        auto run = [&](int Y, int X, int wblock, int col, uint32_t idesc, bool first) {
+          const uint64_t ad0 = make_desc_sw128(img + (uint32_t)img_row(Y, X) * 128u);
 #pragma unroll
-        for (int w = 0; w < 4; ++w) {
-#pragma unroll
-          for (int d = 0; d < 4; ++d) {
-            const int s = (w >> 1) + (d >> 1), t = (w & 1) + (d & 1);
-            const uint64_t ad0 = make_desc_sw128(img + (uint32_t)img_row(s, t) * 128u);
-#pragma unroll
-            for (int j = 0; j < 4; ++j)
-              mma_bf16(tmem + ib * 128 + w * 32, desc_advance(ad0, j * 32), desc_advance(bd0, d * 4096 + j * 32), idesc,
-                       (d | j) ? 1u : 0u);
-          }
-        }
+          for (int j = 0; j < 4; ++j)
+            mma_bf16(acc + col, desc_advance(ad0, j * 32), desc_advance(bd0, wblock * 4096 + j * 32), idesc, (first && j == 0) ? 0u : 1u);
+        };
+        run(1, 1, 0, 0, idesc128, true);       // centre: w00<-11, w01<-10, w11<-00, w10<-01 (first write of every column)
+        run(0, 1, 6, 0, idesc64, false);       // edge: w00<-01, w01<-00
+        run(1, 2, 5, 32, idesc64, false);      // edge: w01<-11, w11<-01
+        run(2, 1, 4, 64, idesc64, false);      // edge: w11<-10, w10<-11
+        run(1, 0, 1, 0, idesc32, false);       // edge (1,0): w00<-10 ...
+        run(1, 0, 2, 96, idesc32, false);      //             ... and w10<-00
+        run(0, 0, 2, 0, idesc32, false);       // corners: w00<-00
+        run(0, 2, 3, 32, idesc32, false);      //          w01<-01
+        run(2, 0, 1, 96, idesc32, false);      //          w10<-10
+        run(2, 2, 0, 64, idesc32, false);      //          w11<-11
         mma_commit(&img_empty[ib]);
         mma_commit(&acc_full[ib]);
         trace_stamp(a.trace, i, 5);
@@ -344,28 +365,39 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, 1) conv1_s2d_fwd_kernel(FwdArg
       mbar_wait(&acc_full[ib], ph);
       tc_fence_after();
       if (tid == 64) trace_stamp(a.trace, i, 6);
-      // all four window positions' accumulators first (their TMEM latencies overlap), one wait, then the TMEM set goes back
-      uint32_t r[4][16];
-#pragma unroll
-      for (int w = 0; w < 4; ++w) tmem_ld16_nowait(tmem + ((uint32_t)(32 * q) << 16) + ib * 128 + w * 32 + h * 16, r[w]);
-      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&acc_empty[ib]);
       // A value's float bits, taken as a SIGNED integer, order like the value for values >= 0 and put every negative
       // value below them; with the 2 lowest mantissa bits replaced by 3-w the maximum over the window positions is the
       // largest value (first position on ties) whenever the pooled ReLU output is positive, and negative otherwise.
+      // Two window positions per round of TMEM loads: all four at once need more registers than a 21-warp CTA has per
+      // thread (80), and the spills ran through the same L1/shared-memory path the MMAs and the builders saturate.
       int key[16];
 #pragma unroll
       for (int j = 0; j < 16; ++j) key[j] = (int)0x80000000;
 #pragma unroll
-      for (int w = 0; w < 4; ++w) {
-        // window position (wy, wx) lies inside the 21x21 conv output unless it is the pool's padding row / column
-        const bool in = ((w >> 1) == 0 || py < PW - 1) && ((w & 1) == 0 || px < PW - 1);
+      for (int half = 0; half < 2; ++half) {
+        uint32_t r[2][16];
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const int kj = (__float_as_int(__uint_as_float(r[w][j]) + bias[j]) & ~3) | (3 - w);
-          key[j] = in ? max(key[j], kj) : key[j];
+        for (int u = 0; u < 2; ++u) {        // accumulator column block of window position w: [w00, w01, w11, w10]
+          const int w = 2 * half + u;
+          tmem_ld16_nowait(tmem + ((uint32_t)(32 * q) << 16) + ib * 128 + (w ^ (w >> 1)) * 32 + h * 16, r[u]);
+        }
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        if (half == 1) {                     // the TMEM set goes back to the MMA warp
+          if (tid == 64) trace_stamp(a.trace, i, 2);
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&acc_empty[ib]);
+        }
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          const int w = 2 * half + u;
+          // window position (wy, wx) lies inside the 21x21 conv output unless it is the pool's padding row / column
+          const bool in = ((w >> 1) == 0 || py < PW - 1) && ((w & 1) == 0 || px < PW - 1);
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const int kj = (__float_as_int(__uint_as_float(r[u][j]) + bias[j]) & ~3) | (3 - w);
+            key[j] = in ? max(key[j], kj) : key[j];
+          }
         }
       }
       if (valid) {
@@ -395,7 +427,6 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, 1) conv1_s2d_fwd_kernel(FwdArg
       mbar_wait(&raw_full[rb], ph);
       if (bt == 0) trace_stamp(a.trace, i, 1);
       mbar_wait(&img_empty[rb], ph ^ 1);
-      if (bt == 0) trace_stamp(a.trace, i, 2);
       build_image<PLANAR, true>(smem + rb * RAW_BYTES, smem + FWD_OFF_IMG + rb * IMG_BYTES, bt);       // exact f16 image
       fence_async_proxy();
       __syncwarp();

@@ -192,7 +192,14 @@ __global__ void __launch_bounds__(NT) conv_fwd_kernel(FwdArgs a) {
   __shared__ __align__(16) float Bs[BK][BN];
   const unsigned S = cg::this_cluster().num_blocks();          // cluster = (1,1,S): split of the reduction
   const unsigned rank = cg::this_cluster().block_rank();
-  const FwdPass P = a.p[blockIdx.z / S];
+  // selected field by field: a run-time index into the parameter block would move it to local memory
+  const bool p1 = blockIdx.z / S != 0;
+  FwdPass P;
+  P.x = p1 ? a.p[1].x : a.p[0].x;
+  P.w = p1 ? a.p[1].w : a.p[0].w;
+  P.bias = p1 ? a.p[1].bias : a.p[0].bias;
+  P.out = p1 ? a.p[1].out : a.p[0].out;
+  P.arg = p1 ? a.p[1].arg : a.p[0].arg;
   const TIn* __restrict__ x = static_cast<const TIn*>(P.x);
   const int tid = threadIdx.x;
   const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;

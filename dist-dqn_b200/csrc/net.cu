@@ -20,6 +20,7 @@
 #include "conv1_s2d.cuh"
 #include "fc_cluster.cuh"
 
+#include <algorithm>
 #include <cmath>
 #include <cstdlib>
 #include <new>
@@ -205,7 +206,7 @@ struct OptArgs {
   // double-buffered exchange block that all ranks have mapped; flags[p] = last step whose gradient rank p published
   int world;
   const float* peer_grad[8];             // exchange gradient buffers of all ranks ([2][P] floats each), rank order
-  const unsigned long long* flags;       // this rank's flag arrays (written by the peers): slot 0 = [0..7], slot 1 = [8..15]
+  const unsigned long long* flags;       // this rank's flag arrays (written by the peers): slot s = [8s..8s+7], s = 0..3
   long long P;
   int peer_mask;                         // bit s set: segment s is summed over the ranks here; clear: already summed locally
   int flag_slot;                         // which flag array guards the peer-summed segments
@@ -246,17 +247,21 @@ __device__ __forceinline__ unsigned long long global_timer_ns() {
 // a.timeout_ns of wall-clock time (dqn_net_dp_set_timeout; ranks are driven by independent host code, so seconds of skew
 // are normal): when it expires the step number is left in *a.err for the host (dqn_net_dp_status) and the kernel goes on
 // with whatever the exchange buffers hold, instead of trapping and taking the CUDA context down.
+// Called by the first warp of a block: lane r polls rank r's flag, so the system-scope acquire loads (0.6 us each,
+// tools/trace_dp.py) overlap instead of queueing one rank after the other.
 __device__ __forceinline__ void wait_peer_flags(const OptArgs& a, unsigned long long step) {
-  const unsigned long long t0 = global_timer_ns();
-  for (int r = 0; r < a.world; ++r) {
+  const int r = threadIdx.x & 31;
+  if (r < a.world) {
+    const unsigned long long t0 = global_timer_ns();
     unsigned spins = 0;
     while (ld_acquire_sys(a.flags + 8 * a.flag_slot + r) < step) {
       if ((++spins & 1023u) == 0 && (long long)(global_timer_ns() - t0) > a.timeout_ns) {
         atomicMax(a.err, step);
-        return;
+        break;
       }
     }
   }
+  __syncwarp();
 }
 
 // Sum over the ranks of element gi of the exchange buffers.  All loads are issued before the first add (a loop with
@@ -333,9 +338,9 @@ __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs a) {
   if (a.world > 1) {
     // wait until every rank has published its gradient of this step
     const bool tr0 = threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0;
-    if (tr0) dp_stamp(a.trace, 24);
-    if (threadIdx.x == 0) wait_peer_flags(a, (unsigned long long)step);
-    if (tr0) dp_stamp(a.trace, 25);
+    if (tr0) dp_stamp(a.trace, 48);
+    if (threadIdx.x < 32) wait_peer_flags(a, (unsigned long long)step);
+    if (tr0) dp_stamp(a.trace, 49);
     __syncthreads();
   }
   if (i >= s.len) return;
@@ -399,7 +404,7 @@ __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs a) {
     } break;
   }
   a.w[p] = w;
-  if (threadIdx.x == 0) dp_stamp(a.trace, 26, true);
+  if (threadIdx.x == 0) dp_stamp(a.trace, 50, true);
   if (tiled) {
     const int k = i / s.N, n = i - k * s.N;
     const __nv_bfloat16 v = __float2bfloat16_rn(w);
@@ -425,7 +430,7 @@ struct PublishArgs {
   unsigned int* done_counter;              // blocks finished so far (reset by the last one)
   int rank, world;
   int flag_slot;                           // flag array to raise: 0 = early segments, 1 = final segment(s)
-  int seg_base;                            // first segment this launch covers (gridDim.y segments)
+  int segs;                                // segments this launch covers, 4 bits each: blockIdx.y -> (segs >> 4*y) & 15
   int sys_release;                         // 1: raise the flags with a system-scope release store (see reduce_grad_kernel)
 };
 static int dp_sys_release() {
@@ -437,7 +442,7 @@ __global__ void __launch_bounds__(256) reduce_grad_kernel(OptArgs a, float* __re
                                                           PublishArgs pub) {
   pdl_wait();
   if (pub.peer_flags && threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0) dp_stamp(a.trace, 8 * pub.flag_slot);
-  const Seg s = a.seg[blockIdx.y + pub.seg_base];
+  const Seg s = a.seg[(pub.segs >> (4 * blockIdx.y)) & 15];
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (by_parity) grad += (size_t)(*a.step & 1) * (size_t)a.P;     // exchange block: buffer of this step's parity
   if (i < s.len) {
@@ -480,15 +485,15 @@ __global__ void __launch_bounds__(256) reduce_grad_kernel(OptArgs a, float* __re
 // Early half of the data-parallel exchange: sums the already published segments of all ranks into the local flat
 // gradient buffer while the data-gradient chain is still running; the optimizer then only has to exchange what the
 // last kernel of the step produces.
-__global__ void __launch_bounds__(256) peer_sum_kernel(OptArgs a, int seg_base, float* __restrict__ gsum) {
+__global__ void __launch_bounds__(256) peer_sum_kernel(OptArgs a, int segs, float* __restrict__ gsum) {
   pdl_wait();
-  const Seg s = a.seg[blockIdx.y + seg_base];
+  const Seg s = a.seg[(segs >> (4 * blockIdx.y)) & 15];
   const int i = (blockIdx.x * blockDim.x + threadIdx.x) * 4;            // 4 consecutive parameters per thread: 16-byte peer loads
   const long long step = *a.step;
   const bool tr0 = threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0;
-  if (tr0) dp_stamp(a.trace, 16);
-  if (threadIdx.x == 0) wait_peer_flags(a, (unsigned long long)step);
-  if (tr0) dp_stamp(a.trace, 17);
+  if (tr0) dp_stamp(a.trace, 32 + 4 * a.flag_slot);
+  if (threadIdx.x < 32) wait_peer_flags(a, (unsigned long long)step);
+  if (tr0) dp_stamp(a.trace, 33 + 4 * a.flag_slot);
   __syncthreads();
   if (i >= s.len) return;
   const size_t p = (size_t)s.off + i;                                  // segments start at multiples of 4 floats
@@ -498,7 +503,7 @@ __global__ void __launch_bounds__(256) peer_sum_kernel(OptArgs a, int seg_base, 
   } else {
     for (int e = 0; i + e < s.len; ++e) gsum[p + e] = peer_sum1(a, gi + e);
   }
-  if (threadIdx.x == 0) dp_stamp(a.trace, 18, true);
+  if (threadIdx.x == 0) dp_stamp(a.trace, 34 + 4 * a.flag_slot, true);
 }
 
 // loss = mean_b se_b + reg * sum_{reg tensors} ||w||^2 / 2   (network.py:150-152); one CTA.  The weights are not written by
@@ -1070,8 +1075,8 @@ extern "C" int dqn_net_set_global_step(dqn_net_t h, int64_t step) {
     // the exchange flags count steps too ("rank r has published step s"): realign this rank's flag arrays, otherwise a
     // smaller restored step would make every wait pass at once.  Every rank must do this at the same point, with no
     // dqn_net_dp_step in flight on any rank (Network.load puts a barrier on both sides).
-    unsigned long long f[16];
-    for (int i = 0; i < 16; ++i) f[i] = (unsigned long long)step;
+    unsigned long long f[32];
+    for (int i = 0; i < 32; ++i) f[i] = (unsigned long long)step;
     DQN_CUDA(cudaMemcpy(h->dp_block, f, sizeof(f), cudaMemcpyHostToDevice));
     if (h->dp_err) DQN_CUDA(cudaMemset(h->dp_err, 0, 8));
   }
@@ -1582,13 +1587,13 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       // grad already holds the data term; add reg*w in place through the reduce kernel (partial == grad)
       dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
       StageScope sc(h, DQN_STAGE_REDUCE_GRAD, st);
-      reduce_grad_kernel<<<grid, 256, 0, st>>>(oa, h->grad, h->hyper.reg_param, 0, PublishArgs{nullptr, nullptr, 0, 1, 0, 0, 0});
+      reduce_grad_kernel<<<grid, 256, 0, st>>>(oa, h->grad, h->hyper.reg_param, 0, PublishArgs{nullptr, nullptr, 0, 1, 0, 0x43210, 0});
     }
     if (mode == 2) {
       dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
       StageScope sc(h, DQN_STAGE_REDUCE_GRAD, st);
       reduce_grad_kernel<<<grid, 256, 0, st>>>(oa, h->dp_grad, 0.f, 1,      // copy into this step's exchange buffer + publish
-                                               PublishArgs{h->dp_peer_flags_dev, h->dp_counter + 1, h->dp_rank, h->dp_world, 1, 0, dp_sys_release()});
+                                               PublishArgs{h->dp_peer_flags_dev, h->dp_counter + 1, h->dp_rank, h->dp_world, 1, 0x43210, dp_sys_release()});
     }
   } else {
     const bool nat = h->arch == DQN_ARCH_NATURE;
@@ -1661,25 +1666,35 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
                h->g, d_actions, k, head_per, h->F, h->A, h->head_partial);
     }
     if (mode != 2) DQN_CUDA(cudaEventRecord(h->ev_join2, h->side2));
-    // data-parallel: as soon as the gradients of conv3, fc and the head (segments 2..4, 72% of the parameters) exist,
-    // a third stream publishes them and sums them over the ranks into the local flat gradient buffer, in the shadow
-    // of the rest of the backward pass
-    auto early_exchange = [&]() -> int {
+    // data-parallel: the gradients of conv3, fc and the head (segments 2..4, 72% of the parameters) are published and summed
+    // over the ranks into the local flat gradient buffer in the shadow of the rest of the backward pass, in two parts
+    // that run side by side: fc (the largest tensor) on its own stream right behind its weight-gradient kernel (flag
+    // slot 2), conv3 + head on a third stream (flag slot 0).  At 8 ranks one part pulls 1-2 MB over NVLink; as a single
+    // exchange behind the LAST of the three weight gradients it ended after the conv1 weight gradient (tools/trace_dp.py).
+    auto exchange_part = [&](cudaStream_t s, int segs, int nsegs, int slot) -> int {
+      OptArgs ea;
+      fill_segs(h, &ea, nsplit, false);
+      set_dp_args(h, &ea, slot);
+      int len = 0;
+      for (int y = 0; y < nsegs; ++y) len = std::max(len, ea.seg[(segs >> (4 * y)) & 15].len);
+      dqn::count_launch();
+      launch_pdl(reduce_grad_kernel, dim3((len + 255) / 256, nsegs), dim3(256), 0, s, 1, ea, h->dp_grad, 0.f, 1,
+                 PublishArgs{h->dp_peer_flags_dev, h->dp_counter + slot, h->dp_rank, h->dp_world, slot, segs,
+                             dp_sys_release()});
+      dqn::count_launch();
+      launch_pdl(peer_sum_kernel, dim3((len / 4 + 256) / 256, nsegs), dim3(256), 0, s, 1, ea, segs, h->grad);   // 4 parameters per thread
+      return 0;
+    };
+    auto early_exchange_fc = [&]() -> int {          // on `sh`, right behind the fc weight gradient
+      if (mode != 2) return 0;
+      return exchange_part(sh, 0x3, 1, 2);
+    };
+    auto early_exchange = [&]() -> int {             // conv3 + head, on the stream of the head weight gradient
       if (mode != 2) return 0;
       cudaStream_t s2 = h->side2;
       DQN_CUDA(cudaEventRecord(h->ev_x, sd));
       DQN_CUDA(cudaStreamWaitEvent(s2, h->ev_x, 0));
-      DQN_CUDA(cudaStreamWaitEvent(s2, h->ev_head, 0));
-      OptArgs ea;
-      fill_segs(h, &ea, nsplit, false);
-      set_dp_args(h, &ea, 0);
-      dim3 g3((max_seg_len(ea) + 255) / 256, 3);
-      dqn::count_launch();
-      launch_pdl(reduce_grad_kernel, g3, dim3(256), 0, s2, 1, ea, h->dp_grad, 0.f, 1,
-                 PublishArgs{h->dp_peer_flags_dev, h->dp_counter, h->dp_rank, h->dp_world, 0, 2, dp_sys_release()});
-      dqn::count_launch();
-      dim3 g3v((max_seg_len(ea) / 4 + 256) / 256, 3);          // 4 parameters per thread
-      launch_pdl(peer_sum_kernel, g3v, dim3(256), 0, s2, 1, ea, 2, h->grad);
+      if (exchange_part(s2, 0x42, 2, 0)) return DQN_ERR_CUDA;
       DQN_CUDA(cudaEventRecord(h->ev_join2, s2));
       return 0;
     };
@@ -1690,6 +1705,7 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
     };
     if (h->precision == 1 && nat) {
       launch_wgrad_tc<NF, __nv_bfloat16, 128>(h, 3, h->act_bf[0][2], k, sh, &nsplit[3]);
+      if (early_exchange_fc()) return DQN_ERR_CUDA;
       DQN_CUDA(cudaEventRecord(h->ev_head, sh));
       launch_dgrad_tc<NF, 64>(h, 3, k, st);
       if (fork_after_dgrad(1)) return DQN_ERR_CUDA;
@@ -1700,6 +1716,7 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       launch_wgrad_tc<N1, uint8_t, 32>(h, 0, d_states, k, st, &nsplit[0]);
     } else if (h->precision == 1) {
       launch_wgrad_tc<F4, __nv_bfloat16, 128>(h, 3, h->act_bf[0][2], k, sh, &nsplit[3]);
+      if (early_exchange_fc()) return DQN_ERR_CUDA;
       DQN_CUDA(cudaEventRecord(h->ev_head, sh));
       if (!fused) {                  // the fused kernel already produced the fc data gradient
         if (k <= 64) launch_dgrad_tc<F4, 32>(h, 3, k, st);
@@ -1716,6 +1733,7 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       else launch_wgrad_res_u8<C1>(h, d_states, k, st, &nsplit[0]);
     } else if (nat) {
       launch_wgrad<NF, float>(h, 3, h->act[0][2], k, sh, &nsplit[3]); launch_dgrad<NF>(h, 3, k, st);
+      if (early_exchange_fc()) return DQN_ERR_CUDA;
       DQN_CUDA(cudaEventRecord(h->ev_head, sh));
       if (fork_after_dgrad(1)) return DQN_ERR_CUDA;
       launch_wgrad<N3, float>(h, 2, h->act[0][1], k, sd, &nsplit[2]); launch_dgrad<N3>(h, 2, k, st);
@@ -1726,6 +1744,7 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       else launch_wgrad<N1, float>(h, 0, d_states, k, st, &nsplit[0]);
     } else {
       launch_wgrad<F4, float>(h, 3, h->act[0][2], k, sh, &nsplit[3]); launch_dgrad<F4>(h, 3, k, st);
+      if (early_exchange_fc()) return DQN_ERR_CUDA;
       DQN_CUDA(cudaEventRecord(h->ev_head, sh));
       if (fork_after_dgrad(1)) return DQN_ERR_CUDA;
       launch_wgrad<C3, float>(h, 2, h->act[0][1], k, sd, &nsplit[2]); launch_dgrad<C3>(h, 2, k, st);
@@ -1752,13 +1771,14 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
     DQN_CUDA(cudaStreamWaitEvent(st, h->ev_head, 0));
     DQN_CUDA(cudaGetLastError());
     if (mode == 2) {
-      // late half of the exchange: conv1 and conv2 (segments 0, 1) are published here and summed by the optimizer
+      // last part of the exchange: conv1 and conv2 (segments 0, 1) are published here and summed by the optimizer.  (conv2
+      // as a part of its own behind its weight gradient was measured: that chain of two kernels ends after this one.)
       set_dp_args(h, &oa, 1);
-      dim3 g01((max_seg_len(oa) + 255) / 256, 2);
+      dim3 g01((std::max(oa.seg[0].len, oa.seg[1].len) + 255) / 256, 2);
       {
         StageScope sc(h, DQN_STAGE_REDUCE_GRAD, st);
         launch_pdl(reduce_grad_kernel, g01, dim3(256), 0, st, 1, oa, h->dp_grad, 0.f, 1,
-                   PublishArgs{h->dp_peer_flags_dev, h->dp_counter + 1, h->dp_rank, h->dp_world, 1, 0, dp_sys_release()});
+                   PublishArgs{h->dp_peer_flags_dev, h->dp_counter + 1, h->dp_rank, h->dp_world, 1, 0x10, dp_sys_release()});
       }
     }
     DQN_CUDA(cudaStreamWaitEvent(st, h->ev_join2, 0));
@@ -1766,7 +1786,7 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
       StageScope sc(h, DQN_STAGE_REDUCE_GRAD, st);
       launch_pdl(reduce_grad_kernel, grid, dim3(256), 0, st, 1, oa, h->grad, include_reg ? h->hyper.reg_param : 0.f, 0,
-                 PublishArgs{nullptr, nullptr, 0, 1, 0, 0, 0});
+                 PublishArgs{nullptr, nullptr, 0, 1, 0, 0x43210, 0});
     }
   }
   if (mode == 0) {

@@ -333,6 +333,19 @@ struct FwdArgsT {
   int tiles_per_cta;    // ... and consecutive tiles per CTA
 };
 
+// kernel parameters are selected field by field: indexing a.p[] with a run-time value makes the compiler copy the whole
+// parameter block to local memory (112 bytes of stack, read back through L1 at the start of every thread)
+__device__ __forceinline__ FwdPassT pick_pass(const FwdArgsT& a, int pass) {
+  FwdPassT P;
+  P.x = pass ? a.p[1].x : a.p[0].x;
+  P.wt = pass ? a.p[1].wt : a.p[0].wt;
+  P.bias = pass ? a.p[1].bias : a.p[0].bias;
+  P.out = pass ? a.p[1].out : a.p[0].out;
+  P.out_f32 = pass ? a.p[1].out_f32 : a.p[0].out_f32;
+  P.arg = pass ? a.p[1].arg : a.p[0].arg;
+  return P;
+}
+
 // Forward epilogue: TMEM -> bias + ReLU (+ 2x2 max-pool and arg-max) -> bf16 NHWC (+ optional fp32 copy).
 template <class G, int NTILE>
 __device__ __forceinline__ void fwd_epilogue(uint32_t tmem, const FwdPassT& P, int m0, int n0, int B, const float* bias_sm) {
@@ -422,7 +435,7 @@ __global__ void __launch_bounds__(TT) umma_fwd_kernel(FwdArgsT a) {
   __shared__ uint64_t full[RSN];      // a ring slot is filled: one arrival per warp
   __shared__ uint32_t tmem_slot;
   __shared__ float bias_sm[NTILE];
-  const FwdPassT P = a.p[blockIdx.z];
+  const FwdPassT P = pick_pass(a, (int)blockIdx.z);
   const TIn* __restrict__ x = static_cast<const TIn*>(P.x);
   const int tid = threadIdx.x;
   const int m0 = blockIdx.x * TM, n0 = blockIdx.y * NTILE;
@@ -568,7 +581,7 @@ __global__ void __launch_bounds__(TT) umma_fwd_res_kernel(FwdArgsT a) {
   __shared__ uint64_t patchbar;       // the input feature maps have landed
   __shared__ uint32_t tmem_slot;
   __shared__ float bias_sm[NTILE];
-  const FwdPassT P = a.p[blockIdx.z];
+  const FwdPassT P = pick_pass(a, (int)blockIdx.z);
   const __nv_bfloat16* __restrict__ x = static_cast<const __nv_bfloat16*>(P.x);
   const int tid = threadIdx.x, lane = tid & 31;
   const int m0 = blockIdx.x * TM, n0 = blockIdx.y * NTILE;
@@ -1286,8 +1299,10 @@ __global__ void __launch_bounds__(TT) umma_dgrad_kernel(DgradArgsT a) {
   // which rows does this tile cover?  dense: m0 + r over all input pixels; S2: r-th pixel of parity class `cls`
   int cls = 0, row0 = m0;
   if constexpr (S2) {
-    while (cls < 3 && (int)blockIdx.x >= a.cls_tile[cls + 1]) ++cls;
-    row0 = ((int)blockIdx.x - a.cls_tile[cls]) * TM;
+    // (no run-time index into the parameter block: that would move it to local memory)
+    const int bx = (int)blockIdx.x, t1 = a.cls_tile[1], t2 = a.cls_tile[2], t3 = a.cls_tile[3];
+    cls = (bx >= t1) + (bx >= t2) + (bx >= t3);
+    row0 = (bx - (cls == 0 ? a.cls_tile[0] : cls == 1 ? t1 : cls == 2 ? t2 : t3)) * TM;
   }
   const int cy = cls >> 1, cx = cls & 1;
   auto decode = [&](int r, int& b, int& iy, int& ix) -> bool {
@@ -1462,8 +1477,10 @@ __global__ void __launch_bounds__(TT) umma_dgrad_res_kernel(DgradArgsT a) {
   // which rows does this tile cover?  dense: m0 + r over all input pixels; S2: r-th pixel of parity class `cls`
   int cls = 0, row0 = blockIdx.x * TM;
   if constexpr (S2) {
-    while (cls < 3 && (int)blockIdx.x >= a.cls_tile[cls + 1]) ++cls;
-    row0 = ((int)blockIdx.x - a.cls_tile[cls]) * TM;
+    // (no run-time index into the parameter block: that would move it to local memory)
+    const int bx = (int)blockIdx.x, t1 = a.cls_tile[1], t2 = a.cls_tile[2], t3 = a.cls_tile[3];
+    cls = (bx >= t1) + (bx >= t2) + (bx >= t3);
+    row0 = (bx - (cls == 0 ? a.cls_tile[0] : cls == 1 ? t1 : cls == 2 ? t2 : t3)) * TM;
   }
   const int cy = cls >> 1, cx = cls & 1;
   // weights first (they do not depend on the previous kernel); S2: k-block i is the class's i-th tap

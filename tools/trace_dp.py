@@ -26,10 +26,12 @@ side = torch.cuda.Stream()
 n = 60 * 8 + 160 * 4 + 16 + 64
 buf = (C.c_uint64 * n)()
 c.lib.dqn_debug_trace.argtypes = [C.c_void_p, C.c_int32]
-names = {0: "early reduce: start", 1: "early reduce: last block", 2: "early reduce: flags raised",
-         16: "early peer sum: start", 17: "early peer sum: flags seen", 18: "early peer sum: end",
-         8: "late reduce: start", 9: "late reduce: last block", 10: "late reduce: flags raised",
-         24: "optimizer: start", 25: "optimizer: flags seen", 26: "optimizer: end"}
+names = {0: "conv3+head reduce: start", 1: "conv3+head reduce: last block", 2: "conv3+head reduce: flags raised",
+         32: "conv3+head peer sum: start", 33: "conv3+head peer sum: flags seen", 34: "conv3+head peer sum: end",
+         16: "fc reduce: start", 17: "fc reduce: last block", 18: "fc reduce: flags raised",
+         40: "fc peer sum: start", 41: "fc peer sum: flags seen", 42: "fc peer sum: end",
+         8: "conv1+conv2 reduce: start", 9: "conv1+conv2 reduce: last block", 10: "conv1+conv2 reduce: flags raised",
+         48: "optimizer: start", 49: "optimizer: flags seen", 50: "optimizer: end"}
 with torch.cuda.stream(side):
     for _ in range(3):
         dp.train_step(net, rm, B, d_idx)
@@ -48,12 +50,12 @@ torch.cuda.synchronize()
 dist.barrier()
 for r in range(world):
     if r == rank:
-        print("rank %d (us relative to the start of the late reduce, median of 10 updates)" % rank)
+        print("rank %d (us relative to the start of the conv1+conv2 reduce = end of the backward pass, median of 10 updates)" % rank)
         keys = sorted(names)
         ref = keys.index(8)
         import statistics
         for j, k in enumerate(keys):
-            print("  %-30s %8.2f" % (names[k], statistics.median((row[j] - row[ref]) / 1e3 for row in rows)))
+            print("  %-34s %8.2f" % (names[k], statistics.median((row[j] - row[ref]) / 1e3 for row in rows)))
         sys.stdout.flush()
     dist.barrier()
 dist.destroy_process_group()
