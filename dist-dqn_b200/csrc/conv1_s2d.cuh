@@ -456,14 +456,19 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, 1) conv1_s2d_fwd_kernel(FwdArg
 // As MMAs: M = 128 = the two dy taps x 64 channels (two 64-element blocks of the MN-major A operand, LBO apart: both
 // taps read plane rows a fixed distance apart), N = 32, reduction over m in 8 steps of 16.  For wy = 1 the row distance
 // between tap dy = 0 and dy = 1 is negative, so there the blocks are taken in the order (dy = 1, dy = 0) and accumulated
-// separately: four accumulators (wy, dx); the epilogue adds accumulator (1, dx) to (0, dx) with its halves swapped.
+// separately: four accumulators (wy, dx) in the column order [(0,1), (0,0), (1,1), (1,0)]; the epilogue adds accumulator
+// (1, dx) to (0, dx) with its halves swapped.
 struct WgradArgs {
   Src src;                       // pass 0 only
   const __nv_bfloat16* dactg;    // [B][121][32] ReLU-gated gradient of the pooled conv1 output
   const uint8_t* arg;            // [B][121][32]
   float* partial;                // [gridDim.x][(256+1)*32] fp32, reference index order
   int B;
+  unsigned long long* trace;     // debugging (DQN_S2D_TRACE=1): CTA 0 stamps clock64() per tile at trace[1136 + 8*tile + ev]
 };
+__device__ __forceinline__ void wg_stamp(unsigned long long* trace, int tile, int ev) {
+  if (trace && blockIdx.x == 0 && tile < 8) trace[1136 + tile * 8 + ev] = (unsigned long long)clock64();
+}
 
 constexpr uint32_t WG_GRAD_BYTES = NWIN * 32 * 2, WG_ARG_BYTES = NWIN * 32;          // 7744, 3872 per sample
 constexpr uint32_t WG_GA_SLOT = 12 * 1024;                                           // gradient (8 KB) + arg-max (4 KB) staging
@@ -524,32 +529,36 @@ __global__ void __launch_bounds__(NWARPS * 32, 1) conv1_s2d_wgrad_kernel(WgradAr
         });
   } else if (warp == 1) {
     // ---------------------------------------------------------------- MMA issuer
-    constexpr uint32_t idesc = make_idesc(TM, 32, true, true);
+    // MMAs that read the same image slice are merged (see the forward kernel): for X = wx + dx = 1 the pairs (wx=0, dx=1)
+    // and (wx=1, dx=0) share it, their B operands dZ(wy,0), dZ(wy,1) are neighbours in shared memory (one descriptor, N=64)
+    // and so are their accumulators, which therefore sit in the order [(wy,dx=1), (wy,dx=0)]: 48 MMAs instead of 64.
+    constexpr uint32_t idesc32 = make_idesc(TM, 32, true, true), idesc64 = make_idesc(TM, 64, true, true);
     for (int i = 0; i < ntiles; ++i) {
       mbar_wait(&op_full, i & 1);
       tc_fence_after();
       if (elect_one()) {
+        wg_stamp(a.trace, i, 5);
         const uint32_t img = sbase + WG_OFF_IMG;
 #pragma unroll
         for (int wy = 0; wy < 2; ++wy) {
+          // (X; first dZ tile; first accumulator column block; N; first write of the columns)
+          auto run = [&](int t, int wx, int col, uint32_t idesc, bool first) {
+            // block 0 / block 1 of the M = 128 rows: wy = 0 -> taps dy = 0, 1 (rows +248); wy = 1 -> taps dy = 1, 0 (rows +237)
+            const int r0 = wy ? img_row(2, t) : img_row(0, t);
+            const int r1 = img_row(1, t);
+            const uint64_t ad0 = make_desc_sw128_mn(img + (uint32_t)r0 * 128u, (uint32_t)(r1 - r0) * 128u, 1024);
+            const uint64_t bd0 = make_desc(sbase + WG_OFF_DZ + (wy * 2 + wx) * 8192, 128, 2048);
 #pragma unroll
-          for (int dx = 0; dx < 2; ++dx) {
-#pragma unroll
-            for (int wx = 0; wx < 2; ++wx) {
-              const int t = wx + dx;
-              // block 0 / block 1 of the M = 128 rows: wy = 0 -> taps dy = 0, 1 (rows +248); wy = 1 -> taps dy = 1, 0 (rows +237)
-              const int r0 = wy ? img_row(2, t) : img_row(0, t);
-              const int r1 = img_row(1, t);
-              const uint64_t ad0 = make_desc_sw128_mn(img + (uint32_t)r0 * 128u, (uint32_t)(r1 - r0) * 128u, 1024);
-              const uint64_t bd0 = make_desc(sbase + WG_OFF_DZ + (wy * 2 + wx) * 8192, 128, 2048);
-#pragma unroll
-              for (int j = 0; j < 8; ++j)
-                mma_bf16(tmem + (wy * 2 + dx) * 32, desc_advance(ad0, j * 2048), desc_advance(bd0, j * 256), idesc,
-                         (i | wx | j) ? 1u : 0u);
-            }
-          }
+            for (int j = 0; j < 8; ++j)
+              mma_bf16(tmem + wy * 64 + col * 32, desc_advance(ad0, j * 2048), desc_advance(bd0, j * 256), idesc,
+                       (first && i == 0 && j == 0) ? 0u : 1u);
+          };
+          run(1, 0, 0, idesc64, true);       // X = 1: (wx=0 -> dx=1, column block 0), (wx=1 -> dx=0, column block 1)
+          run(0, 0, 1, idesc32, false);      // X = 0: wx=0, dx=0
+          run(2, 1, 0, idesc32, false);      // X = 2: wx=1, dx=1
         }
         mma_commit(&op_empty);
+        wg_stamp(a.trace, i, 6);
       }
       __syncwarp();
     }
@@ -559,9 +568,13 @@ __global__ void __launch_bounds__(NWARPS * 32, 1) conv1_s2d_wgrad_kernel(WgradAr
     for (int i = 0; i < ntiles; ++i) {
       const int rb = i & 1;
       mbar_wait(&stk_full[rb], (i >> 1) & 1);
+      if (bt == 0) wg_stamp(a.trace, i, 0);
       if (i > 0) mbar_wait(&op_empty, (i - 1) & 1);             // the previous sample's MMAs have read the operands
+      if (bt == 0) wg_stamp(a.trace, i, 1);
       build_image<PLANAR, false>(smem + rb * RAW_BYTES, smem + WG_OFF_IMG, bt);
+      if (bt == 0) wg_stamp(a.trace, i, 2);
       mbar_wait(&ga_full[rb], (i >> 1) & 1);
+      if (bt == 0) wg_stamp(a.trace, i, 3);
       const uint8_t* ga = smem + WG_OFF_GA + rb * WG_GA_SLOT;
 #pragma unroll
       for (int q = 0; q < 2; ++q) {
@@ -578,6 +591,7 @@ __global__ void __launch_bounds__(NWARPS * 32, 1) conv1_s2d_wgrad_kernel(WgradAr
       }
       fence_async_proxy();
       __syncwarp();
+      if (bt == 0) wg_stamp(a.trace, i, 4);
       if (lane == 0) {
         mbar_arrive(&op_full);
         mbar_arrive(&ld_empty[rb]);
@@ -587,54 +601,74 @@ __global__ void __launch_bounds__(NWARPS * 32, 1) conv1_s2d_wgrad_kernel(WgradAr
   pdl_trigger();
   // ------------------------------------------------------------------ epilogue: one partial per CTA
   if (ntiles > 0) mbar_wait(&op_empty, (ntiles - 1) & 1);      // every MMA has completed (all threads wait: the operand area is reused)
+  if (tid == 64) wg_stamp(a.trace, 0, 7);
   tc_fence_after();
   __syncthreads();
+  if (tid == 64) wg_stamp(a.trace, 4, 7);
   float* out = a.partial + (size_t)blockIdx.x * (257 * 32);
   float* stage = reinterpret_cast<float*>(smem + WG_OFF_IMG);  // [2 dx][128 rows][32] fp32, 16-byte chunks XOR-ed with the row
-  float* csum = reinterpret_cast<float*>(smem + WG_OFF_IMG + 32768);   // [4 cq][8 e][121 m] bias-gradient terms
+  float* csum = reinterpret_cast<float*>(smem + WG_OFF_IMG + 32768);   // [builder warp][4 cq][8 e] bias-gradient partial sums
   if (warp >= WG_BUILD_WARP0) {
-    const int bt = tid - WG_BUILD_WARP0 * 32;
+    // bias gradient: a thread's items are (m, channel chunk cq = lane & 3) for two m; sum over the 8 m of the warp with
+    // shuffles (fixed tree), one partial per warp and channel; warp 8 adds the 14 partials in order
 #pragma unroll
-    for (int q = 0; q < 2; ++q) {
-      const int item = bt + q * WG_BUILDERS;
-      if (item < NWIN * 4) {
-#pragma unroll
-        for (int e = 0; e < 8; ++e) csum[((item & 3) * 8 + e) * NWIN + (item >> 2)] = colsum[q][e];
-      }
+    for (int e = 0; e < 8; ++e) {
+      float v = colsum[0][e] + colsum[1][e];
+      v += __shfl_xor_sync(0xffffffffu, v, 4);
+      v += __shfl_xor_sync(0xffffffffu, v, 8);
+      v += __shfl_xor_sync(0xffffffffu, v, 16);
+      if (lane < 4) csum[((warp - WG_BUILD_WARP0) * 4 + lane) * 8 + e] = v;
     }
   }
   const int q4 = warp & 3, dxe = (warp >> 2) & 1, row = 32 * q4 + lane;             // warps 0..7: accumulators (., dx = warp>>2)
-  float acc0[32];
   if (warp < 8 && ntiles > 0) {
     float acc1[32];
-    tmem_ld32(tmem + ((uint32_t)(32 * q4) << 16) + (2 + dxe) * 32, acc1);            // accumulator (wy = 1, dx): halves swapped
+    tmem_ld32(tmem + ((uint32_t)(32 * q4) << 16) + (2 + (1 - dxe)) * 32, acc1);      // accumulator (wy = 1, dx): halves swapped
     const int prow = row ^ 64;
 #pragma unroll
     for (int j = 0; j < 8; ++j)
       *reinterpret_cast<float4*>(stage + (dxe * 128 + prow) * 32 + ((j ^ (prow & 7)) << 2)) =
           make_float4(acc1[4 * j], acc1[4 * j + 1], acc1[4 * j + 2], acc1[4 * j + 3]);
-    tmem_ld32(tmem + ((uint32_t)(32 * q4) << 16) + dxe * 32, acc0);                  // accumulator (wy = 0, dx)
   }
+  if (tid == 64) wg_stamp(a.trace, 2, 7);
   __syncthreads();
-  if (warp < 8) {
-    const int dy = row >> 6, c64 = row & 63;
-    float* dst = out + (size_t)kref(dy, dxe, c64) * 32;
+  if (warp < 8 && ntiles > 0) {
+    // add accumulator (wy = 0, dx) to the row its partner left in the staging tile (in place: only this thread touches
+    // this row now)
+    float acc0[32];
+    tmem_ld32(tmem + ((uint32_t)(32 * q4) << 16) + (1 - dxe) * 32, acc0);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (ntiles > 0) {
-        const float4 o = *reinterpret_cast<const float4*>(stage + (dxe * 128 + row) * 32 + ((j ^ (row & 7)) << 2));
-        v = make_float4(acc0[4 * j] + o.x, acc0[4 * j + 1] + o.y, acc0[4 * j + 2] + o.z, acc0[4 * j + 3] + o.w);
-      }
-      *reinterpret_cast<float4*>(dst + 4 * j) = v;
+      float4* p = reinterpret_cast<float4*>(stage + (dxe * 128 + row) * 32 + ((j ^ (row & 7)) << 2));
+      const float4 o = *p;
+      *p = make_float4(acc0[4 * j] + o.x, acc0[4 * j + 1] + o.y, acc0[4 * j + 2] + o.z, acc0[4 * j + 3] + o.w);
     }
-  } else if (warp == 8) {
-    // bias gradient: channel n = lane, fixed-order sum over the 121 windows (and over the samples, in the registers above)
+  }
+  if (tid == 64) wg_stamp(a.trace, 3, 7);
+  __syncthreads();
+  if (warp < 8) {
+    // write-out: 8 lanes per row (16 bytes each), 4 rows per instruction; 4 consecutive channels are 4 consecutive rows of
+    // the reference order, i.e. 512 contiguous bytes (instead of every thread writing its own row 16 bytes at a
+    // time, 32 separate lines per instruction)
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+      const int r = warp * 32 + it * 4 + (lane >> 3), ch = lane & 7;            // r = dx * 128 + dy * 64 + c64
+      const int rdx = r >> 7, rdy = (r >> 6) & 1, c64 = r & 63;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (ntiles > 0) v = *reinterpret_cast<const float4*>(stage + r * 32 + ((ch ^ (r & 7)) << 2));
+      *reinterpret_cast<float4*>(out + (size_t)kref(rdy, rdx, c64) * 32 + ch * 4) = v;
+    }
+  }
+  if (warp == 8) {
+    // bias gradient: channel n = lane, the builder warps' partial sums added in warp order
     float s = 0.f;
-    if (ntiles > 0)
-      for (int m = 0; m < NWIN; ++m) s += csum[lane * NWIN + m];
+    if (ntiles > 0) {
+#pragma unroll
+      for (int w = 0; w < WG_BUILD_WARPS; ++w) s += csum[w * 32 + lane];
+    }
     out[256 * 32 + lane] = s;
   }
+  if (tid == 64) wg_stamp(a.trace, 1, 7);
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem, 128);

@@ -1269,6 +1269,7 @@ static void launch_conv1_s2d_wgrad(dqn_net_s* h, const umma::s2d::Src& src, int 
   a.arg = h->arg[0][0];
   a.partial = h->L[0].partial;
   a.B = B;
+  a.trace = h->dp_world > 1 ? nullptr : s2d_trace_ptr();      // (the stamps share their slots with the data-parallel exchange stamps)
   const int grid = B < h->num_sms ? B : h->num_sms;
   {
     StageScope sc(h, DQN_STAGE_WGRAD_CONV1, st);
@@ -1456,9 +1457,9 @@ static int run_trunk_tc(dqn_net_s* h, int npass, const void* const x[2], const i
         else launch_fwd_res<C3, 64, 3, 2>(a, npass, st);
         break;
       case 3:          // few rows: narrow tiles spread the weight traffic over more SMs (a lone CTA is bound by its SM's L2 port)
-        if (B <= 64) launch_fwd_tc<F4, __nv_bfloat16, 32, 4, 4>(a, npass, h->num_sms, st);
-        else if (B <= 256) launch_fwd_tc<F4, __nv_bfloat16, 64, 4, 4>(a, npass, h->num_sms, st);
-        else launch_fwd_tc<F4, __nv_bfloat16, 256, 4, 4>(a, npass, h->num_sms, st);
+        // 32-column tiles at every batch size: the layer is tiny (256x256 weights), so its time is the latency of ONE
+        // CTA's chain of loads; more, narrower CTAs shorten it (B=512: 10.4 -> 4.0 us against 256-column tiles)
+        launch_fwd_tc<F4, __nv_bfloat16, 32, 4, 4>(a, npass, h->num_sms, st);
         break;
     }
   }
@@ -1719,9 +1720,7 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
       if (early_exchange_fc()) return DQN_ERR_CUDA;
       DQN_CUDA(cudaEventRecord(h->ev_head, sh));
       if (!fused) {                  // the fused kernel already produced the fc data gradient
-        if (k <= 64) launch_dgrad_tc<F4, 32>(h, 3, k, st);
-        else if (k <= 256) launch_dgrad_tc<F4, 64>(h, 3, k, st);
-        else launch_dgrad_tc<F4, 256>(h, 3, k, st);
+        launch_dgrad_tc<F4, 32>(h, 3, k, st);          // narrow tiles, see the fc forward
         if (fork_after_dgrad(1)) return DQN_ERR_CUDA;
       }
       launch_wgrad_tc<C3, __nv_bfloat16, 64>(h, 2, h->act_bf[0][1], k, sd, &nsplit[2]); if (h->no_resident) launch_dgrad_tc<C3, 64>(h, 2, k, st); else launch_dgrad_res<C3, 64, 3, 2>(h, 2, k, st);

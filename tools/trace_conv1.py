@@ -53,3 +53,12 @@ tot, cnt = c.c_f64(), c.c_i32()
 c.lib.dqn_net_timing_read(net.handle, 1, C.byref(tot), C.byref(cnt))
 print("eager event bracket fwd_conv1: %.2f us (mean of %d)" % (tot.value / cnt.value * 1e3, cnt.value))
 fl = c.c_f64(); c.lib.dqn_net_timing_floor(net.handle, c.current_stream(), C.byref(fl)); print("empty-launch floor %.2f us" % fl.value)
+# weight-gradient kernel, CTA 0 (stamps at 1136 + 8*tile + ev)
+n2 = 60 * 8 + 160 * 4 + 16 + 64
+buf2 = (C.c_uint64 * n2)()
+assert c.lib.dqn_debug_trace(buf2, n2) == 0
+wn = ["stack landed", "prev MMAs done", "image built", "grad landed", "dZ routed", "mma start", "mma issued", "(t0: MMAs done, t1: exit)"]
+w0 = buf2[1136]
+print("weight gradient, CTA 0 (clk)\ntile " + " ".join("%14s" % x for x in wn))
+for t in range(5):
+    print("%4d " % t + " ".join("%14d" % (buf2[1136 + t * 8 + e] - w0 if buf2[1136 + t * 8 + e] else -1) for e in range(8)))
