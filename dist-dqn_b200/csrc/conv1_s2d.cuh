@@ -472,8 +472,9 @@ __device__ __forceinline__ void wg_stamp(unsigned long long* trace, int tile, in
 
 constexpr uint32_t WG_GRAD_BYTES = NWIN * 32 * 2, WG_ARG_BYTES = NWIN * 32;          // 7744, 3872 per sample
 constexpr uint32_t WG_GA_SLOT = 12 * 1024;                                           // gradient (8 KB) + arg-max (4 KB) staging
-constexpr uint32_t WG_OFF_IMG = 2 * RAW_BYTES, WG_OFF_DZ = WG_OFF_IMG + IMG_BYTES, WG_OFF_GA = WG_OFF_DZ + 4 * 8192;
-constexpr uint32_t WG_SMEM = SMEM_SLACK + WG_OFF_GA + 2 * WG_GA_SLOT;                // 181,248 bytes
+constexpr uint32_t WG_DZ_SET = 4 * 8192;                                             // the four routed gradient tiles of a sample
+constexpr uint32_t WG_OFF_IMG = 2 * RAW_BYTES, WG_OFF_DZ = WG_OFF_IMG + IMG_BYTES, WG_OFF_GA = WG_OFF_DZ + 2 * WG_DZ_SET;
+constexpr uint32_t WG_SMEM = SMEM_SLACK + WG_OFF_GA + 2 * WG_GA_SLOT;                // 214,016 bytes
 constexpr int WG_BUILD_WARP0 = 2, WG_BUILD_WARPS = NWARPS - WG_BUILD_WARP0, WG_BUILDERS = WG_BUILD_WARPS * 32;
 
 template <bool PLANAR>
@@ -496,7 +497,7 @@ __global__ void __launch_bounds__(NWARPS * 32, 1) conv1_s2d_wgrad_kernel(WgradAr
   }
   if (warp == 1) tmem_alloc(&tmem_slot, 128);                 // four 128x32 fp32 accumulators
   // image padding and the unused dZ rows (m >= 121) stay zero for the whole kernel (the reduction runs over them)
-  for (int i = tid; i < (int)((IMG_BYTES + 4 * 8192) / 16); i += NWARPS * 32)
+  for (int i = tid; i < (int)((IMG_BYTES + 2 * WG_DZ_SET) / 16); i += NWARPS * 32)
     reinterpret_cast<uint4*>(smem + WG_OFF_IMG)[i] = make_uint4(0u, 0u, 0u, 0u);
   fence_async_proxy();
   tc_fence_before();
@@ -547,7 +548,7 @@ __global__ void __launch_bounds__(NWARPS * 32, 1) conv1_s2d_wgrad_kernel(WgradAr
             const int r0 = wy ? img_row(2, t) : img_row(0, t);
             const int r1 = img_row(1, t);
             const uint64_t ad0 = make_desc_sw128_mn(img + (uint32_t)r0 * 128u, (uint32_t)(r1 - r0) * 128u, 1024);
-            const uint64_t bd0 = make_desc(sbase + WG_OFF_DZ + (wy * 2 + wx) * 8192, 128, 2048);
+            const uint64_t bd0 = make_desc(sbase + WG_OFF_DZ + (i & 1) * WG_DZ_SET + (wy * 2 + wx) * 8192, 128, 2048);
 #pragma unroll
             for (int j = 0; j < 8; ++j)
               mma_bf16(tmem + wy * 64 + col * 32, desc_advance(ad0, j * 2048), desc_advance(bd0, j * 256), idesc,
@@ -565,17 +566,16 @@ __global__ void __launch_bounds__(NWARPS * 32, 1) conv1_s2d_wgrad_kernel(WgradAr
   } else {
     // ---------------------------------------------------------------- builders: image + routed gradient tiles
     const int bt = tid - WG_BUILD_WARP0 * 32;
-    for (int i = 0; i < ntiles; ++i) {
+    // The routed gradient tiles are double-buffered: those of sample i are written while the MMAs of sample i-1 still
+    // run (their set was last read by sample i-2, whose completion this thread saw before it built image i-1); only the
+    // image, 64 KB, is single and waits for the MMAs.  Sample 0 goes the other way round: its image can be built before
+    // the gradient has landed (before the predecessor kernel has finished, even).
+    auto route = [&](int i) {
       const int rb = i & 1;
-      mbar_wait(&stk_full[rb], (i >> 1) & 1);
-      if (bt == 0) wg_stamp(a.trace, i, 0);
-      if (i > 0) mbar_wait(&op_empty, (i - 1) & 1);             // the previous sample's MMAs have read the operands
-      if (bt == 0) wg_stamp(a.trace, i, 1);
-      build_image<PLANAR, false>(smem + rb * RAW_BYTES, smem + WG_OFF_IMG, bt);
-      if (bt == 0) wg_stamp(a.trace, i, 2);
       mbar_wait(&ga_full[rb], (i >> 1) & 1);
       if (bt == 0) wg_stamp(a.trace, i, 3);
       const uint8_t* ga = smem + WG_OFF_GA + rb * WG_GA_SLOT;
+      uint8_t* dz = smem + WG_OFF_DZ + rb * WG_DZ_SET;
 #pragma unroll
       for (int q = 0; q < 2; ++q) {
         const int item = bt + q * WG_BUILDERS;                  // item = (m, channel chunk cq): m = item >> 2
@@ -586,12 +586,23 @@ __global__ void __launch_bounds__(NWARPS * 32, 1) conv1_s2d_wgrad_kernel(WgradAr
           add_chunk(colsum[q], d);
           const uint32_t off = (uint32_t)(cq * 2048 + (m >> 3) * 128 + (m & 7) * 16);
 #pragma unroll
-          for (int w = 0; w < 4; ++w) *reinterpret_cast<uint4*>(smem + WG_OFF_DZ + w * 8192 + off) = route_chunk(d, ag, w);
+          for (int w = 0; w < 4; ++w) *reinterpret_cast<uint4*>(dz + w * 8192 + off) = route_chunk(d, ag, w);
         }
       }
+      if (bt == 0) wg_stamp(a.trace, i, 4);
+    };
+    for (int i = 0; i < ntiles; ++i) {
+      const int rb = i & 1;
+      if (i > 0) route(i);
+      mbar_wait(&stk_full[rb], (i >> 1) & 1);
+      if (bt == 0) wg_stamp(a.trace, i, 0);
+      if (i > 0) mbar_wait(&op_empty, (i - 1) & 1);             // the previous sample's MMAs have read the image
+      if (bt == 0) wg_stamp(a.trace, i, 1);
+      build_image<PLANAR, false>(smem + rb * RAW_BYTES, smem + WG_OFF_IMG, bt);
+      if (bt == 0) wg_stamp(a.trace, i, 2);
+      if (i == 0) route(0);
       fence_async_proxy();
       __syncwarp();
-      if (bt == 0) wg_stamp(a.trace, i, 4);
       if (lane == 0) {
         mbar_arrive(&op_full);
         mbar_arrive(&ld_empty[rb]);
