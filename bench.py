@@ -888,6 +888,17 @@ def roofline(kernels, arch, batch, nparams, floor_us=0.0):
                 "peak_source": src + " bf16 sustained",
                 "note": "implicit GEMM against the measured bf16 tensor-pipe peak; at batch 32 every kernel is a few "
                         "CTAs of latency-bound work and the fraction only says so -- see roofline_large_batch"}
+    if name == "fc_td_fused":
+        # fc forward of both nets + Q head of both + fc data gradient, one cluster launch
+        flops = 2.0 * (3 * macs[3] + 2 * 256 * A_PONG) * batch
+        ach = flops / (us * 1e-6) / 1e12
+        return {"kernel": name, "bound": "tensor", "achieved": ach, "peak": sustained, "unit": "TFLOP/s",
+                "frac": ach / sustained, "traffic": traffic, "traffic_source": tsrc, "us_per_launch": us,
+                "us_event_bracket": raw_us, "event_floor_us": floor_us, "minibatch": batch,
+                "peak_source": src + " bf16 sustained",
+                "note": "fc forward (both nets) + Q head + TD target/loss/gradient + fc data gradient in ONE 8-CTA cluster "
+                        "launch: 13 MFLOP behind three cluster barriers, a latency chain, not a throughput kernel -- the "
+                        "fraction only says so; see roofline_large_batch for a kernel that fills the GPU"}
     if name == "gather":
         byts = GATHER_BYTES * batch
     elif name in ("optimizer", "reduce_grad"):

@@ -335,8 +335,9 @@ __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs a) {
     __syncthreads();
   }
   const long long step = *a.step;
-  if (a.world > 1) {
-    // wait until every rank has published its gradient of this step
+  if (a.world > 1 && ((a.peer_mask >> blockIdx.y) & 1)) {
+    // wait until every rank has published its gradient of this step (segments that were exchanged earlier in the step
+    // do not wait: their blocks finish while the flags are still on their way)
     const bool tr0 = threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0;
     if (tr0) dp_stamp(a.trace, 48);
     if (threadIdx.x < 32) wait_peer_flags(a, (unsigned long long)step);
