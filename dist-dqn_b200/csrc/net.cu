@@ -213,6 +213,13 @@ struct OptArgs {
   long long timeout_ns;                  // how long a rank waits for its peers' flags before it reports them missing
   unsigned long long* err;               // device word: last step whose wait timed out (0 = none); read by dqn_net_dp_status
   unsigned long long* trace;             // DQN_S2D_TRACE=1: globaltimer stamps of the exchange (tools/trace_dp.py), else null
+  // optimizer only, conv nets: the blocks of the peer-summed segments first PUBLISH this rank's gradient of those segments
+  // (sum of the weight-gradient partials -> exchange block, block counter, flags), then wait and sum over the ranks
+  unsigned long long* const* pub_flags;  // null: a separate kernel published (MLP, NCCL mode)
+  unsigned int* pub_counter;
+  float* pub_grad;                       // this rank's exchange gradient buffers [2][P]
+  int pub_total;                         // blocks that publish (those with work in the peer-summed segments)
+  int rank, pub_sys_release;
 };
 __device__ __forceinline__ void dp_stamp(unsigned long long* trace, int slot, bool max_of_all = false) {
   if (!trace) return;
@@ -336,9 +343,34 @@ __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs a) {
   }
   const long long step = *a.step;
   if (a.world > 1 && ((a.peer_mask >> blockIdx.y) & 1)) {
+    const bool tr0 = threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0;
+    if (a.pub_flags && (int)blockIdx.x < (s.len + 255) / 256) {
+      // Publish first: this rank's gradient of the element (sum of the weight-gradient partials) goes to its exchange
+      // block; the last block to get there raises the rank's flag on every peer (see reduce_grad_kernel).  Every block
+      // that waits below has published before, and the few hundred blocks of these segments are the first of the grid
+      // to be scheduled (blockIdx.y = 0, 1) and all fit on the GPU at once, so the wait cannot starve a publisher.
+      if (tr0) dp_stamp(a.trace, 8);
+      if (i < s.len) a.pub_grad[(size_t)(step & 1) * (size_t)a.P + (size_t)s.off + i] = seg_grad(s, i);
+      __shared__ bool last;
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        __threadfence();
+        last = atomicAdd(a.pub_counter, 1u) == (unsigned)a.pub_total - 1u;
+      }
+      __syncthreads();
+      if (last) {
+        if (threadIdx.x == 0) { *a.pub_counter = 0; dp_stamp(a.trace, 9); }
+        if ((int)threadIdx.x < a.world) {
+          __threadfence();
+          unsigned long long* f = a.pub_flags[threadIdx.x] + 8 * a.flag_slot + a.rank;
+          if (a.pub_sys_release) asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(f), "l"((unsigned long long)step) : "memory");
+          else asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(f), "l"((unsigned long long)step) : "memory");
+          if (threadIdx.x == 0) dp_stamp(a.trace, 10);
+        }
+      }
+    }
     // wait until every rank has published its gradient of this step (segments that were exchanged earlier in the step
     // do not wait: their blocks finish while the flags are still on their way)
-    const bool tr0 = threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0;
     if (tr0) dp_stamp(a.trace, 48);
     if (threadIdx.x < 32) wait_peer_flags(a, (unsigned long long)step);
     if (tr0) dp_stamp(a.trace, 49);
@@ -434,6 +466,10 @@ struct PublishArgs {
   int segs;                                // segments this launch covers, 4 bits each: blockIdx.y -> (segs >> 4*y) & 15
   int sys_release;                         // 1: raise the flags with a system-scope release store (see reduce_grad_kernel)
 };
+static int dp_separate_publish() {     // DQN_DP_SEPARATE_PUBLISH=1: conv1 / conv2 are published by a kernel of their own (A/B switch)
+  static const int v = [] { const char* e = getenv("DQN_DP_SEPARATE_PUBLISH"); return e && e[0] == '1' ? 1 : 0; }();
+  return v;
+}
 static int dp_sys_release() {
   static const int v = [] { const char* e = getenv("DQN_DP_SYS_RELEASE"); return e && e[0] == '1' ? 1 : 0; }();
   return v;
@@ -1770,7 +1806,7 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
     DQN_CUDA(cudaStreamWaitEvent(st, h->ev_join, 0));
     DQN_CUDA(cudaStreamWaitEvent(st, h->ev_head, 0));
     DQN_CUDA(cudaGetLastError());
-    if (mode == 2) {
+    if (mode == 2 && dp_separate_publish()) {
       // last part of the exchange: conv1 and conv2 (segments 0, 1) are published here and summed by the optimizer.  (conv2
       // as a part of its own behind its weight gradient was measured: that chain of two kernels ends after this one.)
       set_dp_args(h, &oa, 1);
@@ -1800,10 +1836,23 @@ static int run_step(dqn_net_s* h, const void* d_states, const void* d_next, cons
     // the reduce kernel above published this rank's gradient; now sum all ranks' gradients inside the optimizer
     // (peer loads over NVLink)
     const int one[4] = {1, 1, 1, 1};
+    OptArgs part = oa;                         // conv nets: segments with the weight-gradient partials of this step
     fill_segs(h, &oa, one, true);
     set_dp_args(h, &oa, 1);
     // conv nets: only segments 0, 1 (conv1, conv2) are still to be summed over the ranks; the MLP exchanges everything here
     oa.peer_mask = h->arch == DQN_ARCH_SIMPLE ? 0x7 : 0x3;
+    if (h->arch != DQN_ARCH_SIMPLE && !dp_separate_publish()) {
+      // the optimizer's own blocks publish conv1 / conv2 (no separate kernel on the critical path)
+      for (int l = 0; l < 2; ++l) {
+        oa.seg[l].partial = part.seg[l].partial; oa.seg[l].nsplit = part.seg[l].nsplit; oa.seg[l].stride = part.seg[l].stride;
+      }
+      oa.pub_flags = h->dp_peer_flags_dev;
+      oa.pub_counter = h->dp_counter + 1;
+      oa.pub_grad = h->dp_grad;
+      oa.pub_total = (oa.seg[0].len + 255) / 256 + (oa.seg[1].len + 255) / 256;
+      oa.rank = h->dp_rank;
+      oa.pub_sys_release = dp_sys_release();
+    }
     dim3 grid((max_seg_len(oa) + 255) / 256, oa.nseg);
     StageScope sc(h, DQN_STAGE_OPTIMIZER, st);
     launch_pdl(optimizer_kernel, grid, dim3(256), 0, st, 1, oa);

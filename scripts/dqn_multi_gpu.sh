@@ -20,4 +20,4 @@ if [[ "$num_gpus" -le 1 ]]; then
 fi
 echo "Starting $num_gpus workers (one per GPU). Train logs: $LOG_ROOT/train"
 exec python -m torch.distributed.run --nnodes=1 --nproc-per-node="$num_gpus" --master-addr 127.0.0.1 \
-  --master-port "${DQN_MASTER_PORT:-29533}" "$HERE/../dist-dqn_b200/main.py" $common
+  --master-port "${DQN_MASTER_PORT:-29533}" -- "$HERE/../dist-dqn_b200/main.py" $common      # "--": main.py's --monitor is not torchrun's
