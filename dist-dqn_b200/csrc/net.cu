@@ -766,6 +766,7 @@ struct Tensor { int64_t off, numel; int rank; int64_t shape[4]; };
 struct GemmLayer {           // conv1..3 + fc of the conv architectures
   int K, N, rows, in_elems, out_elems;
   int maxsplit;
+  int maxsplit_tc;        // cap of the reduction split of the tensor-core weight-gradient kernel
   float* partial = nullptr;
   int w_tensor;              // index of the weight tensor (bias = +1)
 };
@@ -940,7 +941,11 @@ extern "C" int dqn_net_create(dqn_net_t* out, int32_t arch, const int32_t* in_sh
       const int base = (K / BM) * (N / BN);
       int ms = (3 * h->num_sms + base - 1) / base;
       l.maxsplit = ms < 1 ? 1 : (ms > h->num_sms ? h->num_sms : ms);
-      if (i == 0) l.maxsplit = h->num_sms;      // conv1's resident weight-gradient kernel: one CTA per SM
+      // tensor-core weight gradients tile the output as 128 x 64 (fc: 128 x 128): one wave of CTAs over the reduction splits
+      const int base_tc = ((K + 127) / 128) * (i == 3 ? (N + 127) / 128 : (N + 63) / 64);
+      l.maxsplit_tc = h->num_sms / base_tc < 1 ? 1 : h->num_sms / base_tc;
+      if (l.maxsplit < l.maxsplit_tc) l.maxsplit = l.maxsplit_tc;     // the partial-sum scratch is sized by maxsplit
+      if (i == 0) l.maxsplit = l.maxsplit_tc = h->num_sms;      // conv1's resident weight-gradient kernel: one CTA per SM
     };
     if (!nat) {
       setL(0, C1::K, C1::COUT, C1::ROWS, 84 * 84 * 4, C1::OUT_PER_SAMPLE);
@@ -1335,7 +1340,7 @@ static void launch_wgrad_tc(dqn_net_s* h, int l, const void* x, int B, cudaStrea
   const GemmLayer& L = h->L[l];
   const int R = B * G::ROWS;
   const int tiles = (R + umma::TK - 1) / umma::TK;
-  int ns = L.maxsplit < tiles ? L.maxsplit : tiles;
+  int ns = L.maxsplit_tc < tiles ? L.maxsplit_tc : tiles;
   const int per = (tiles + ns - 1) / ns;
   ns = (tiles + per - 1) / per;
   umma::WgradArgsT a{x, h->dact_bf[l], l < 3 ? h->arg[0][l] : nullptr, L.partial, B, per * umma::TK};
