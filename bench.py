@@ -245,7 +245,9 @@ def workload_config(arch, batch, n, capacity):
             "arch": arch, "minibatch_per_gpu": batch, "global_batch": batch * n, "replay_capacity_per_gpu": capacity,
             "parallelism": "dp%d" % n,
             "cache": "inputs larger than L2: each step gathers fresh random transitions from a %.1f GB frame ring"
-                     % (capacity * FRAME / 1e9)}
+                     % (capacity * FRAME / 1e9),
+            "indices": "random.sample per step, drawn before timing and resident in HBM as one table; the captured "
+                       "update takes its own row (dqn_index_table_next, one kernel) -- the host only replays the graph"}
 
 
 # ----------------------------------------------------------------------------------------------- own arm
@@ -464,17 +466,23 @@ def run_update_bench(args, torch, dist, dp, rank, local, world, dev):
         torch.cuda.synchronize()
         launches_per_step = c.lib.dqn_launch_count() - n0
 
+        # The captured update starts with ONE kernel that takes the step's row of the index table (fresh indices every
+        # step, the ring is far larger than L2) and advances a device-side cursor: the host only replays the graph.
         graph = None
         if not args.no_graph:
+            cursor_table = replay_memory.IndexTable(idx_table, dev)
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph, stream=side):
+                cursor_table.next(d_idx)
                 eager_step()
+            cursor_table.cursor.zero_()
+            launches_per_step += 1
 
         def step(i):
-            d_idx.copy_(idx_table[i], non_blocking=True)
             if graph is not None:
                 graph.replay()
             else:
+                d_idx.copy_(idx_table[i], non_blocking=True)
                 eager_step()
 
         def after(j):
@@ -573,15 +581,19 @@ def large_batch_block(args, torch, c, network, rm, dev, side, batch=512, steps=1
     d_idx.copy_(tab[0])
     for _ in range(3):
         net.train_step(rm, batch, d_indices=d_idx)
+    import replay_memory
+    cursor_table = replay_memory.IndexTable(tab, dev)
     g = torch.cuda.CUDAGraph()
     with torch.cuda.graph(g, stream=side):
+        cursor_table.next(d_idx)                       # as in run_update_bench: the graph takes its own row of indices
         net.train_step(rm, batch, d_indices=d_idx)
+    cursor_table.cursor.zero_()
     for i in range(10):
-        d_idx.copy_(tab[i], non_blocking=True); g.replay()
+        g.replay()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for i in range(steps):
-        d_idx.copy_(tab[10 + i], non_blocking=True); g.replay()
+        g.replay()
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / steps

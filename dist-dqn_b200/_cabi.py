@@ -54,6 +54,7 @@ SIGNATURES = {
     "dqn_replay_size": (C.c_int, [c_vp, C.POINTER(c_i64), C.POINTER(c_i64)]),
     "dqn_replay_next_frame_pos": (C.c_int, [c_vp, C.POINTER(c_i64)]),
     "dqn_replay_gather": (C.c_int, [c_vp, c_vp, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "dqn_index_table_next": (C.c_int, [c_vp, c_i64, c_i32, c_vp, c_vp, c_vp]),
     "dqn_net_create": (C.c_int, [C.POINTER(c_vp), c_i32, C.POINTER(c_i32), c_i32, c_i32, c_i32, c_i32, c_i32]),
     "dqn_net_destroy": (C.c_int, [c_vp]),
     "dqn_net_param_count": (C.c_int, [c_vp, C.POINTER(c_i64), C.POINTER(c_i32)]),

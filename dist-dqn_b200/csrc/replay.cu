@@ -736,6 +736,27 @@ int dqn_replay_view_(dqn_replay_t h, dqn::RingView* out) {
 }
 int dqn_replay_device_(dqn_replay_t h) { return h->device; }
 
+// row (*cursor % rows) of a device-resident [rows][k] index table -> idx; *cursor += 1
+__global__ void __launch_bounds__(256) index_table_next_kernel(const int32_t* __restrict__ table, long long rows, int k,
+                                                               long long* __restrict__ cursor, int32_t* __restrict__ idx) {
+  pdl_trigger();
+  pdl_wait();
+  const long long cur = *cursor;
+  const int32_t* row = table + (size_t)(cur % rows) * (size_t)k;
+  for (int i = threadIdx.x; i < k; i += blockDim.x) idx[i] = row[i];
+  __syncthreads();                          // every thread has read the cursor
+  if (threadIdx.x == 0) *cursor = cur + 1;
+}
+
+extern "C" int dqn_index_table_next(const int32_t* d_table, int64_t rows, int32_t k, int64_t* d_cursor, int32_t* d_idx,
+                                    dqn_stream_t stream) {
+  DQN_REQUIRE(d_table && d_cursor && d_idx && rows > 0 && k > 0, DQN_ERR_INVALID, "index_table_next: bad argument");
+  dqn::count_launch();
+  DQN_CUDA(launch_pdl(index_table_next_kernel, dim3(1), dim3(256), 0, static_cast<cudaStream_t>(stream), 1, d_table,
+                      (long long)rows, (int)k, reinterpret_cast<long long*>(d_cursor), d_idx));
+  return 0;
+}
+
 extern "C" int dqn_replay_gather(dqn_replay_t h, const int32_t* d_logical_idx, int32_t k, void* d_states,
                                  void* d_next_states, int32_t* d_actions, double* d_rewards, uint8_t* d_terminals,
                                  dqn_stream_t stream) {

@@ -321,3 +321,24 @@ class ReplayMemory(object):
         k = 0 if pinned_idx is None else int(pinned_idx.numel())
         _c.check(_c.lib.dqn_replay_ingest_staged(self._h, int(stage), _c.ptr(pinned_idx), _c.ptr(d_idx), k,
                                                  _c.current_stream()), "ReplayMemory.ingest_staged")
+
+
+class IndexTable(object):
+    """Sample indices of the next `rows` updates, drawn at once on the host (``random.sample`` per update, the
+    reference's sampler, dqn_agent.py:110) and kept on the device: ``next(d_idx)`` enqueues ONE kernel that copies
+    the current row into ``d_idx`` and advances a device-side cursor, so a captured update replays without the host
+    touching the indices again (dqn_index_table_next)."""
+
+    def __init__(self, rows_of_indices, device):
+        import torch
+        if isinstance(rows_of_indices, torch.Tensor):
+            self.table = rows_of_indices.to(device=device, dtype=torch.int32).contiguous()
+        else:
+            self.table = torch.tensor(rows_of_indices, dtype=torch.int32, device=device).contiguous()
+        self.rows, self.k = int(self.table.shape[0]), int(self.table.shape[1])
+        self.cursor = torch.zeros(1, dtype=torch.int64, device=device)
+
+    def next(self, d_idx):
+        _c.check(_c.lib.dqn_index_table_next(_c.ptr(self.table), self.rows, self.k, _c.ptr(self.cursor), _c.ptr(d_idx),
+                                             _c.current_stream()), "IndexTable.next")
+        return d_idx

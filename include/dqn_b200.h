@@ -163,6 +163,14 @@ int dqn_replay_gather(dqn_replay_t h, const int32_t* d_logical_idx, int32_t k, v
                       void* d_next_states, int32_t* d_actions, double* d_rewards, uint8_t* d_terminals,
                       dqn_stream_t stream);
 
+/* Pre-drawn sample indices resident on the device: a host that draws the index sets of the next `rows` updates at
+ * once (random.sample per update, dqn_agent.py:110, uploaded as one [rows][k] int32 table) replays a captured update
+ * without touching the indices again.  ONE kernel: copies row (*d_cursor % rows) to d_idx and advances *d_cursor
+ * (int64, caller-owned device memory, start it at 0).  Capturable; the kernel that follows it on the stream may be
+ * launched with programmatic dependent launch. */
+int dqn_index_table_next(const int32_t* d_table, int64_t rows, int32_t k, int64_t* d_cursor, int32_t* d_idx,
+                         dqn_stream_t stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Q-network -- replaces Network.create_network and the graph it builds (network.py:13-116), the
  * session.run calls of DQNAgent (dqn_agent.py:132-138, 189, 222) and the host TD-target loop

@@ -254,3 +254,27 @@ def test_batched_actor_epsilon_greedy_matches_the_reference_rule():
     assert 0 < rm.size() <= 30 * E and actor.random_action_prob <= cfg.min_random_action_prob + 1e-9
     q = net.predict(rm.current_states())
     assert q.shape == (E, 6) and bool(q.isfinite().all())
+
+
+def test_index_table_next_walks_the_rows_and_wraps():
+    """dqn_index_table_next: the captured update's own source of sample indices -- row (cursor % rows) of a
+    device-resident table, cursor advanced on the device, also inside a CUDA graph."""
+    _mods()
+    import torch
+    import replay_memory as R
+    rows = [[r * 10 + j for j in range(5)] for r in range(3)]
+    tab = R.IndexTable(rows, torch.device("cuda", 0))
+    d_idx = torch.full((5,), -1, dtype=torch.int32, device="cuda")
+    seen = []
+    for _ in range(4):
+        tab.next(d_idx)
+        seen.append(d_idx.cpu().tolist())
+    assert seen == [rows[0], rows[1], rows[2], rows[0]] and int(tab.cursor.item()) == 4
+    side = torch.cuda.Stream()
+    with torch.cuda.stream(side):
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=side):
+            tab.next(d_idx)
+        g.replay(); g.replay()
+    torch.cuda.synchronize()
+    assert d_idx.cpu().tolist() == rows[(4 + 2 - 1) % 3] and int(tab.cursor.item()) == 6
