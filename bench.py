@@ -247,7 +247,8 @@ def workload_config(arch, batch, n, capacity):
             "cache": "inputs larger than L2: each step gathers fresh random transitions from a %.1f GB frame ring"
                      % (capacity * FRAME / 1e9),
             "indices": "random.sample per step, drawn before timing and resident in HBM as one table; the captured "
-                       "update takes its own row (dqn_index_table_next, one kernel) -- the host only replays the graph"}
+                       "update reads its own row and advances the cursor (dqn_train_step_table) -- the host only "
+                       "replays the graph"}
 
 
 # ----------------------------------------------------------------------------------------------- own arm
@@ -466,24 +467,26 @@ def run_update_bench(args, torch, dist, dp, rank, local, world, dev):
         torch.cuda.synchronize()
         launches_per_step = c.lib.dqn_launch_count() - n0
 
-        # The captured update starts with ONE kernel that takes the step's row of the index table (fresh indices every
-        # step, the ring is far larger than L2) and advances a device-side cursor: the host only replays the graph.
+        # The captured update reads the step's row of the index table itself (fresh indices every step, the ring is far
+        # larger than L2) and advances the table's device-side cursor: the host only replays the graph.
         graph = None
+        copy_indices = os.environ.get("DQN_BENCH_COPY_INDICES") == "1"      # A/B: a D2D copy in front of every replay
         if not args.no_graph:
             cursor_table = replay_memory.IndexTable(idx_table, dev)
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph, stream=side):
-                cursor_table.next(d_idx)
-                eager_step()
+                if copy_indices:
+                    eager_step()
+                else:
+                    dp.train_step_table(net, rm, cursor_table)      # the conv1 kernels read the row, the optimizer advances the cursor
             cursor_table.cursor.zero_()
-            launches_per_step += 1
 
         def step(i):
-            if graph is not None:
+            if graph is not None and not copy_indices:
                 graph.replay()
             else:
                 d_idx.copy_(idx_table[i], non_blocking=True)
-                eager_step()
+                graph.replay() if graph is not None else eager_step()
 
         def after(j):
             if j % 10000 == 9999:
@@ -585,8 +588,7 @@ def large_batch_block(args, torch, c, network, rm, dev, side, batch=512, steps=1
     cursor_table = replay_memory.IndexTable(tab, dev)
     g = torch.cuda.CUDAGraph()
     with torch.cuda.graph(g, stream=side):
-        cursor_table.next(d_idx)                       # as in run_update_bench: the graph takes its own row of indices
-        net.train_step(rm, batch, d_indices=d_idx)
+        net.train_step_table(rm, cursor_table)         # as in run_update_bench: the update takes its own row of indices
     cursor_table.cursor.zero_()
     for i in range(10):
         g.replay()

@@ -80,6 +80,7 @@ SIGNATURES = {
     "dqn_net_dp_step": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
     "dqn_train_step_dp": (C.c_int, [c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
     "dqn_train_step": (C.c_int, [c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
+    "dqn_train_step_table": (C.c_int, [c_vp, c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_vp, c_i32, c_vp]),
     "dqn_preproc_create": (C.c_int, [C.POINTER(c_vp), c_i32, c_i32, c_i32, c_i32, c_i32]),
     "dqn_preproc_destroy": (C.c_int, [c_vp]),
     "dqn_preproc_run": (C.c_int, [c_vp, c_vp, c_i32, c_vp, c_vp]),

@@ -61,6 +61,11 @@ struct Src {
   const void* meta;
   const int64_t* ring_state;
   const int32_t* idx;
+  // idx_cursor != null: idx is a [idx_rows][idx_k] table of pre-drawn index sets and the update uses row
+  // (*idx_cursor % idx_rows); the optimizer advances the cursor at the end of the update (dqn_train_step_table)
+  const int64_t* idx_cursor;
+  int64_t idx_rows;
+  int32_t idx_k;
   int64_t capacity, frame_capacity;
   int32_t pitch;
   // scalars of the sampled transitions, written by pass 0 in ring mode (null = not wanted)
@@ -75,7 +80,9 @@ struct RingRec { int64_t state_pos, next_pos; double reward; int32_t action; uin
 // look-up is a chain of dependent global loads (index -> record -> positions), so a whole warp resolves up to 64 tiles
 // at once into a shared-memory table ahead of the copy loop.  Pass 0 also copies the transition's scalars.
 __device__ __forceinline__ void resolve_stack(const Src& s, int pass, int b, int64_t off[4]) {
-  int64_t slot = s.ring_state[0] + (int64_t)s.idx[b];
+  const int32_t* ip = s.idx;
+  if (s.idx_cursor) ip += (size_t)(*s.idx_cursor % s.idx_rows) * (size_t)s.idx_k;
+  int64_t slot = s.ring_state[0] + (int64_t)ip[b];
   if (slot >= s.capacity) slot -= s.capacity;
   const RingRec* r = static_cast<const RingRec*>(s.meta) + slot;
   const int64_t pos = pass ? r->next_pos : r->state_pos;

@@ -220,6 +220,7 @@ struct OptArgs {
   float* pub_grad;                       // this rank's exchange gradient buffers [2][P]
   int pub_total;                         // blocks that publish (those with work in the peer-summed segments)
   int rank, pub_sys_release;
+  long long* idx_cursor;                 // dqn_train_step_table: cursor of the index table, advanced here (null otherwise)
 };
 __device__ __forceinline__ void dp_stamp(unsigned long long* trace, int slot, bool max_of_all = false) {
   if (!trace) return;
@@ -322,6 +323,8 @@ __device__ __forceinline__ float seg_grad(const Seg& s, int i) {
 
 __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs a) {
   pdl_wait();
+  // every reader of this update's row of the index table (the conv1 kernels) has finished: the next update takes the next row
+  if (a.idx_cursor && threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0) *a.idx_cursor += 1;
   const Seg s = a.seg[blockIdx.y];
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   // bf16 mode, weight part of a conv / fc tensor: the block owns a tile of 8 reduction rows x 32 output columns instead
@@ -810,6 +813,7 @@ struct dqn_net_s {
   bool no_resident = false;                         // DQN_NO_RESIDENT=1: im2col gathers from L2 instead of a shared-memory resident input block
   bool no_fused_fc = true;                          // DQN_FUSED_FC=1: fc forward / TD head / fc dgrad as one launch (experimental)
   bool fc_cluster = true;                           // B <= 32: fc forward / TD head / fc dgrad as one 8-CTA cluster launch (DQN_NO_FC_CLUSTER=1: off)
+  long long* idx_cursor = nullptr;                  // set for the duration of a dqn_train_step_table call
   bool conv1_s2d = false;                           // reference conv net, bf16: conv1 forward / weight gradient in the space-to-depth formulation
   bool fuse_gather = true;                          // ... reading the frames straight from the replay ring in dqn_train_step (DQN_NO_FUSED_GATHER=1: off)
   cudaEvent_t ev_fork[3] = {}, ev_join = nullptr, ev_x = nullptr, ev_join2 = nullptr, ev_head = nullptr, ev_loss = nullptr;
@@ -1545,6 +1549,7 @@ static void fill_segs(dqn_net_s* h, OptArgs* o, const int nsplit[4], bool from_f
   o->world = 1; o->P = h->P;
   o->lr = h->hyper.lr; o->reg = h->hyper.reg_param; o->momentum = h->hyper.momentum; o->decay = h->hyper.rmsprop_decay;
   o->gscale = h->hyper.grad_scale; o->opt = h->hyper.optimizer;
+  o->idx_cursor = h->idx_cursor;
 }
 
 // data-parallel fields of the optimizer / exchange kernels' arguments
@@ -1911,11 +1916,23 @@ extern "C" int dqn_net_target_sync(dqn_net_t h, dqn_stream_t stream) {
 // Sample-to-update.  Reference conv net in bf16 mode: no gather launch -- the conv1 kernels fetch the frames of the
 // sampled transitions from the ring themselves (4 bulk copies per stack) and the forward kernel copies the scalars.
 // Everything else: gather into the net's staging buffers, then the step.
-static int step_from_ring(dqn_net_s* net, dqn_replay_t replay, const int32_t* d_idx, int k, float* d_loss, int mode, cudaStream_t st) {
+struct IndexTableRef { const int32_t* table; int64_t rows; int64_t* cursor; int32_t* scratch; };
+int dqn_index_table_next_(const int32_t* d_table, int64_t rows, int32_t k, int64_t* d_cursor, int32_t* d_idx, cudaStream_t st);
+
+static int step_from_ring(dqn_net_s* net, dqn_replay_t replay, const int32_t* d_idx, int k, float* d_loss, int mode, cudaStream_t st,
+                          const IndexTableRef* tab = nullptr) {
   RingView rv;
   dqn_replay_view_(replay, &rv);
-  if (net->conv1_s2d && net->fuse_gather && rv.frames_per_state == 4 && rv.elem_bytes == 1 &&
-      rv.frame_bytes == (int)umma::s2d::FRAME_BYTES) {
+  const bool fused = net->conv1_s2d && net->fuse_gather && rv.frames_per_state == 4 && rv.elem_bytes == 1 &&
+                     rv.frame_bytes == (int)umma::s2d::FRAME_BYTES;
+  if (tab && !fused) {
+    // kernels that cannot read the table themselves: one small kernel takes the row (and advances the cursor)
+    int rc = dqn_index_table_next_(tab->table, tab->rows, k, tab->cursor, tab->scratch, st);
+    if (rc) return rc;
+    d_idx = tab->scratch;
+    tab = nullptr;
+  }
+  if (fused) {
     int rc = dqn_replay_flush(replay, st);                  // frames / records staged on the host go to the ring first
     if (rc) return rc;
     umma::s2d::Src src;
@@ -1923,7 +1940,14 @@ static int step_from_ring(dqn_net_s* net, dqn_replay_t replay, const int32_t* d_
     src.frames = rv.frames; src.meta = rv.meta; src.ring_state = rv.state; src.idx = d_idx;
     src.capacity = rv.capacity; src.frame_capacity = rv.frame_capacity; src.pitch = rv.pitch;
     src.actions = net->st_actions; src.rewards = net->st_rewards; src.terminals = net->st_term;
-    return run_step(net, nullptr, nullptr, net->st_actions, net->st_rewards, net->st_term, k, d_loss, nullptr, mode, 0, st, &src);
+    if (tab) {
+      // the conv1 kernels read row (*cursor % rows) of the table themselves; the optimizer advances the cursor
+      src.idx = tab->table; src.idx_cursor = tab->cursor; src.idx_rows = tab->rows; src.idx_k = k;
+      net->idx_cursor = reinterpret_cast<long long*>(tab->cursor);
+    }
+    rc = run_step(net, nullptr, nullptr, net->st_actions, net->st_rewards, net->st_term, k, d_loss, nullptr, mode, 0, st, &src);
+    net->idx_cursor = nullptr;
+    return rc;
   }
   if (net->timing) stage_record(net->ev0[DQN_STAGE_GATHER], st);
   int rc = dqn_replay_gather(replay, d_idx, k, net->st_states, net->st_next, net->st_actions, net->st_rewards, net->st_term, st);
@@ -1951,6 +1975,23 @@ extern "C" int dqn_train_step(dqn_net_t net, dqn_replay_t replay, const int32_t*
               "replay stacks are %d bytes but the net expects %zu", rv.frame_bytes * rv.frames_per_state, net->state_bytes);
   DeviceGuard g(net->device);
   return step_from_ring(net, replay, d_logical_idx, k, d_loss, 0, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int dqn_train_step_table(dqn_net_t net, dqn_replay_t replay, const int32_t* d_table, int64_t rows, int32_t k,
+                                    int64_t* d_cursor, int32_t* d_idx_scratch, float* d_loss, int32_t data_parallel,
+                                    dqn_stream_t stream) {
+  DQN_REQUIRE(net && replay && d_table && d_cursor && d_idx_scratch && rows > 0, DQN_ERR_INVALID, "dqn_train_step_table: bad argument");
+  DQN_REQUIRE(k >= 1 && k <= net->MB, DQN_ERR_INVALID, "dqn_train_step_table: minibatch %d outside [1, max_batch=%d]", k, net->MB);
+  DQN_REQUIRE(dqn_replay_device_(replay) == net->device, DQN_ERR_INVALID, "replay and net live on different devices");
+  DQN_REQUIRE(!data_parallel || (net->dp_world >= 2 && net->dp_peer_flags_dev), DQN_ERR_STATE,
+              "dqn_train_step_table: call dqn_net_dp_connect first");
+  RingView rv;
+  dqn_replay_view_(replay, &rv);
+  DQN_REQUIRE((size_t)rv.frame_bytes * rv.frames_per_state == net->state_bytes, DQN_ERR_INVALID,
+              "replay stacks are %d bytes but the net expects %zu", rv.frame_bytes * rv.frames_per_state, net->state_bytes);
+  DeviceGuard g(net->device);
+  const IndexTableRef tab{d_table, rows, d_cursor, d_idx_scratch};
+  return step_from_ring(net, replay, nullptr, k, d_loss, data_parallel ? 2 : 0, static_cast<cudaStream_t>(stream), &tab);
 }
 
 // ---------------------------------------------------------------------------------------------- peer-memory data parallelism

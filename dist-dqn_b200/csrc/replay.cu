@@ -748,13 +748,16 @@ __global__ void __launch_bounds__(256) index_table_next_kernel(const int32_t* __
   if (threadIdx.x == 0) *cursor = cur + 1;
 }
 
-extern "C" int dqn_index_table_next(const int32_t* d_table, int64_t rows, int32_t k, int64_t* d_cursor, int32_t* d_idx,
-                                    dqn_stream_t stream) {
+int dqn_index_table_next_(const int32_t* d_table, int64_t rows, int32_t k, int64_t* d_cursor, int32_t* d_idx, cudaStream_t st) {
   DQN_REQUIRE(d_table && d_cursor && d_idx && rows > 0 && k > 0, DQN_ERR_INVALID, "index_table_next: bad argument");
   dqn::count_launch();
-  DQN_CUDA(launch_pdl(index_table_next_kernel, dim3(1), dim3(256), 0, static_cast<cudaStream_t>(stream), 1, d_table,
-                      (long long)rows, (int)k, reinterpret_cast<long long*>(d_cursor), d_idx));
+  DQN_CUDA(launch_pdl(index_table_next_kernel, dim3(1), dim3(256), 0, st, 1, d_table, (long long)rows, (int)k,
+                      reinterpret_cast<long long*>(d_cursor), d_idx));
   return 0;
+}
+extern "C" int dqn_index_table_next(const int32_t* d_table, int64_t rows, int32_t k, int64_t* d_cursor, int32_t* d_idx,
+                                    dqn_stream_t stream) {
+  return dqn_index_table_next_(d_table, rows, k, d_cursor, d_idx, static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int dqn_replay_gather(dqn_replay_t h, const int32_t* d_logical_idx, int32_t k, void* d_states,

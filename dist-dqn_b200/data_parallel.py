@@ -93,6 +93,16 @@ def setup_network(network, config, mode='peer'):
     return world
 
 
+def train_step_table(network, replay_memory, index_table, want_loss=False, loss_out=None):
+    """``train_step`` on the current row of a device-resident ``replay_memory.IndexTable`` (the update advances the
+    table's cursor): single GPU or peer-memory exchange; the NCCL path takes the row with ``IndexTable.next``."""
+    if not is_distributed() or getattr(network, 'peers_connected', False):
+        return network.train_step_table(replay_memory, index_table, want_loss=want_loss, loss_out=loss_out,
+                                        data_parallel=is_distributed())
+    return train_step(network, replay_memory, index_table.k, index_table.next(index_table.scratch), want_loss=want_loss,
+                      loss_out=loss_out)
+
+
 def train_step(network, replay_memory, k, d_indices, want_loss=False, loss_out=None):
     """One synchronous update from this rank's replay shard: single GPU, peer-memory exchange, or NCCL all-reduce,
     whichever the network was set up for.  Every rank must call it the same number of times."""

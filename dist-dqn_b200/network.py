@@ -263,6 +263,17 @@ class Network(object):
                                        out.data_ptr() if want_loss else None, _c.current_stream()), 'train_step')
         return out
 
+    def train_step_table(self, replay_memory, index_table, want_loss=False, loss_out=None, data_parallel=False):
+        """``train_step`` (or ``dp_train_step``) on the current row of a ``replay_memory.IndexTable``: the update reads
+        its pre-drawn sample indices from the device-resident table and advances the table's cursor itself, so a
+        captured update replays with no per-update work on the indices (dqn_train_step_table)."""
+        out = (loss_out if loss_out is not None else self._loss) if want_loss else None
+        _c.check(_c.lib.dqn_train_step_table(self._h, replay_memory.handle, _c.ptr(index_table.table), index_table.rows,
+                                             index_table.k, _c.ptr(index_table.cursor), _c.ptr(index_table.scratch),
+                                             out.data_ptr() if want_loss else None, 1 if data_parallel else 0,
+                                             _c.current_stream()), 'train_step_table')
+        return out
+
     # ------------------------------------------------------------------ checkpoint / resume
     def save(self, path, extra=None):
         """Everything needed to resume training -- the reference got this from tf.train.Supervisor's Saver

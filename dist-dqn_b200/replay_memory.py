@@ -337,6 +337,7 @@ class IndexTable(object):
             self.table = torch.tensor(rows_of_indices, dtype=torch.int32, device=device).contiguous()
         self.rows, self.k = int(self.table.shape[0]), int(self.table.shape[1])
         self.cursor = torch.zeros(1, dtype=torch.int64, device=device)
+        self.scratch = torch.empty(self.k, dtype=torch.int32, device=device)     # for kernels that take the row as a plain array
 
     def next(self, d_idx):
         _c.check(_c.lib.dqn_index_table_next(_c.ptr(self.table), self.rows, self.k, _c.ptr(self.cursor), _c.ptr(d_idx),

@@ -270,6 +270,14 @@ int dqn_net_refresh_operands(dqn_net_t h, int32_t which, dqn_stream_t stream);
 int dqn_train_step(dqn_net_t net, dqn_replay_t replay, const int32_t* d_logical_idx, int32_t k, float* d_loss,
                    dqn_stream_t stream);
 
+/* dqn_train_step / dqn_train_step_dp (data_parallel != 0) on row (*d_cursor % rows) of a device-resident [rows][k] table
+ * of pre-drawn index sets (see dqn_index_table_next); the update advances *d_cursor itself, so a captured update replays
+ * with no per-update work on the indices at all.  The conv1 kernels of the reference architecture in 16-bit mode read
+ * the row directly; every other configuration first copies it to d_idx_scratch [k] with one small kernel. */
+int dqn_train_step_table(dqn_net_t net, dqn_replay_t replay, const int32_t* d_table, int64_t rows, int32_t k,
+                         int64_t* d_cursor, int32_t* d_idx_scratch, float* d_loss, int32_t data_parallel,
+                         dqn_stream_t stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Frame preprocessing on the device -- utils.resize_image (utils.py:39-45: cv2.cvtColor(RGB2GRAY) then
  * cv2.resize, bilinear), bit-exact with OpenCV's fixed-point uint8 paths.  d_rgb: n frames uint8

@@ -233,3 +233,51 @@ def test_sample_to_update_call_equals_gather_then_train():
     assert l1 == l2.item()
     for g, e in zip(nets[0].get_params(), nets[1].get_params()):
         assert np.array_equal(g, e)
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_update_on_an_index_table_equals_update_on_the_same_indices(precision):
+    """dqn_train_step_table: three updates that read their rows of a device-resident index table (and advance its
+    cursor themselves, also inside one captured graph) == three dqn_train_step calls on the same rows, bit for bit.
+    bf16: the conv1 kernels read the table directly; fp32: a small kernel copies the row first."""
+    import random
+    import torch
+    import replay_memory
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    A, B = 6, 16
+    rng = np.random.default_rng(0)
+    rm = replay_memory.ReplayMemory(200)
+    state = np.repeat(rng.integers(0, 256, (84, 84, 1), dtype=np.uint8), 4, axis=2)
+    for i in range(120):
+        nxt = np.concatenate([state[..., 1:], rng.integers(0, 256, (84, 84, 1), dtype=np.uint8)], axis=-1)
+        rm.add(state, int(rng.integers(0, A)), float(rng.integers(-1, 2)), nxt, bool(i % 17 == 16))
+        state = nxt
+    nets = []
+    for _ in range(2):
+        net, cfg = _net("cnn", (84, 84, 4), A, B, precision=precision)
+        net.set_params(oracle_params("cnn", (84, 84, 4), A, 11))
+        net.sync_target()
+        nets.append(net)
+    random.seed(3)
+    rows = [rm.sample_indices(B) for _ in range(2)]          # 2 rows, 3 updates: the third wraps to row 0
+    table = replay_memory.IndexTable(rows, torch.device("cuda", 0))
+    losses = []
+    side = torch.cuda.Stream()
+    with torch.cuda.stream(side):
+        losses.append(nets[0].train_step_table(rm, table, want_loss=True).item())
+        g = torch.cuda.CUDAGraph()
+        loss_buf = torch.zeros(1, dtype=torch.float32, device="cuda")
+        with torch.cuda.graph(g, stream=side):
+            nets[0].train_step_table(rm, table, want_loss=True, loss_out=loss_buf)
+        torch.cuda.synchronize()
+        assert int(table.cursor.item()) == 1             # capture does not execute
+        for _ in range(2):
+            g.replay()
+            losses.append(loss_buf.item())
+    assert int(table.cursor.item()) == 3
+    for u in range(3):
+        l = nets[1].train_step(rm, B, d_indices=rm.upload_indices(rows[u % 2]), want_loss=True).item()
+        assert l == losses[u], (u, l, losses[u])
+    for a, e in zip(nets[0].get_params(), nets[1].get_params()):
+        assert np.array_equal(a, e)

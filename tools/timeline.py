@@ -8,7 +8,7 @@ import random
 import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "dist-dqn_b200"))
-ap = argparse.ArgumentParser(); ap.add_argument("--batch", type=int, default=32); ap.add_argument("--eager", action="store_true")
+ap = argparse.ArgumentParser(); ap.add_argument("--batch", type=int, default=32); ap.add_argument("--eager", action="store_true"); ap.add_argument("--copy-indices", action="store_true")
 a = ap.parse_args()
 import torch
 import __graft_entry__ as ge
@@ -32,12 +32,17 @@ side = torch.cuda.Stream()
 with torch.cuda.stream(side):
     for _ in range(3):
         dp.train_step(net, rm, a.batch, d_idx)
+    cursor = replay_memory.IndexTable(tab, dev)
     g = torch.cuda.CUDAGraph()
     with torch.cuda.graph(g, stream=side):
-        dp.train_step(net, rm, a.batch, d_idx)
+        if a.copy_indices:
+            dp.train_step(net, rm, a.batch, d_idx)
+        else:
+            dp.train_step_table(net, rm, cursor)      # as bench.py: the update takes its own row of the index table
 
     def step(i):
-        d_idx.copy_(tab[i % 64], non_blocking=True)
+        if a.eager or a.copy_indices:
+            d_idx.copy_(tab[i % 64], non_blocking=True)
         if a.eager:
             dp.train_step(net, rm, a.batch, d_idx)
         else:
@@ -54,7 +59,7 @@ evs.sort(key=lambda e: e.time_range.start)
 # split into steps at the index copy (memcpy DtoD) that precedes every update
 steps, cur = [], []
 for e in evs:
-    if "Memcpy" in e.name or "memcpy" in e.name:
+    if "Memcpy" in e.name or "memcpy" in e.name or "index_table_next" in e.name or (not a.copy_indices and "conv1_s2d_fwd" in e.name):
         if cur:
             steps.append(cur)
         cur = []
@@ -68,7 +73,7 @@ if rank != 0:
     sys.exit(0)
 st = steps[-2]
 t0 = st[0].time_range.start
-print("kernels of one update (us from the index copy): start, duration, name")
+print("kernels of one update (us from the index copy / index kernel): start, duration, name")
 for e in st:
     print("%8.2f %7.2f  %s" % (e.time_range.start - t0, e.time_range.end - e.time_range.start, e.name[:90]))
 print("update period: %.2f us" % (steps[-1][0].time_range.start - t0))
