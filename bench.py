@@ -494,6 +494,18 @@ def run_update_bench(args, torch, dist, dp, rank, local, world, dev):
 
         ms_total, per_rank_ms, clocks = _timed_steps(torch, dist, world, rank, local, dev, step, warmup, steps, after)
         ms_per_step = ms_total / steps
+        if world > 1 and dp_check is not None:
+            # after the timed updates: every rank must still hold bit-identical weights (a stale read in the exchange
+            # would have made the replicas drift apart for good), and no exchange wait may have timed out
+            wa = net.flat_buffer("online").clone()
+            ref = wa.clone()
+            dist.broadcast(ref, 0)
+            t = torch.tensor([0.0 if torch.equal(ref, wa) else 1.0], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            net.dp_status()
+            dp_check["weights_identical_after_timed_steps"] = t[0].item() == 0.0
+            if t[0].item() != 0.0:
+                dp_check["result"] = "FAILED"
         # whole-job aggregate: per-GPU minibatches of `batch` samples processed per second, summed over ranks
         # (one synchronous update = `world` such minibatches)
         value = world * steps / (ms_total / 1e3)
