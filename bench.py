@@ -445,7 +445,7 @@ def run_update_bench(args, torch, dist, dp, rank, local, world, dev):
         size = rm.size()
         # sample indices for every step, drawn with the reference's own sampler and uploaded before timing
         random.seed(1234 + rank)
-        total_steps = warmup + steps
+        total_steps = warmup + 3 + steps          # warm-up, the 3 untimed synchronised steps of _timed_steps, timed steps: no row is used twice
         idx_table = torch.tensor([random.sample(range(size), batch) for _ in range(total_steps)], dtype=torch.int32,
                                  device=dev)
         d_idx = torch.empty(batch, dtype=torch.int32, device=dev)
