@@ -20,6 +20,20 @@ def test_library_exports_every_declared_symbol():
     assert _cabi.lib.dqn_version() >= 100
 
 
+def test_ctypes_signatures_have_the_arity_of_the_header():
+    import __graft_entry__ as ge
+    ge.build()
+    import _cabi
+    hdr = open(os.path.join(ROOT, "include", "dqn_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    decls = re.findall(r"\b(dqn_[a-z0-9_]+)\s*\(([^()]*)\)\s*;", hdr)
+    assert len(decls) >= 25
+    for name, params in decls:
+        params = params.strip()
+        n = 0 if params in ("", "void") else params.count(",") + 1
+        assert n == len(_cabi.SIGNATURES[name][1]), "%s: header has %d parameters, _cabi.py %d" % (name, n, len(_cabi.SIGNATURES[name][1]))
+
+
 def test_no_cuda_device_fails_loudly_not_silently():
     import torch
     if torch.cuda.is_available():
